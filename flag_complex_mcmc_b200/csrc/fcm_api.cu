@@ -1,0 +1,222 @@
+// fcm_api.cu — the extern "C" surface of libfcm.so (include/fcm.h) and the host-side setup.
+#include "fcm_internal.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <thread>
+
+// ---------------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+void fcm_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+extern "C" const char* fcm_last_error(void) { return g_err; }
+extern "C" int fcm_abi_version(void) { return FCM_ABI_VERSION; }
+extern "C" int fcm_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+extern "C" void fcm_free(void* p) { free(p); }
+
+#define REQUIRE(cond, msg)                                 \
+  do {                                                     \
+    if (!(cond)) { fcm_set_error("%s", msg); return FCM_EINVAL; } \
+  } while (0)
+
+static int use_ctx(const fcm_ctx* c) {
+  FCM_CUDA(cudaSetDevice(c->device));
+  return FCM_OK;
+}
+#define USE(c)                          \
+  do {                                  \
+    int rc__ = use_ctx(c);              \
+    if (rc__) return rc__;              \
+  } while (0)
+
+// ---------------------------------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------------------------------
+extern "C" int fcm_ctx_create(int device, fcm_ctx** out) {
+  REQUIRE(out, "fcm_ctx_create: out is null");
+  *out = nullptr;
+  int ndev = fcm_device_count();
+  if (ndev <= 0) { fcm_set_error("no CUDA device available (libfcm has no CPU fallback)"); return FCM_ENODEVICE; }
+  if (device < 0 || device >= ndev) { fcm_set_error("device ordinal %d out of range (0..%d)", device, ndev - 1); return FCM_EINVAL; }
+  FCM_CUDA(cudaSetDevice(device));
+  fcm_ctx* c = new fcm_ctx();
+  c->device = device;
+  cudaDeviceProp prop;
+  FCM_CUDA(cudaGetDeviceProperties(&prop, device));
+  c->sm_count = prop.multiProcessorCount;
+  c->smem_optin = prop.sharedMemPerBlockOptin;
+  FCM_CUDA(cudaStreamCreateWithFlags(&c->own, cudaStreamNonBlocking));
+  c->stream = c->own;
+  FCM_CUDA(cudaEventCreate(&c->ev0));
+  FCM_CUDA(cudaEventCreate(&c->ev1));
+  *out = c;
+  return FCM_OK;
+}
+extern "C" int fcm_ctx_destroy(fcm_ctx* c) {
+  if (!c) return FCM_OK;
+  USE(c);
+  cudaStreamSynchronize(c->stream);
+  cudaEventDestroy(c->ev0);
+  cudaEventDestroy(c->ev1);
+  cudaStreamDestroy(c->own);
+  delete c;
+  return FCM_OK;
+}
+extern "C" int fcm_ctx_set_stream(fcm_ctx* c, void* s) {
+  REQUIRE(c, "ctx is null");
+  c->stream = s ? (cudaStream_t)s : c->own;
+  return FCM_OK;
+}
+extern "C" int fcm_ctx_synchronize(fcm_ctx* c) {
+  REQUIRE(c, "ctx is null");
+  USE(c);
+  FCM_CUDA(cudaStreamSynchronize(c->stream));
+  return FCM_OK;
+}
+extern "C" int fcm_ctx_timer_begin(fcm_ctx* c) {
+  REQUIRE(c, "ctx is null");
+  USE(c);
+  FCM_CUDA(cudaEventRecord(c->ev0, c->stream));
+  return FCM_OK;
+}
+extern "C" int fcm_ctx_timer_end(fcm_ctx* c, float* ms) {
+  REQUIRE(c && ms, "ctx/ms is null");
+  USE(c);
+  FCM_CUDA(cudaEventRecord(c->ev1, c->stream));
+  FCM_CUDA(cudaEventSynchronize(c->ev1));
+  FCM_CUDA(cudaEventElapsedTime(ms, c->ev0, c->ev1));
+  return FCM_OK;
+}
+extern "C" uint64_t fcm_ctx_launches(const fcm_ctx* c) { return c ? c->launches : 0; }
+
+// ---------------------------------------------------------------------------------------------------
+// device graph
+// ---------------------------------------------------------------------------------------------------
+static int graph_create(fcm_ctx* c, u32 n, u64 ne, const uint32_t (*edges)[2], int normalise, fcm_graph** out) {
+  REQUIRE(c && out, "ctx/out is null");
+  REQUIRE(ne == 0 || edges, "edges is null");
+  *out = nullptr;
+  USE(c);
+  fcm_graph* g = new fcm_graph();
+  g->ctx = c;
+  g->n = n;
+  g->W = ((n + 63) / 64 + 1) & ~1u;                  // even number of words: 16-byte row stride
+  if (g->W == 0) g->W = 2;
+  int rc = FCM_OK;
+  uint2* edges_dev = nullptr;
+  std::vector<u64> off;
+  auto fail = [&](int code) { if (edges_dev) cudaFree(edges_dev); fcm_graph_destroy(g); return code; };
+#define G_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { fcm_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); return fail(FCM_ECUDA); } } while (0)
+  G_CUDA(cudaMalloc(&g->adj, std::max<size_t>((size_t)n * g->W, 2) * 8));
+  G_CUDA(cudaMalloc(&g->csr_off, ((size_t)n + 1) * 8));
+  G_CUDA(cudaMalloc(&g->order, std::max<u32>(n, 1) * 4));
+  G_CUDA(cudaMalloc(&g->overflow, std::max<u32>(n, 1) * 4));
+  G_CUDA(cudaMalloc(&g->counts, FCM_MAXD * 8));
+  G_CUDA(cudaMalloc(&g->ctrl, CT_WORDS * 4));
+  if (ne) {
+    G_CUDA(cudaMalloc(&edges_dev, ne * 8));
+    G_CUDA(cudaMemcpyAsync(edges_dev, edges, ne * 8, cudaMemcpyHostToDevice, c->stream));
+  }
+  rc = fcm_graph_build_device(g, edges_dev, ne, normalise, off);
+  if (rc) return fail(rc);
+  // source vertices by descending out-degree: the heavy ones start first and shards
+  // (part, nparts) taken round-robin from this order are degree-balanced
+  std::vector<u32> order(n);
+  for (u32 v = 0; v < n; v++) order[v] = v;
+  std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) { return off[a + 1] - off[a] > off[b + 1] - off[b]; });
+  if (n) G_CUDA(cudaMemcpyAsync(g->order, order.data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+  G_CUDA(cudaStreamSynchronize(c->stream));
+  if (edges_dev) cudaFree(edges_dev);
+#undef G_CUDA
+  *out = g;
+  return FCM_OK;
+}
+extern "C" int fcm_graph_create(fcm_ctx* c, uint32_t n, uint64_t ne, const uint32_t (*edges)[2], fcm_graph** out) {
+  return graph_create(c, n, ne, edges, 0, out);
+}
+extern "C" int fcm_graph_create_normalised(fcm_ctx* c, uint32_t n, uint64_t ne, const uint32_t (*edges)[2], fcm_graph** out) {
+  return graph_create(c, n, ne, edges, 1, out);
+}
+extern "C" int fcm_graph_destroy(fcm_graph* g) {
+  if (!g) return FCM_OK;
+  if (g->ctx) cudaSetDevice(g->ctx->device);
+  cudaFree(g->adj); cudaFree(g->csr_off); cudaFree(g->csr); cudaFree(g->order);
+  cudaFree(g->overflow); cudaFree(g->counts); cudaFree(g->ctrl); cudaFree(g->scratch);
+  delete g;
+  return FCM_OK;
+}
+extern "C" int fcm_graph_set_kernel(fcm_graph* g, int kind) {
+  REQUIRE(g, "graph is null");
+  REQUIRE(kind == 0 || kind == 1, "kernel kind must be 0 (auto) or 1 (dense-row)");
+  g->kernel_kind = kind;
+  return FCM_OK;
+}
+extern "C" int fcm_graph_info(const fcm_graph* g, uint32_t* n, uint64_t* ne, uint32_t* W, uint32_t* maxout) {
+  REQUIRE(g, "graph is null");
+  if (n) *n = g->n;
+  if (ne) *ne = g->ne;
+  if (W) *W = g->W;
+  if (maxout) *maxout = g->maxout;
+  return FCM_OK;
+}
+extern "C" int fcm_graph_count_async(fcm_graph* g, uint32_t part, uint32_t nparts, uint64_t** counts_dev) {
+  REQUIRE(g, "graph is null");
+  REQUIRE(nparts >= 1 && part < nparts, "need part < nparts");
+  USE(g->ctx);
+  int rc = fcm_count_launch(g, part, nparts);
+  if (rc) return rc;
+  if (counts_dev) *counts_dev = g->counts;
+  return FCM_OK;
+}
+extern "C" int fcm_graph_count(fcm_graph* g, uint32_t part, uint32_t nparts, uint64_t* counts, int* len) {
+  REQUIRE(counts && len, "counts/len is null");
+  int rc = fcm_graph_count_async(g, part, nparts, nullptr);
+  if (rc) return rc;
+  u32 ctrl[CT_WORDS];
+  FCM_CUDA(cudaMemcpyAsync(counts, g->counts, FCM_MAXD * 8, cudaMemcpyDeviceToHost, g->ctx->stream));
+  FCM_CUDA(cudaMemcpyAsync(ctrl, g->ctrl, sizeof(ctrl), cudaMemcpyDeviceToHost, g->ctx->stream));
+  FCM_CUDA(cudaStreamSynchronize(g->ctx->stream));
+  if (ctrl[CT_ERR]) { fcm_set_error("a simplex of dimension >= %d was met", FCM_MAXD); return FCM_EDIM; }
+  int l = FCM_MAXD;
+  while (l > 0 && counts[l - 1] == 0) l--;
+  *len = l;
+  return FCM_OK;
+}
+
+// flagser_count_unweighted precedent (src/flagser.rs:7-21): malloc'd result, NULL on error
+static std::mutex g_default_mu;
+static fcm_ctx* g_default_ctx = nullptr;
+extern "C" size_t* fcm_count_unweighted(size_t nvertices, size_t nedges, const uint32_t (*edges)[2], size_t* res_size) {
+  if (!res_size) { fcm_set_error("res_size is null"); return nullptr; }
+  *res_size = 0;
+  if (nvertices > 0xffffffffull) { fcm_set_error("too many vertices"); return nullptr; }
+  std::lock_guard<std::mutex> lk(g_default_mu);
+  if (!g_default_ctx && fcm_ctx_create(0, &g_default_ctx)) return nullptr;
+  fcm_graph* g = nullptr;
+  if (fcm_graph_create(g_default_ctx, (u32)nvertices, nedges, edges, &g)) return nullptr;
+  u64 counts[FCM_MAXD];
+  int len = 0;
+  int rc = fcm_graph_count(g, 0, 1, counts, &len);
+  fcm_graph_destroy(g);
+  if (rc) return nullptr;
+  size_t* res = (size_t*)malloc(sizeof(size_t) * (len ? len : 1));
+  if (!res) { fcm_set_error("out of host memory"); return nullptr; }
+  for (int i = 0; i < len; i++) res[i] = (size_t)counts[i];
+  *res_size = (size_t)len;
+  return res;
+}

@@ -1,0 +1,425 @@
+// fcm_ensemble.cu — host side of the chain ensemble: builds the static structures
+// (undirected pairs, common-neighbour CSR = compute_edge_neighborhoods, src/lib.rs:331-356), the
+// initial edge containers in insertion order, uploads them and replicates them per chain.
+#include "fcm_internal.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <thread>
+
+#define REQUIRE(cond, msg)                                 \
+  do {                                                     \
+    if (!(cond)) { fcm_set_error("%s", msg); return FCM_EINVAL; } \
+  } while (0)
+
+static inline u64 pkey(u32 big, u32 small) { return ((u64)big << 32) | small; }
+
+// rand 0.8 SplitMix64 seeding of xoshiro256** (Xoshiro256StarStar::seed_from_u64, src/bin/sample.rs:86)
+static void seed_from_u64(u64 seed, u64 s[4]) {
+  u64 x = seed;
+  for (int i = 0; i < 4; i++) {
+    x += 0x9e3779b97f4a7c15ULL;
+    u64 z = x;
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+    s[i] = z ^ (z >> 31);
+  }
+}
+
+// rand 0.8 WeightedIndex<f64>::new + Uniform<f64>::new(0, total)
+static int weighted_index_init(const double w[4], double cum[3], double* scale) {
+  double total = w[0];
+  for (int i = 0; i < 4; i++) if (!(w[i] >= 0.0) || !std::isfinite(w[i])) { fcm_set_error("move weight %d is invalid", i); return FCM_EINVAL; }
+  for (int i = 1; i < 4; i++) { cum[i - 1] = total; total += w[i]; }
+  if (!(total > 0.0)) { fcm_set_error("all move weights are zero"); return FCM_EINVAL; }
+  const double max_rand = 1.0 - 2.220446049250313e-16;
+  double sc = total;
+  for (;;) {
+    volatile double prod = sc * max_rand;
+    if (prod + 0.0 < total) break;
+    u64 b; memcpy(&b, &sc, 8); b -= 1; memcpy(&sc, &b, 8);
+  }
+  *scale = sc;
+  return FCM_OK;
+}
+
+template <typename T>
+static int dev_alloc(fcm_ensemble* e, T** p, size_t count) {
+  void* q = nullptr;
+  cudaError_t err = cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T));
+  if (err != cudaSuccess) {
+    fcm_set_error("cudaMalloc of %zu bytes failed: %s", count * sizeof(T), cudaGetErrorString(err));
+    return err == cudaErrorMemoryAllocation ? FCM_ENOMEM : FCM_ECUDA;
+  }
+  e->dev_allocs.push_back(q);
+  *p = (T*)q;
+  return FCM_OK;
+}
+
+static int copy_bounds(EnsParams& p, const u64* mn, int nmin, const u64* mx, int nmax) {
+  REQUIRE(nmin >= 0 && nmin <= FCM_MAXB && nmax >= 0 && nmax <= FCM_MAXB, "bounds longer than FCM_MAXD+1");
+  REQUIRE((nmin == 0 || mn) && (nmax == 0 || mx), "bounds pointer is null");
+  memset(p.bmin, 0, sizeof(p.bmin));
+  memset(p.bmax, 0, sizeof(p.bmax));
+  for (int i = 0; i < nmin; i++) p.bmin[i] = mn[i];
+  for (int i = 0; i < nmax; i++) p.bmax[i] = mx[i];
+  p.nmin = nmin; p.nmax = nmax;
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_destroy(fcm_ensemble* e) {
+  if (!e) return FCM_OK;
+  if (e->ctx) { cudaSetDevice(e->ctx->device); cudaStreamSynchronize(e->ctx->stream); }
+  for (void* q : e->dev_allocs) cudaFree(q);
+  if (e->trace_dev) cudaFree(e->trace_dev);
+  delete e;
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, const uint32_t (*edges)[2],
+                                   uint32_t nchains, const uint64_t* seeds,
+                                   const uint64_t* flag_count0, int len0,
+                                   const uint64_t* bounds_min, int nmin, const uint64_t* bounds_max, int nmax,
+                                   const double move_weights[4], fcm_ensemble** out) {
+  REQUIRE(ctx && out, "ctx/out is null");
+  *out = nullptr;
+  REQUIRE(nedges == 0 || edges, "edges is null");
+  REQUIRE(nchains >= 1 && seeds, "need at least one chain and its seed");
+  REQUIRE(flag_count0 && len0 >= 0 && len0 <= FCM_MAXD, "flag_count0 missing or longer than FCM_MAXD");
+  REQUIRE(move_weights, "move_weights is null");
+  if (move_weights[2] != 0.0 || move_weights[3] != 0.0) {
+    fcm_set_error("clique_permute / clique_swap moves are not implemented (weights must be 0)");
+    return FCM_EUNSUPPORTED;
+  }
+  FCM_CUDA(cudaSetDevice(ctx->device));
+  fcm_ensemble* e = new fcm_ensemble();
+  e->ctx = ctx;
+  EnsParams& p = e->p;
+  memset(&p, 0, sizeof(p));
+  int rc;
+  auto fail = [&](int code) { fcm_ensemble_destroy(e); return code; };
+  if ((rc = copy_bounds(p, bounds_min, nmin, bounds_max, nmax))) return fail(rc);
+  if ((rc = weighted_index_init(move_weights, p.cum, &p.scale))) return fail(rc);
+  p.n = n; p.nchains = nchains;
+  p.W = ((n + 63) / 64 + 1) & ~1u;
+  if (p.W == 0) p.W = 2;
+
+  // ---- pairs, slots, containers: replay Graph::add_edge in edge-list order (src/io.rs:26-33) ----
+  std::vector<uint2> pair_ab;
+  std::vector<u32> items, pos, dbl, dblpos;
+  std::vector<u64> adj((size_t)n * p.W, 0);
+  e->pairmap.reserve(nedges * 2);
+  for (u64 i = 0; i < nedges; i++) {
+    u32 a = edges[i][0], b = edges[i][1];
+    if (a >= n || b >= n || a == b) { fcm_set_error("edge %llu = (%u,%u): vertex id >= n or self loop", (unsigned long long)i, a, b); return fail(FCM_EINVAL); }
+    u32 big = std::max(a, b), small = std::min(a, b);
+    auto it = e->pairmap.find(pkey(big, small));
+    u32 pair;
+    if (it == e->pairmap.end()) {
+      pair = (u32)pair_ab.size();
+      e->pairmap.emplace(pkey(big, small), pair);
+      pair_ab.push_back(make_uint2(big, small));
+      pos.push_back(FCM_NONE); pos.push_back(FCM_NONE);
+      dblpos.push_back(FCM_NONE);
+    } else pair = it->second;
+    u32 slot = 2 * pair + (a > b ? 0u : 1u);
+    if (pos[slot] != FCM_NONE) continue;               // duplicate line: IndexSet insert is a no-op
+    pos[slot] = (u32)items.size();
+    items.push_back(slot);
+    adj[(size_t)a * p.W + (b >> 6)] |= 1ULL << (b & 63);
+    if (pos[slot ^ 1] != FCM_NONE) { dblpos[pair] = (u32)dbl.size(); dbl.push_back(pair); }
+  }
+  p.npairs = pair_ab.size();
+  e->ne0 = items.size(); e->nd0 = dbl.size();
+  if (p.npairs > 0x7fffffffULL) { fcm_set_error("too many adjacent pairs"); return fail(FCM_EINVAL); }
+  if (len0 >= 2 && flag_count0[1] != e->ne0) { fcm_set_error("flag_count0[1] = %llu but the graph has %llu edges", (unsigned long long)flag_count0[1], (unsigned long long)e->ne0); return fail(FCM_EINVAL); }
+
+  // ---- compute_edge_neighborhoods (src/lib.rs:331-356): sorted common undirected neighbours ----
+  std::vector<std::vector<u32>> und(n);
+  for (const uint2& ab : pair_ab) { und[ab.x].push_back(ab.y); und[ab.y].push_back(ab.x); }
+  int nthreads = (int)std::max(1u, std::min(std::thread::hardware_concurrency(), 32u));
+  {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; t++) th.emplace_back([&, t]() { for (u32 v = t; v < n; v += nthreads) std::sort(und[v].begin(), und[v].end()); });
+    for (auto& t : th) t.join();
+  }
+  std::vector<u64> nb_off(p.npairs + 1, 0);
+  auto intersect = [&](u32 a, u32 b, u32* outp) -> u32 {
+    const std::vector<u32>&A = und[a], &B = und[b];
+    size_t i = 0, j = 0; u32 c = 0;
+    while (i < A.size() && j < B.size()) {
+      if (A[i] == B[j]) { if (outp) outp[c] = A[i]; c++; i++; j++; }
+      else if (A[i] < B[j]) i++; else j++;
+    }
+    return c;
+  };
+  {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; t++) th.emplace_back([&, t]() { for (u64 q = t; q < p.npairs; q += nthreads) nb_off[q + 1] = intersect(pair_ab[q].x, pair_ab[q].y, nullptr); });
+    for (auto& t : th) t.join();
+  }
+  u32 maxc = 0;
+  for (u64 q = 0; q < p.npairs; q++) { maxc = std::max<u32>(maxc, (u32)nb_off[q + 1]); nb_off[q + 1] += nb_off[q]; }
+  std::vector<u32> nb_list(std::max<u64>(nb_off[p.npairs], 1));
+  {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; t++) th.emplace_back([&, t]() { for (u64 q = t; q < p.npairs; q += nthreads) intersect(pair_ab[q].x, pair_ab[q].y, &nb_list[nb_off[q]]); });
+    for (auto& t : th) t.join();
+  }
+  p.maxc = maxc;
+  u32 kneed = 2 * maxc + 4;                            // double-edge move: two pairs + four endpoints
+  p.Kcap = std::min<u32>(std::max<u32>(kneed, 8), 512);
+  u32 kw = (p.Kcap + 63) / 64;
+  p.KWcap = kw <= 1 ? 1 : kw <= 2 ? 2 : kw <= 4 ? 4 : 8;
+  e->smem_per_warp = fcm_chain_smem_per_warp(p.Kcap, p.KWcap);
+  e->warps_per_block = 4;
+  while (e->warps_per_block > 1 && e->smem_per_warp * e->warps_per_block > ctx->smem_optin) e->warps_per_block >>= 1;
+  if (e->smem_per_warp > ctx->smem_optin) { fcm_set_error("neighbourhood tile does not fit shared memory"); return fail(FCM_ELIMIT); }
+
+  // ---- device memory ----
+  const u64 nslots = 2 * p.npairs;
+  const u64 adjw = (u64)n * p.W;
+  e->bytes_per_chain = adjw * 8 + nslots * 8 + p.npairs * 8 + sizeof(ChainState);
+  uint2* d_pair; u64* d_off; u32* d_list;
+  if ((rc = dev_alloc(e, &d_pair, p.npairs))) return fail(rc);
+  if ((rc = dev_alloc(e, &d_off, p.npairs + 1))) return fail(rc);
+  if ((rc = dev_alloc(e, &d_list, nb_list.size()))) return fail(rc);
+  if ((rc = dev_alloc(e, &p.adj, adjw * nchains))) return fail(rc);
+  if ((rc = dev_alloc(e, &p.items, nslots * nchains))) return fail(rc);
+  if ((rc = dev_alloc(e, &p.pos, nslots * nchains))) return fail(rc);
+  if ((rc = dev_alloc(e, &p.dbl, p.npairs * nchains))) return fail(rc);
+  if ((rc = dev_alloc(e, &p.dblpos, p.npairs * nchains))) return fail(rc);
+  if ((rc = dev_alloc(e, &p.st, (size_t)nchains))) return fail(rc);
+  if ((rc = dev_alloc(e, &e->edit_dev, (size_t)FCM_MAXEDIT * 2))) return fail(rc);
+  if ((rc = dev_alloc(e, &e->io_dev, (size_t)2 * FCM_MAXD + 8))) return fail(rc);
+  p.pair_ab = d_pair; p.nb_off = d_off; p.nb_list = d_list;
+  cudaStream_t s = ctx->stream;
+#define E_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { fcm_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); return fail(FCM_ECUDA); } } while (0)
+  items.resize(nslots, 0); dbl.resize(p.npairs, 0);
+  if (p.npairs) {
+    E_CUDA(cudaMemcpyAsync(d_pair, pair_ab.data(), p.npairs * 8, cudaMemcpyHostToDevice, s));
+    E_CUDA(cudaMemcpyAsync(p.items, items.data(), nslots * 4, cudaMemcpyHostToDevice, s));
+    E_CUDA(cudaMemcpyAsync(p.pos, pos.data(), nslots * 4, cudaMemcpyHostToDevice, s));
+    E_CUDA(cudaMemcpyAsync(p.dbl, dbl.data(), p.npairs * 4, cudaMemcpyHostToDevice, s));
+    E_CUDA(cudaMemcpyAsync(p.dblpos, dblpos.data(), p.npairs * 4, cudaMemcpyHostToDevice, s));
+  }
+  E_CUDA(cudaMemcpyAsync(d_off, nb_off.data(), (p.npairs + 1) * 8, cudaMemcpyHostToDevice, s));
+  E_CUDA(cudaMemcpyAsync(d_list, nb_list.data(), nb_list.size() * 4, cudaMemcpyHostToDevice, s));
+  if (adjw) E_CUDA(cudaMemcpyAsync(p.adj, adj.data(), adjw * 8, cudaMemcpyHostToDevice, s));
+  std::vector<ChainState> st(nchains);
+  for (u32 k = 0; k < nchains; k++) {
+    memset(&st[k], 0, sizeof(ChainState));
+    seed_from_u64(seeds[k], st[k].rng);
+    for (int d = 0; d < len0; d++) st[k].flag_count[d] = flag_count0[d];
+    st[k].fc_len = len0;
+    st[k].E = (u32)e->ne0; st[k].ND = (u32)e->nd0;
+  }
+  E_CUDA(cudaMemcpyAsync(p.st, st.data(), sizeof(ChainState) * nchains, cudaMemcpyHostToDevice, s));
+  if ((rc = fcm_chain_launch_replicate(e))) return fail(rc);
+  E_CUDA(cudaStreamSynchronize(s));
+#undef E_CUDA
+  e->pair_ab_host = std::move(pair_ab);
+  *out = e;
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_set_bounds(fcm_ensemble* e, const uint64_t* mn, int nmin, const uint64_t* mx, int nmax) {
+  REQUIRE(e, "ensemble is null");
+  return copy_bounds(e->p, mn, nmin, mx, nmax);
+}
+
+extern "C" int fcm_ensemble_info(const fcm_ensemble* e, uint32_t* n, uint64_t* npairs, uint32_t* nchains,
+                                 uint32_t* maxc, uint64_t* bytes_per_chain) {
+  REQUIRE(e, "ensemble is null");
+  if (n) *n = e->p.n;
+  if (npairs) *npairs = e->p.npairs;
+  if (nchains) *nchains = e->p.nchains;
+  if (maxc) *maxc = e->p.maxc;
+  if (bytes_per_chain) *bytes_per_chain = e->bytes_per_chain;
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_step(fcm_ensemble* e, uint64_t nproposals) {
+  REQUIRE(e, "ensemble is null");
+  FCM_CUDA(cudaSetDevice(e->ctx->device));
+  if (nproposals == 0) return FCM_OK;
+  return fcm_chain_launch_step(e, nproposals, nullptr, 0);
+}
+
+static const char* status_text(int st) {
+  switch (st) {
+    case FCM_EDIM: return "a simplex of dimension >= FCM_MAXD was met";
+    case FCM_EASSERT: return "flag_count would go negative (reference: assert!(*s >= *p), src/lib.rs:65,86)";
+    case FCM_ELIMIT: return "neighbourhood larger than the local-matrix capacity (512 vertices)";
+    case FCM_EINVAL: return "double_edge_move on a graph without single edges (reference loops forever, src/lib.rs:307)";
+    case FCM_EUNSUPPORTED: return "clique move drawn";
+    default: return "unknown device status";
+  }
+}
+
+extern "C" int fcm_ensemble_step_trace(fcm_ensemble* e, uint64_t nproposals, uint32_t chain, fcm_trace_rec* trace_out) {
+  REQUIRE(e && trace_out, "ensemble/trace_out is null");
+  REQUIRE(chain < e->p.nchains, "chain out of range");
+  FCM_CUDA(cudaSetDevice(e->ctx->device));
+  if (nproposals == 0) return FCM_OK;
+  if (nproposals > e->trace_cap) {
+    if (e->trace_dev) FCM_CUDA(cudaFree(e->trace_dev));
+    e->trace_dev = nullptr; e->trace_cap = 0;
+    FCM_CUDA(cudaMalloc(&e->trace_dev, nproposals * sizeof(fcm_trace_rec)));
+    e->trace_cap = nproposals;
+  }
+  FCM_CUDA(cudaMemsetAsync(e->trace_dev, 0, nproposals * sizeof(fcm_trace_rec), e->ctx->stream));
+  int rc = fcm_chain_launch_step(e, nproposals, e->trace_dev, chain);
+  if (rc) return rc;
+  FCM_CUDA(cudaMemcpyAsync(trace_out, e->trace_dev, nproposals * sizeof(fcm_trace_rec), cudaMemcpyDeviceToHost, e->ctx->stream));
+  FCM_CUDA(cudaStreamSynchronize(e->ctx->stream));
+  return fcm_ensemble_status(e);
+}
+
+static int fetch_states(fcm_ensemble* e, std::vector<ChainState>& st, u32 first, u32 count) {
+  st.resize(count);
+  FCM_CUDA(cudaSetDevice(e->ctx->device));
+  FCM_CUDA(cudaMemcpyAsync(st.data(), e->p.st + first, sizeof(ChainState) * count, cudaMemcpyDeviceToHost, e->ctx->stream));
+  FCM_CUDA(cudaStreamSynchronize(e->ctx->stream));
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_status(fcm_ensemble* e) {
+  REQUIRE(e, "ensemble is null");
+  std::vector<ChainState> st;
+  int rc = fetch_states(e, st, 0, e->p.nchains);
+  if (rc) return rc;
+  for (u32 k = 0; k < e->p.nchains; k++)
+    if (st[k].err) { fcm_set_error("chain %u: %s", k, status_text(st[k].err)); return st[k].err; }
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_read(fcm_ensemble* e, uint32_t chain, uint64_t* fc, int* len, uint64_t* sampled,
+                                 uint64_t* accepted, uint32_t* edges_out, uint64_t* nedges_out,
+                                 uint64_t* ndouble_out, uint64_t* rng_out) {
+  REQUIRE(e, "ensemble is null");
+  REQUIRE(chain < e->p.nchains, "chain out of range");
+  std::vector<ChainState> st;
+  int rc = fetch_states(e, st, chain, 1);
+  if (rc) return rc;
+  const ChainState& c = st[0];
+  if (fc) for (int d = 0; d < FCM_MAXD; d++) fc[d] = c.flag_count[d];
+  if (len) *len = c.fc_len;
+  if (sampled) *sampled = c.sampled;
+  if (accepted) *accepted = c.accepted;
+  if (nedges_out) *nedges_out = c.E;
+  if (ndouble_out) *ndouble_out = c.ND;
+  if (rng_out) memcpy(rng_out, c.rng, 32);
+  if (edges_out && c.E) {
+    std::vector<u32> items(c.E);
+    FCM_CUDA(cudaMemcpyAsync(items.data(), e->p.items + (u64)chain * 2 * e->p.npairs, (size_t)c.E * 4, cudaMemcpyDeviceToHost, e->ctx->stream));
+    FCM_CUDA(cudaStreamSynchronize(e->ctx->stream));
+    for (u32 i = 0; i < c.E; i++) {
+      uint2 ab = e->pair_ab_host[items[i] >> 1];
+      bool up = items[i] & 1;                          // dir 1: small -> big
+      edges_out[2 * i] = up ? ab.y : ab.x;
+      edges_out[2 * i + 1] = up ? ab.x : ab.y;
+    }
+  }
+  if (c.err) { fcm_set_error("chain %u: %s", chain, status_text(c.err)); return c.err; }
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_read_all(fcm_ensemble* e, uint64_t* fcs, int* lens, uint64_t* sampled,
+                                     uint64_t* accepted, uint64_t* stats) {
+  REQUIRE(e, "ensemble is null");
+  std::vector<ChainState> st;
+  int rc = fetch_states(e, st, 0, e->p.nchains);
+  if (rc) return rc;
+  u64 sk = 0, ne = 0;
+  int err = 0; u32 errchain = 0;
+  for (u32 k = 0; k < e->p.nchains; k++) {
+    if (fcs) memcpy(fcs + (size_t)k * FCM_MAXD, st[k].flag_count, FCM_MAXD * 8);
+    if (lens) lens[k] = st[k].fc_len;
+    if (sampled) sampled[k] = st[k].sampled;
+    if (accepted) accepted[k] = st[k].accepted;
+    sk += st[k].sumK;
+    ne += st[k].nonempty;
+    if (st[k].err && !err) { err = st[k].err; errchain = k; }
+  }
+  if (stats) { stats[0] = sk; stats[1] = ne; }
+  if (err) { fcm_set_error("chain %u: %s", errchain, status_text(err)); return err; }
+  return FCM_OK;
+}
+
+// ---- explicit-edit API: State::apply_transition / revert_transition (src/lib.rs:61-95) ----
+static int upload_edits(fcm_ensemble* e, const uint32_t* edits3, int nedits) {
+  REQUIRE(nedits >= 0 && nedits <= FCM_MAXEDIT, "too many edits (FCM_MAXEDIT = 64)");
+  REQUIRE(nedits == 0 || edits3, "edits is null");
+  u32 buf[2 * FCM_MAXEDIT];
+  for (int i = 0; i < nedits; i++) {
+    u32 a = edits3[3 * i], b = edits3[3 * i + 1];
+    auto it = a == b ? e->pairmap.end() : e->pairmap.find(pkey(std::max(a, b), std::min(a, b)));
+    if (it == e->pairmap.end()) {
+      fcm_set_error("edit %d: vertices %u and %u are not adjacent in the underlying undirected graph", i, a, b);
+      return FCM_ENOTADJ;
+    }
+    buf[2 * i] = 2 * it->second + (a > b ? 0u : 1u);
+    buf[2 * i + 1] = edits3[3 * i + 2] ? 1u : 0u;
+  }
+  if (nedits) FCM_CUDA(cudaMemcpyAsync(e->edit_dev, buf, (size_t)nedits * 8, cudaMemcpyHostToDevice, e->ctx->stream));
+  return FCM_OK;
+}
+
+extern "C" int fcm_apply(fcm_ensemble* e, uint32_t chain, const uint32_t* edits3, int nedits,
+                         uint64_t* pre, int* prelen, uint64_t* post, int* postlen) {
+  REQUIRE(e && pre && prelen && post && postlen, "null argument");
+  REQUIRE(chain < e->p.nchains, "chain out of range");
+  FCM_CUDA(cudaSetDevice(e->ctx->device));
+  int rc = upload_edits(e, edits3, nedits);
+  if (rc) return rc;
+  if ((rc = fcm_chain_launch_apply(e, chain, nedits, 0))) return rc;
+  u64 io[2 * FCM_MAXD + 8];
+  FCM_CUDA(cudaMemcpyAsync(io, e->io_dev, sizeof(io), cudaMemcpyDeviceToHost, e->ctx->stream));
+  FCM_CUDA(cudaStreamSynchronize(e->ctx->stream));
+  int st = (int)(long long)io[66];
+  if (st) { fcm_set_error("fcm_apply: %s", status_text(st)); return st; }
+  memcpy(pre, io, FCM_MAXD * 8);
+  memcpy(post, io + FCM_MAXD, FCM_MAXD * 8);
+  *prelen = (int)io[64]; *postlen = (int)io[65];
+  return FCM_OK;
+}
+
+extern "C" int fcm_revert(fcm_ensemble* e, uint32_t chain, const uint32_t* edits3, int nedits,
+                          const uint64_t* pre, int prelen, const uint64_t* post, int postlen) {
+  REQUIRE(e, "ensemble is null");
+  REQUIRE(chain < e->p.nchains, "chain out of range");
+  REQUIRE(prelen >= 0 && prelen <= FCM_MAXD && postlen >= 0 && postlen <= FCM_MAXD, "pre/post longer than FCM_MAXD");
+  REQUIRE((prelen == 0 || pre) && (postlen == 0 || post), "pre/post is null");
+  FCM_CUDA(cudaSetDevice(e->ctx->device));
+  int rc = upload_edits(e, edits3, nedits);
+  if (rc) return rc;
+  u64 io[2 * FCM_MAXD + 8];
+  memset(io, 0, sizeof(io));
+  for (int d = 0; d < prelen; d++) io[d] = pre[d];
+  for (int d = 0; d < postlen; d++) io[FCM_MAXD + d] = post[d];
+  io[64] = prelen; io[65] = postlen;
+  FCM_CUDA(cudaMemcpyAsync(e->io_dev, io, sizeof(io), cudaMemcpyHostToDevice, e->ctx->stream));
+  if ((rc = fcm_chain_launch_apply(e, chain, nedits, 1))) return rc;
+  FCM_CUDA(cudaMemcpyAsync(io, e->io_dev, sizeof(io), cudaMemcpyDeviceToHost, e->ctx->stream));
+  FCM_CUDA(cudaStreamSynchronize(e->ctx->stream));
+  int st = (int)(long long)io[66];
+  if (st) { fcm_set_error("fcm_revert: %s", status_text(st)); return st; }
+  return FCM_OK;
+}
+
+extern "C" int fcm_bounds_check(fcm_ensemble* e, uint32_t chain, int* ok) {
+  REQUIRE(e && ok, "null argument");
+  REQUIRE(chain < e->p.nchains, "chain out of range");
+  FCM_CUDA(cudaSetDevice(e->ctx->device));
+  int rc = fcm_chain_launch_apply(e, chain, 0, 2);
+  if (rc) return rc;
+  u64 io[2 * FCM_MAXD + 8];
+  FCM_CUDA(cudaMemcpyAsync(io, e->io_dev, sizeof(io), cudaMemcpyDeviceToHost, e->ctx->stream));
+  FCM_CUDA(cudaStreamSynchronize(e->ctx->stream));
+  *ok = (int)io[67];
+  return FCM_OK;
+}

@@ -1,0 +1,115 @@
+// fcm_internal.cuh — shared declarations of libfcm.so (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/fcm.h"
+
+typedef uint64_t u64;
+typedef uint32_t u32;
+
+#define FCM_NONE 0xffffffffu
+
+// ---- error plumbing ------------------------------------------------------------------------------
+void fcm_set_error(const char* fmt, ...);
+#define FCM_CUDA(call)                                                                       \
+  do {                                                                                       \
+    cudaError_t e__ = (call);                                                                \
+    if (e__ != cudaSuccess) {                                                                \
+      fcm_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__));  \
+      return FCM_ECUDA;                                                                      \
+    }                                                                                        \
+  } while (0)
+
+struct fcm_ctx {
+  int device = 0;
+  int sm_count = 0;
+  size_t smem_optin = 0;
+  cudaStream_t own = nullptr, stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  u64 launches = 0;
+};
+
+// ---- device graph for recounts ---------------------------------------------------------------------
+struct fcm_graph {
+  fcm_ctx* ctx = nullptr;
+  u32 n = 0, W = 0, maxout = 0;     // W = u64 words per adjacency row (even: 16-byte row stride)
+  u64 ne = 0;                       // number of distinct directed edges
+  u64* adj = nullptr;               // n * W
+  u64* csr_off = nullptr;           // n + 1
+  u32* csr = nullptr;               // ne, each out-list ascending
+  u32* order = nullptr;             // vertices by descending out-degree
+  u64* counts = nullptr;            // FCM_MAXD
+  u32* ctrl = nullptr;              // [0] ticket, [1] overflow count, [2] error flag, [3] ticket2
+  u32* overflow = nullptr;          // n
+  u64* scratch = nullptr;           // dense-row kernel P stacks
+  size_t scratch_words = 0;
+  int kernel_kind = 0;
+};
+
+// device control words
+enum { CT_TICKET = 0, CT_NOVER = 1, CT_ERR = 2, CT_TICKET2 = 3, CT_WORDS = 8 };
+
+// fcm_count.cu
+int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts);
+int fcm_graph_build_device(fcm_graph* g, const uint2* edges_dev, u64 ne_in, int normalise,
+                           std::vector<u64>& off_host);
+
+// ---- ensemble of chains ----------------------------------------------------------------------------
+#define FCM_MAXB (FCM_MAXD + 1)     // bounds vectors may be one longer (src/lib.rs:152 push(10))
+#define FCM_MAXEDIT 64
+
+struct ChainState {                 // one per chain, in HBM
+  u64 rng[4];
+  u64 sampled, accepted, sumK, nonempty;
+  u64 flag_count[FCM_MAXD];
+  u32 E, ND;
+  int fc_len;
+  int err;
+};
+
+struct EnsParams {
+  u32 n, W, nchains;
+  u64 npairs;
+  u32 maxc, Kcap, KWcap;
+  // static, shared by all chains
+  const uint2* pair_ab;             // pair id -> (big, small)
+  const u64* nb_off;                // npairs + 1
+  const u32* nb_list;               // common undirected neighbours, ascending
+  // per chain (chain-major)
+  u64* adj;                         // nchains * n * W
+  u32* items;                       // nchains * 2*npairs  (directed-edge slots in container order)
+  u32* pos;                         // nchains * 2*npairs  (slot -> index in items | NONE)
+  u32* dbl;                         // nchains * npairs    (pair ids in container order)
+  u32* dblpos;                      // nchains * npairs
+  ChainState* st;                   // nchains
+  // settings
+  u64 bmin[FCM_MAXB], bmax[FCM_MAXB];
+  int nmin, nmax;
+  double cum[3], scale;             // WeightedIndex<f64>
+};
+
+struct fcm_ensemble {
+  fcm_ctx* ctx = nullptr;
+  EnsParams p;
+  u64 ne0 = 0, nd0 = 0;
+  std::unordered_map<u64, u32> pairmap;   // (big<<32|small) -> pair id   (host side, for fcm_apply)
+  std::vector<uint2> pair_ab_host;
+  std::vector<void*> dev_allocs;
+  u64 bytes_per_chain = 0;
+  size_t smem_per_warp = 0;
+  int warps_per_block = 4;
+  fcm_trace_rec* trace_dev = nullptr;
+  u64 trace_cap = 0;
+  u32* edit_dev = nullptr;                // FCM_MAXEDIT * 2 (slot, add)
+  u64* io_dev = nullptr;                  // pre/post exchange: 2*FCM_MAXD + 4
+};
+
+// fcm_chain.cu
+size_t fcm_chain_smem_per_warp(u32 Kcap, u32 KWcap);
+int fcm_chain_launch_step(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain);
+int fcm_chain_launch_apply(fcm_ensemble* e, u32 chain, int nedits, int revert);
+int fcm_chain_launch_replicate(fcm_ensemble* e);

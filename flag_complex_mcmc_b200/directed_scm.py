@@ -1,0 +1,404 @@
+"""Host-side mirror of the reference crate's interface for the hot path (crate `directed-scm`,
+src/lib.rs) over libfcm.so.  Names, argument meaning and error behaviour follow the reference:
+
+  read_flag_file                      src/io.rs:18-35
+  flagser_count / count_cells         external flag-complex crate; call sites src/lib.rs:51,130
+  Bounds.calculate / Bounds.check     src/lib.rs:119-160
+  util: all_le, factorial (the (x-1)! quirk), binomial, calc_relax_de, OEIS_A058298   src/util.rs:53-105
+  initialize_new_sampler              src/bin/sample.rs:80-105
+  MCMCSampler.next / acceptance_ratio src/lib.rs:181-197   (here: an ensemble of chains, one per seed)
+  State.apply_transition / revert_transition   src/lib.rs:61-95
+
+All counting and all chain steps run in CUDA (libfcm.so); nothing here falls back to the CPU.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _native as N
+from ._native import FCM_MAXD, FcmError, check, edges_array, lib, ptr
+
+U64 = (1 << 64) - 1
+USIZE_MAX = U64
+
+MOVE_DISTRIBUTION = [0.1, 0.1, 0.6, 0.2]          # src/bin/sample.rs:16
+MOVE_DISTRIBUTION_SIMPLE = [0.5, 0.5, 0.0, 0.0]   # src/bin/sample.rs:17
+
+OEIS_A058298 = [2, 3, 6, 8, 12, 24, 30, 40, 60, 120, 144, 180, 240, 360, 720,
+                840, 1008, 1260, 1680, 2520, 5040, 5760, 6720, 8064, 10080,
+                13440, 20160, 40320, 45360, 51840, 60480, 72576, 90720,
+                120960, 181440, 362880, 403200, 453600, 518400, 604800,
+                725760, 907200, 1209600, 1814400, 3628800, 3991680, 4435200, 4989600,
+                5702400, 6652800, 7983360, 9979200, 13305600, 19958400, 39916800,
+                43545600, 47900160, 53222400, 59875200, 68428800,
+                79833600, 95800320, 119750400, 159667200]     # src/util.rs:98-105
+
+
+# ---- util.rs -------------------------------------------------------------------------------------
+def all_le(a, b, z=0):
+    """src/util.rs:53-63: element-wise a <= b with the shorter side padded by z."""
+    m = max(len(a), len(b))
+    for i in range(m):
+        l = a[i] if i < len(a) else z
+        r = b[i] if i < len(b) else z
+        if l > r:
+            return False
+    return True
+
+
+def factorial(x):
+    """src/util.rs:65-71: `for i in 1..x` => (x-1)!  — the quirk is part of the bounds; usize wraps."""
+    res = 1
+    for i in range(1, x):
+        res = (res * i) & U64
+    return res
+
+
+def binomial(n, k):
+    """src/util.rs:73-77 on the quirky factorial, integer division (panics on n < k / zero divisor)."""
+    if k > n:
+        raise OverflowError("binomial: n - k underflows (reference panics)")
+    den = (factorial(k) * factorial(n - k)) & U64
+    if den == 0:
+        raise ZeroDivisionError("binomial: divisor wrapped to zero (reference panics)")
+    return factorial(n) // den
+
+
+def calc_relax_de(sc):
+    """src/util.rs:79-93."""
+    out = []
+    for d in range(len(sc)):
+        ind = 1
+        lost = []
+        while True:
+            if ind >= len(OEIS_A058298):
+                raise IndexError("calc_relax_de: OEIS_A058298 index out of range (reference panics)")
+            if not (OEIS_A058298[ind] < sc[d]):
+                break
+            lost.append(OEIS_A058298[ind] - OEIS_A058298[ind - 1])
+            ind += 1
+        a = max(lost) if lost else 1
+        out.append(min(a, factorial(d + 1)))
+    return out
+
+
+# ---- io.rs ---------------------------------------------------------------------------------------
+def read_flag_file(fname):
+    """src/io.rs:18-35 -> (n, edges uint32 (E,2) in file order)."""
+    with open(fname) as f:
+        lines = f.read().splitlines()
+    n = len([t for t in lines[1].split(" ") if t != ""])
+    edges = []
+    for ln in lines[3:]:
+        t = [x for x in ln.split(" ") if x != ""]
+        if len(t) >= 2:
+            edges.append((int(t[0]), int(t[1])))
+    return n, np.array(edges, dtype=np.uint32).reshape(-1, 2)
+
+
+# ---- device plumbing -------------------------------------------------------------------------------
+class Context:
+    """One CUDA device + stream (fcm_ctx)."""
+
+    def __init__(self, device=0, stream=None):
+        self.h = C.c_void_p()
+        check(lib().fcm_ctx_create(int(device), C.byref(self.h)))
+        self.device = int(device)
+        if stream is not None:
+            self.set_stream(stream)
+
+    def set_stream(self, stream):
+        check(lib().fcm_ctx_set_stream(self.h, C.c_void_p(int(stream) if stream else 0)))
+
+    def synchronize(self):
+        check(lib().fcm_ctx_synchronize(self.h))
+
+    def timer_begin(self):
+        check(lib().fcm_ctx_timer_begin(self.h))
+
+    def timer_end(self):
+        ms = C.c_float()
+        check(lib().fcm_ctx_timer_end(self.h, C.byref(ms)))
+        return ms.value
+
+    @property
+    def launches(self):
+        return int(lib().fcm_ctx_launches(self.h))
+
+    def close(self):
+        if self.h:
+            lib().fcm_ctx_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DeviceGraph:
+    """Adjacency resident in HBM as packed 64-bit rows (fcm_graph)."""
+
+    def __init__(self, ctx, n, edges, normalised=False):
+        self.ctx = ctx
+        e = edges_array(edges)
+        self.h = C.c_void_p()
+        f = lib().fcm_graph_create_normalised if normalised else lib().fcm_graph_create
+        check(f(ctx.h, int(n), int(e.shape[0]), ptr(e), C.byref(self.h)))
+        n_, ne, w, mo = C.c_uint32(), C.c_uint64(), C.c_uint32(), C.c_uint32()
+        check(lib().fcm_graph_info(self.h, C.byref(n_), C.byref(ne), C.byref(w), C.byref(mo)))
+        self.n, self.nedges, self.words_per_row, self.max_out_degree = n_.value, ne.value, w.value, mo.value
+
+    def set_kernel(self, kind):
+        check(lib().fcm_graph_set_kernel(self.h, int(kind)))
+
+    def count_shard(self, part=0, nparts=1):
+        """uint64[FCM_MAXD] of the simplices whose source vertex lies in the shard (zero padded)."""
+        out = np.zeros(FCM_MAXD, dtype=np.uint64)
+        ln = C.c_int()
+        check(lib().fcm_graph_count(self.h, int(part), int(nparts), ptr(out), C.byref(ln)))
+        return out
+
+    def count_async(self, part=0, nparts=1):
+        """Enqueue the count; returns the device address of the uint64[FCM_MAXD] result."""
+        p = C.c_void_p()
+        check(lib().fcm_graph_count_async(self.h, int(part), int(nparts), C.byref(p)))
+        return p.value
+
+    def flagser_count(self):
+        """`graph.flagser_count()`: list without trailing zeros."""
+        return trim(self.count_shard(0, 1))
+
+    def close(self):
+        if self.h:
+            lib().fcm_graph_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def trim(v):
+    v = [int(x) for x in v]
+    while v and v[-1] == 0:
+        v.pop()
+    return v
+
+
+def flagser_count(n, edges, ctx=None):
+    """Stateless count.  Without a context this is fcm_count_unweighted, the drop-in for the
+    reference's `flagser_count_unweighted` C ABI (src/flagser.rs:7-21)."""
+    e = edges_array(edges)
+    if ctx is not None:
+        g = DeviceGraph(ctx, n, e)
+        try:
+            return g.flagser_count()
+        finally:
+            g.close()
+    sz = C.c_size_t()
+    res = lib().fcm_count_unweighted(int(n), int(e.shape[0]), ptr(e), C.byref(sz))
+    if not res:
+        raise FcmError(-1, lib().fcm_last_error().decode())
+    try:
+        arr = (C.c_size_t * sz.value).from_address(res)
+        return [int(x) for x in arr]
+    finally:
+        lib().fcm_free(res)
+
+
+count_cells = flagser_count      # flag_complex::count_cells (src/bin/all_cxs.rs:123)
+
+
+def undirected_edges(edges):
+    """[a,b] with a > b once per adjacent pair (src/lib.rs:344 asserts a > b)."""
+    e = edges_array(edges)
+    big = np.maximum(e[:, 0], e[:, 1]).astype(np.uint64)
+    small = np.minimum(e[:, 0], e[:, 1]).astype(np.uint64)
+    key = np.unique((big << np.uint64(32)) | small)
+    return np.stack([(key >> np.uint64(32)).astype(np.uint32), (key & np.uint64(0xFFFFFFFF)).astype(np.uint32)], axis=1)
+
+
+# ---- Bounds ----------------------------------------------------------------------------------------
+class Bounds:
+    """src/lib.rs:113-161."""
+
+    def __init__(self, flag_count_min, flag_count_max):
+        self.flag_count_min = [int(x) for x in flag_count_min]
+        self.flag_count_max = [int(x) for x in flag_count_max]
+
+    @staticmethod
+    def target(flag_count, target_relaxation):
+        """src/bin/sample.rs:89-92: exact for d < 2, floor(s*(1-+t)) in f64 for d >= 2."""
+        mn = [s if d < 2 else int(math.floor(float(s) * (1.0 - target_relaxation))) for d, s in enumerate(flag_count)]
+        mx = [s if d < 2 else int(math.floor(float(s) * (1.0 + target_relaxation))) for d, s in enumerate(flag_count)]
+        return Bounds(mn, mx)
+
+    @staticmethod
+    def calculate(flag_count, ncliques, n_undirected_edges, target_bounds):
+        """src/lib.rs:119-156.  `ncliques` = flagser_count of the normalised graph (line 130)."""
+        if n_undirected_edges == flag_count[1]:                      # SEO case, :135-137
+            return Bounds(target_bounds.flag_count_min, ncliques)
+        mn = list(target_bounds.flag_count_min)
+        mx = list(target_bounds.flag_count_max)
+        relax_de = calc_relax_de(flag_count)
+        ln = len(flag_count)
+        for d in range(2, ln):
+            dense = binomial(ln - 2, d - 1)
+            relax = (relax_de[d] * dense) & U64
+            mx[d] = max((mn[d] + relax) & U64, mx[d])
+            if mx[d] < relax:
+                raise OverflowError("flag_count_max[d] - relax underflows (reference panics in debug)")
+            mn[d] = min(mx[d] - relax, mn[d])
+        mx[2] = USIZE_MAX                                            # :151
+        mx.append(10)                                                # :152
+        return Bounds(mn, mx)
+
+    def check_counts(self, flag_count):
+        """src/lib.rs:157-160 on a host copy of flag_count."""
+        return all_le(self.flag_count_min, flag_count) and all_le(flag_count, self.flag_count_max)
+
+
+# ---- the sampler: an ensemble of chains --------------------------------------------------------------
+class MCMCSampler:
+    """`MCMCSampler` (src/lib.rs:164-198) for `len(seeds)` independent chains on one GPU.
+
+    next() advances every chain by sample_distance proposals.  Per-chain results are read with
+    flag_count(k) / edges(k) / sampled / accepted."""
+
+    def __init__(self, ctx, n, edges, seeds, bounds, flag_count0, move_weights=MOVE_DISTRIBUTION_SIMPLE,
+                 sample_distance=0):
+        self.ctx = ctx
+        e = edges_array(edges)
+        self.n = int(n)
+        self.seeds = np.ascontiguousarray(np.asarray(seeds, dtype=np.uint64).reshape(-1))
+        self.nchains = int(self.seeds.size)
+        self.bounds = bounds
+        fc0 = np.asarray(flag_count0, dtype=np.uint64)
+        mn = np.asarray(bounds.flag_count_min, dtype=np.uint64)
+        mx = np.asarray(bounds.flag_count_max, dtype=np.uint64)
+        mw = np.asarray(move_weights, dtype=np.float64)
+        if mw.size != 4:
+            raise ValueError("move_weights must have 4 entries")
+        self.h = C.c_void_p()
+        check(lib().fcm_ensemble_create(ctx.h, self.n, int(e.shape[0]), ptr(e), self.nchains, ptr(self.seeds),
+                                        ptr(fc0), int(fc0.size), ptr(mn), int(mn.size), ptr(mx), int(mx.size),
+                                        ptr(mw), C.byref(self.h)))
+        if sample_distance == 0:                                     # src/bin/sample.rs:102
+            E = float(int(fc0[1])) if fc0.size > 1 else 0.0
+            sd = math.ceil(2.0 * E * math.log2(E)) if E > 0 else 0
+            sample_distance = int(sd)
+        self.sample_distance = int(sample_distance)
+
+    # -- stepping --
+    def step(self, nproposals):
+        """nproposals iterations of the loop body of next() on every chain (asynchronous)."""
+        check(lib().fcm_ensemble_step(self.h, int(nproposals)))
+
+    def next(self):
+        self.step(self.sample_distance)
+        return self
+
+    def step_trace(self, nproposals, chain=0):
+        rec = np.zeros(int(nproposals), dtype=N.TRACE_DTYPE)
+        check(lib().fcm_ensemble_step_trace(self.h, int(nproposals), int(chain), ptr(rec)))
+        return rec
+
+    def status(self):
+        check(lib().fcm_ensemble_status(self.h))
+
+    # -- reading --
+    def read(self, chain=0, want_edges=True):
+        fc = np.zeros(FCM_MAXD, dtype=np.uint64)
+        ln, s, a, ne, nd = C.c_int(), C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_uint64()
+        rng = np.zeros(4, dtype=np.uint64)
+        info = self.info()
+        ebuf = np.zeros((2 * info["npairs"], 2), dtype=np.uint32) if want_edges else None
+        check(lib().fcm_ensemble_read(self.h, int(chain), ptr(fc), C.byref(ln), C.byref(s), C.byref(a),
+                                      ptr(ebuf) if want_edges else None, C.byref(ne), C.byref(nd), ptr(rng)))
+        return {"flag_count": [int(x) for x in fc[:ln.value]], "sampled": s.value, "accepted": a.value,
+                "nedges": ne.value, "ndouble": nd.value, "rng": [int(x) for x in rng],
+                "edges": ebuf[:ne.value].copy() if want_edges else None}
+
+    def read_all(self):
+        fcs = np.zeros((self.nchains, FCM_MAXD), dtype=np.uint64)
+        lens = np.zeros(self.nchains, dtype=np.int32)
+        s = np.zeros(self.nchains, dtype=np.uint64)
+        a = np.zeros(self.nchains, dtype=np.uint64)
+        st = np.zeros(2, dtype=np.uint64)
+        check(lib().fcm_ensemble_read_all(self.h, ptr(fcs), ptr(lens), ptr(s), ptr(a), ptr(st)))
+        return {"flag_counts": fcs, "lens": lens, "sampled": s, "accepted": a, "sumK": int(st[0]),
+                "nonempty": int(st[1])}
+
+    def acceptance_ratio(self, chain=0):
+        r = self.read(chain, want_edges=False)
+        return r["accepted"] / r["sampled"] if r["sampled"] else float("nan")
+
+    def info(self):
+        n, npairs, nch, maxc, bpc = C.c_uint32(), C.c_uint64(), C.c_uint32(), C.c_uint32(), C.c_uint64()
+        check(lib().fcm_ensemble_info(self.h, C.byref(n), C.byref(npairs), C.byref(nch), C.byref(maxc), C.byref(bpc)))
+        return {"n": n.value, "npairs": npairs.value, "nchains": nch.value, "max_common_nbhd": maxc.value,
+                "bytes_per_chain": bpc.value}
+
+    def set_bounds(self, bounds):
+        mn = np.asarray(bounds.flag_count_min, dtype=np.uint64)
+        mx = np.asarray(bounds.flag_count_max, dtype=np.uint64)
+        check(lib().fcm_ensemble_set_bounds(self.h, ptr(mn), int(mn.size), ptr(mx), int(mx.size)))
+        self.bounds = bounds
+
+    # -- State::apply_transition / revert_transition (src/lib.rs:61-95) --
+    def apply_transition(self, change_edges, chain=0):
+        """change_edges = [((a, b), add), ...] -> (pre, post) lists."""
+        ed = np.array([[a, b, 1 if add else 0] for (a, b), add in change_edges], dtype=np.uint32).reshape(-1, 3)
+        pre = np.zeros(FCM_MAXD, dtype=np.uint64)
+        post = np.zeros(FCM_MAXD, dtype=np.uint64)
+        pl, ql = C.c_int(), C.c_int()
+        check(lib().fcm_apply(self.h, int(chain), ptr(ed), int(ed.shape[0]), ptr(pre), C.byref(pl), ptr(post), C.byref(ql)))
+        return [int(x) for x in pre[:pl.value]], [int(x) for x in post[:ql.value]]
+
+    def revert_transition(self, change_edges, counters, chain=0):
+        pre, post = counters
+        ed = np.array([[a, b, 1 if add else 0] for (a, b), add in change_edges], dtype=np.uint32).reshape(-1, 3)
+        p = np.asarray(pre, dtype=np.uint64)
+        q = np.asarray(post, dtype=np.uint64)
+        check(lib().fcm_revert(self.h, int(chain), ptr(ed), int(ed.shape[0]), ptr(p), int(p.size), ptr(q), int(q.size)))
+
+    def bounds_check(self, chain=0):
+        ok = C.c_int()
+        check(lib().fcm_bounds_check(self.h, int(chain), C.byref(ok)))
+        return bool(ok.value)
+
+    def close(self):
+        if self.h:
+            lib().fcm_ensemble_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def initialize_new_sampler(ctx, n, edges, seeds, target_relaxation=0.01, simple=True, sample_distance=0):
+    """src/bin/sample.rs:80-105 for one or many seeds: State::new's full count, target bounds,
+    Bounds::calculate (second full count on the normalised graph), move mix, sample distance."""
+    e = edges_array(edges)
+    g = DeviceGraph(ctx, n, e)
+    flag_count = g.flagser_count()                                   # State::new, src/lib.rs:51
+    g.close()
+    gn = DeviceGraph(ctx, n, e, normalised=True)
+    ncliques = gn.flagser_count()                                    # src/lib.rs:125-130
+    n_und = gn.nedges
+    gn.close()
+    target = Bounds.target(flag_count, target_relaxation)
+    bounds = Bounds.calculate(flag_count, ncliques, n_und, target)
+    mw = MOVE_DISTRIBUTION_SIMPLE if simple else MOVE_DISTRIBUTION
+    s = MCMCSampler(ctx, n, e, seeds, bounds, flag_count, mw, sample_distance)
+    s.initial_flag_count = flag_count
+    s.ncliques = ncliques
+    return s

@@ -1,0 +1,172 @@
+/* fcm.h — C ABI of libfcm.so: the B200-native replacement of flag-complex-mcmc's data-parallel
+ * hot path (directed-flag-complex simplex counting + per-move local delta + bounds test).
+ *
+ * Every entry point replaces one reference interface; the reference file:line is cited beside it
+ * (paths relative to the reference repository, TheJonny/flag-complex-mcmc).  The Rust side binds
+ * these with a ~60-line `extern "C"` block (INTEGRATION.md shows it); nothing here mentions torch.
+ *
+ * Conventions
+ *   - plain pointers + sizes; Node = uint32_t, Edge = uint32_t[2] = (from, to)   src/flagser.rs:9
+ *   - counts are uint64_t (Rust usize on 64-bit)                                src/lib.rs:34
+ *   - every function returns 0 on success, a negative FCM_E* code otherwise; fcm_last_error()
+ *     gives the message (thread-local).  The reference panics/aborts in the same situations
+ *     (src/lib.rs:65,86,104,309); a Rust shim turns non-zero into panic!().
+ *   - no CPU fallback: every compute entry point fails with FCM_ENODEVICE when no CUDA device
+ *     is usable.
+ *   - a handle (ctx / graph / ensemble) is owned by one host thread at a time (the reference's
+ *     `&mut self`, src/lib.rs:61,81,181); different handles may be used from different threads.
+ */
+#ifndef FCM_H
+#define FCM_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FCM_MAXD 32            /* longest flag_count vector handled (dimension <= 31) */
+#define FCM_ABI_VERSION 1
+
+enum {
+  FCM_OK = 0,
+  FCM_EINVAL = -1,             /* bad argument (null pointer, vertex id >= n, self loop ...) */
+  FCM_ENODEVICE = -2,          /* no usable CUDA device / driver */
+  FCM_ECUDA = -3,              /* a CUDA call failed; message holds cudaGetErrorString */
+  FCM_ENOMEM = -4,
+  FCM_EDIM = -5,               /* a simplex of dimension >= FCM_MAXD was met */
+  FCM_ENOTADJ = -6,            /* an edit names a pair that is not adjacent in the underlying
+                                  undirected graph (reference: HashMap index panic, src/lib.rs:104) */
+  FCM_EASSERT = -7,            /* reference assert!(s >= p) would fail (src/lib.rs:65,86) */
+  FCM_EUNSUPPORTED = -8,       /* e.g. clique moves (move_weights[2..3] != 0): SURVEY §8f next row */
+  FCM_ELIMIT = -9              /* neighbourhood larger than the kernel's local-matrix capacity */
+};
+
+typedef struct fcm_ctx fcm_ctx;
+typedef struct fcm_graph fcm_graph;
+typedef struct fcm_ensemble fcm_ensemble;
+
+const char* fcm_last_error(void);
+int fcm_abi_version(void);
+/* number of CUDA devices visible (0 when none; never fails) */
+int fcm_device_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * 1. Stateless count — signature and ownership of the reference's C ABI precedent
+ *    `flagser_count_unweighted` (src/flagser.rs:7-21): callee mallocs the result, caller copies
+ *    and free()s it (fcm_free == free).  Returns NULL on error.  Uses device 0.
+ *    Replaces `graph.flagser_count()`  (src/lib.rs:51,130) / `flag_complex::count_cells`
+ *    (src/bin/all_cxs.rs:123).  Result has no trailing zeros; result[0] = nvertices.
+ * ---------------------------------------------------------------------------------------------- */
+size_t* fcm_count_unweighted(size_t nvertices, size_t nedges, const uint32_t (*edges)[2],
+                             size_t* res_size);
+void fcm_free(void* p);
+
+/* ------------------------------------------------------------------------------------------------
+ * 2. Context = one CUDA device + one stream.  device = ordinal (>= 0).
+ *    fcm_ctx_set_stream lets the host run the kernels on its own stream (cudaStream_t passed as
+ *    void*; NULL restores the context's private stream).
+ * ---------------------------------------------------------------------------------------------- */
+int fcm_ctx_create(int device, fcm_ctx** out);
+int fcm_ctx_destroy(fcm_ctx* ctx);
+int fcm_ctx_set_stream(fcm_ctx* ctx, void* cuda_stream);
+int fcm_ctx_synchronize(fcm_ctx* ctx);
+/* device-side timer on the context's stream (CUDA events): begin ... end -> milliseconds */
+int fcm_ctx_timer_begin(fcm_ctx* ctx);
+int fcm_ctx_timer_end(fcm_ctx* ctx, float* ms_out);
+/* number of kernels this library has launched on this context since creation */
+uint64_t fcm_ctx_launches(const fcm_ctx* ctx);
+
+/* ------------------------------------------------------------------------------------------------
+ * 3. Device-resident graph for (sharded) full recounts: State::new's `graph.flagser_count()`
+ *    (src/lib.rs:51) and Bounds::calculate's count of the normalised graph (src/lib.rs:125-130).
+ *    Adjacency is kept in HBM as packed 64-bit out-neighbour rows (row stride padded to 16 B).
+ * ---------------------------------------------------------------------------------------------- */
+int fcm_graph_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, const uint32_t (*edges)[2],
+                     fcm_graph** out);
+/* graph of the normalised orientation (one edge big->small per adjacent pair, src/lib.rs:126-129) */
+int fcm_graph_create_normalised(fcm_ctx* ctx, uint32_t n, uint64_t nedges,
+                                const uint32_t (*edges)[2], fcm_graph** out);
+int fcm_graph_destroy(fcm_graph* g);
+/* Count the simplices whose source (first) vertex v0 is in shard `part` of `nparts`
+ * (degree-balanced round-robin over source vertices; part 0 of 1 = whole graph).
+ * counts[FCM_MAXD] is filled (zero padded); *len = top non-empty dimension + 1 OF THIS SHARD.
+ * Summing the shards' vectors (NCCL allreduce, 16 x u64) gives flagser_count.  Synchronous. */
+int fcm_graph_count(fcm_graph* g, uint32_t part, uint32_t nparts, uint64_t* counts, int* len);
+/* Same, asynchronous on the context stream: result stays in a device buffer of FCM_MAXD u64
+ * (pointer returned through counts_dev) so that a collective can consume it without a host hop. */
+int fcm_graph_count_async(fcm_graph* g, uint32_t part, uint32_t nparts, uint64_t** counts_dev);
+/* which kernel to use: 0 = auto (block-local relabelled kernel, dense-row kernel for sources whose
+ * out-degree exceeds the shared-memory tile), 1 = force dense-row kernel (the roofline model's
+ * "one adjacency row per simplex" kernel).  Results are identical. */
+int fcm_graph_set_kernel(fcm_graph* g, int kind);
+/* bytes of adjacency rows resident in HBM, words per row */
+int fcm_graph_info(const fcm_graph* g, uint32_t* n, uint64_t* nedges, uint32_t* words_per_row,
+                   uint32_t* max_out_degree);
+
+/* ------------------------------------------------------------------------------------------------
+ * 4. Ensemble of independent chains on one device: MCMCSampler (src/lib.rs:164-198), one warp per
+ *    chain.  All chains start from the same graph (edge order = insertion order of the edge list,
+ *    as read_flag_file inserts them, src/io.rs:26-33) and share bounds / move mix; chain k uses
+ *    Xoshiro256StarStar::seed_from_u64(seeds[k]) (src/bin/sample.rs:86).
+ *    flag_count0/len0 = the initial flagser_count of the graph (State::new, src/lib.rs:51).
+ *    move_weights[4] = MOVE_DISTRIBUTION (src/bin/sample.rs:16-17): flip, double-edge move,
+ *    clique permute, clique swap; the last two must be 0 (FCM_EUNSUPPORTED otherwise).
+ * ---------------------------------------------------------------------------------------------- */
+int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, const uint32_t (*edges)[2],
+                        uint32_t nchains, const uint64_t* seeds,
+                        const uint64_t* flag_count0, int len0,
+                        const uint64_t* bounds_min, int nmin, const uint64_t* bounds_max, int nmax,
+                        const double move_weights[4], fcm_ensemble** out);
+int fcm_ensemble_destroy(fcm_ensemble* e);
+int fcm_ensemble_set_bounds(fcm_ensemble* e, const uint64_t* bounds_min, int nmin,
+                            const uint64_t* bounds_max, int nmax);
+
+/* one record per proposal (optional trace; identical layout in oracle/fcm_oracle.cpp) */
+typedef struct fcm_trace_rec {
+  uint32_t flags;              /* bits 0-1 move kind, bit 4 accepted, bit 5 empty transition */
+  uint32_t a, b;               /* flip: sampled edge (from,to); double move: the single edge [a,b] */
+  uint32_t dm0, dm1;           /* double move: the deleted direction `delme` */
+  uint32_t K;                  /* |neighbourhood| (0 for an empty transition) */
+  uint32_t draws, pad;
+} fcm_trace_rec;
+#define FCM_TR_KIND_MASK 3u
+#define FCM_TR_ACCEPT (1u << 4)
+#define FCM_TR_EMPTY (1u << 5)
+
+/* `nproposals` iterations of the loop body of MCMCSampler::next (src/lib.rs:182-192) on every
+ * chain (next() itself = nproposals = sample_distance).  Asynchronous on the context stream. */
+int fcm_ensemble_step(fcm_ensemble* e, uint64_t nproposals);
+/* same, synchronous, writing chain `chain`'s per-proposal trace to trace_out[nproposals] (host) */
+int fcm_ensemble_step_trace(fcm_ensemble* e, uint64_t nproposals, uint32_t chain,
+                            fcm_trace_rec* trace_out);
+/* Synchronise and read one chain.  Any output pointer may be NULL.  flag_count_out[FCM_MAXD];
+ * edges_out[2*nedges] in container order (State.graph.edges()); rng_out[4] = xoshiro state. */
+int fcm_ensemble_read(fcm_ensemble* e, uint32_t chain, uint64_t* flag_count_out, int* len_out,
+                      uint64_t* sampled_out, uint64_t* accepted_out, uint32_t* edges_out,
+                      uint64_t* nedges_out, uint64_t* ndouble_out, uint64_t* rng_out);
+/* Synchronise and read all chains at once: flag_counts[nchains*FCM_MAXD], lens[nchains],
+ * sampled[nchains], accepted[nchains]; any may be NULL.  stats[2] (may be NULL): [0] = total
+ * neighbourhood size K over all non-empty proposals of all chains since creation, [1] = number of
+ * non-empty proposals (both feed the algorithmic-bytes model of DESIGN.md). */
+int fcm_ensemble_read_all(fcm_ensemble* e, uint64_t* flag_counts, int* lens, uint64_t* sampled,
+                          uint64_t* accepted, uint64_t* stats);
+/* sticky device-side error of the ensemble (FCM_OK, FCM_EDIM, FCM_EASSERT, FCM_ELIMIT) */
+int fcm_ensemble_status(fcm_ensemble* e);
+int fcm_ensemble_info(const fcm_ensemble* e, uint32_t* n, uint64_t* npairs, uint32_t* nchains,
+                      uint32_t* max_common_nbhd, uint64_t* bytes_per_chain);
+
+/* State::apply_transition / revert_transition (src/lib.rs:61-95) on one chain with explicit
+ * edits (a, b, add) x nedits; pre/post[FCM_MAXD] are the API-visible local counts (src/bin/
+ * seo_bt_flip_only_once.rs:51-74 reads post[2]-pre[2]).  Synchronous. */
+int fcm_apply(fcm_ensemble* e, uint32_t chain, const uint32_t* edits3, int nedits,
+              uint64_t* pre, int* prelen, uint64_t* post, int* postlen);
+int fcm_revert(fcm_ensemble* e, uint32_t chain, const uint32_t* edits3, int nedits,
+               const uint64_t* pre, int prelen, const uint64_t* post, int postlen);
+/* Bounds::check (src/lib.rs:157-160) of one chain's current state: *ok = 0/1 */
+int fcm_bounds_check(fcm_ensemble* e, uint32_t chain, int* ok);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FCM_H */

@@ -567,6 +567,19 @@ int orc_count(u32 n, u64 ne, const u32* edges, int nthreads, u64* out /*ORC_MAXD
   return 0;
 }
 
+// count restricted to the given source vertices (first vertex of the simplex): what one shard of a
+// sharded recount computes; the shards' vectors sum to orc_count's.
+int orc_count_sources(u32 n, u64 ne, const u32* edges, const u32* sources, u32 nsrc, u64* out /*ORC_MAXD*/) {
+  BitRows m(n);
+  for (u64 i = 0; i < ne; i++) if (edges[2 * i] != edges[2 * i + 1]) m.set(edges[2 * i], edges[2 * i + 1]);
+  std::vector<u64> c(1, 0);
+  std::vector<std::vector<u64>> scratch;
+  for (u32 i = 0; i < nsrc; i++) { c[0]++; count_rec(m, m.row(sources[i]), 1, c, scratch); }
+  if ((int)c.size() > ORC_MAXD) return -1;
+  for (int i = 0; i < ORC_MAXD; i++) out[i] = i < (int)c.size() ? c[i] : 0;
+  return 0;
+}
+
 // --- rand known-answer hooks --------------------------------------------------------------
 void orc_rng_seed(u64 seed, u64* s4) { Xoshiro256SS r = Xoshiro256SS::seed_from_u64(seed); memcpy(s4, r.s, 32); }
 u64 orc_rng_next(u64* s4) { Xoshiro256SS r; memcpy(r.s, s4, 32); u64 v = r.next_u64(); memcpy(s4, r.s, 32); return v; }

@@ -1,0 +1,198 @@
+"""GPU: MCMC chains through the C ABI against the oracle: per-proposal traces (move kind, sampled
+edge, neighbourhood size, accept/reject), final flag_count, edge-container order, RNG state."""
+import numpy as np
+import pytest
+
+import oracle_binding as orc
+import flag_complex_mcmc_b200 as fcm
+from flag_complex_mcmc_b200 import directed_scm as ds
+from test_gpu_count import rand_graph
+
+pytestmark = pytest.mark.gpu
+
+FIELDS = ("flags", "a", "b", "dm0", "dm1", "K")
+
+
+def assert_trace_equal(got, want):
+    for f in FIELDS:
+        if not np.array_equal(got[f], want[f]):
+            i = int(np.nonzero(got[f] != want[f])[0][0])
+            raise AssertionError("trace field %s differs first at proposal %d: got %s want %s" % (f, i, got[i], want[i]))
+
+
+def compare_chain(s, chain, o):
+    r, w = s.read(chain), o.read()
+    assert r["flag_count"] == w["flag_count"]
+    assert (r["sampled"], r["accepted"]) == (w["sampled"], w["accepted"])
+    assert r["rng"] == w["rng"]
+    assert (r["nedges"], r["ndouble"]) == (w["nedges"], w["ndouble"])
+    assert np.array_equal(r["edges"], w["edges"])        # container order, not just the set
+
+
+@pytest.mark.parametrize("name,seed,steps", [("counterexample_seo_greedy_5_start", 0, 20000),
+                                             ("counterexample_any_order", 3, 3000),
+                                             ("bug_calc_relax_de", 1, 8000),
+                                             ("c2_chunglu_279", 0, 20000)])
+def test_trace_parity_single_chain(name, seed, steps, ctx, graphs):
+    n, e = graphs[name]
+    s = fcm.initialize_new_sampler(ctx, n, e, [seed], target_relaxation=0.01, simple=True)
+    o = orc.Sampler(n, e, seed, 0.01)
+    w = o.read()
+    assert s.bounds.flag_count_min == w["bounds_min"] and s.bounds.flag_count_max == w["bounds_max"]
+    assert s.sample_distance == w["sample_distance"]
+    for chunk in (1, 7, steps):
+        assert_trace_equal(s.step_trace(chunk, 0), o.steps(chunk))
+    compare_chain(s, 0, o)
+    acc = s.read(0)["accepted"]
+    assert 0 < acc <= steps + 8
+    # incremental flag_count == full recount of the chain's final graph (GPU count)
+    r = s.read(0)
+    assert ds.trim(r["flag_count"]) == fcm.flagser_count(n, r["edges"], ctx)
+    s.close()
+
+
+def test_many_chains_match_per_seed_oracle(ctx):
+    n = 120
+    e = rand_graph(n, 0.12, 21, pdouble=0.3)
+    seeds = list(range(40, 40 + 70))                      # 70 chains: partial last block
+    s = fcm.initialize_new_sampler(ctx, n, e, seeds, target_relaxation=0.05, simple=True)
+    s.step(1500)
+    s.step(500)
+    allr = s.read_all()
+    assert (allr["sampled"] == 2000).all()
+    for k in (0, 1, 31, 32, 69):
+        o = orc.Sampler(n, e, seeds[k], 0.05)
+        o.steps(2000, trace=False)
+        compare_chain(s, k, o)
+        assert [int(x) for x in allr["flag_counts"][k][:allr["lens"][k]]] == o.read()["flag_count"]
+    s.status()
+    s.close()
+
+
+def test_next_is_sample_distance_proposals(ctx, graphs):
+    n, e = graphs["counterexample_any_order"]
+    s = fcm.initialize_new_sampler(ctx, n, e, [5, 6], simple=True)
+    o = orc.Sampler(n, e, 6)
+    s.next()
+    o.next()
+    compare_chain(s, 1, o)
+    assert s.read(1)["sampled"] == s.sample_distance == o.info()["sample_distance"]
+    assert abs(s.acceptance_ratio(1) - o.info()["accepted"] / o.info()["sampled"]) < 1e-15
+    s.close()
+
+
+def hub_graph(H, S, ps, seed, pdouble=0.15):
+    """H mutually adjacent hubs, S satellites adjacent to every hub and sparsely to each other:
+    hub-hub pairs have ~S+H common neighbours but the neighbourhood holds few simplices."""
+    r = np.random.default_rng(seed)
+    n = H + S
+    edges = []
+    for a in range(n):
+        for b in range(a):
+            if not (a < H or b < H or r.random() < ps):
+                continue
+            u = r.random()
+            if u < pdouble:
+                edges += [(a, b), (b, a)]
+            elif u < 0.5 + pdouble / 2:
+                edges.append((a, b))
+            else:
+                edges.append((b, a))
+    e = np.array(edges, dtype=np.uint32)
+    return n, e[r.permutation(e.shape[0])]
+
+
+@pytest.mark.parametrize("H,S,kmin,steps", [(8, 75, 64, 1200), (8, 150, 128, 1200), (8, 290, 256, 1500)])
+def test_large_neighbourhoods_multiword_rows(H, S, kmin, steps, ctx):
+    # K > 64 (2-word local rows), > 128 (4-word) and > 256 (8-word)
+    n, e = hub_graph(H, S, 0.03, 100 + S)
+    s = fcm.initialize_new_sampler(ctx, n, e, [S], target_relaxation=0.5, simple=True)
+    o = orc.Sampler(n, e, S, 0.5, nthreads=8)
+    got, want = s.step_trace(steps, 0), o.steps(steps)
+    assert want["K"].max() > kmin
+    assert_trace_equal(got, want)
+    compare_chain(s, 0, o)
+    s.close()
+
+
+def test_apply_revert_api(ctx, graphs):
+    n, e = graphs["c2_chunglu_279"]
+    s = fcm.initialize_new_sampler(ctx, n, e, [0], simple=True)
+    o = orc.Sampler(n, e, 0)
+    es = set(map(tuple, e.tolist()))
+    singles = [(a, b) for (a, b) in e.tolist() if (b, a) not in es]
+    doubles = [(a, b) for (a, b) in e.tolist() if (b, a) in es and a < b]
+    fc0 = s.read(0)["flag_count"]
+    for (a, b) in singles[:40:4]:
+        ch = [((a, b), False), ((b, a), True)]             # a flip, src/lib.rs:295
+        pp, qq = s.apply_transition(ch), o.apply(ch)
+        assert pp == qq
+        assert s.read(0)["flag_count"] == o.read()["flag_count"]
+        assert s.bounds_check(0) == o.bounds_check()
+        s.revert_transition(ch, pp)
+        o.revert(ch, qq)
+        assert ds.trim(s.read(0)["flag_count"]) == ds.trim(fc0)
+        assert np.array_equal(s.read(0)["edges"], o.read()["edges"])
+    # a double-edge move written by hand (src/lib.rs:322): make a single edge double, delete one side of a double
+    (a, b), (x, y) = singles[1], doubles[0]
+    ch = [((b, a), True), ((x, y), False)]
+    assert s.apply_transition(ch) == o.apply(ch)
+    r, w = s.read(0), o.read()
+    assert r["flag_count"] == w["flag_count"] and np.array_equal(r["edges"], w["edges"]) and r["ndouble"] == w["ndouble"]
+    # empty transition
+    assert s.apply_transition([]) == ([], [])
+    # a pair that is not adjacent: the reference panics on the HashMap index (src/lib.rs:104)
+    non = next((a, b) for a in range(n) for b in range(a) if (a, b) not in es and (b, a) not in es)
+    with pytest.raises(fcm.FcmError) as ei:
+        s.apply_transition([(non, True)])
+    assert ei.value.code == fcm._native.FCM_ENOTADJ
+    # chains continue identically after the explicit edits
+    assert_trace_equal(s.step_trace(500, 0), o.steps(500))
+    s.close()
+
+
+def test_rejections_happen_and_revert_restores(ctx, graphs):
+    # tight hand-set bounds: most flips are rejected; state must stay consistent
+    n, e = graphs["c2_chunglu_279"]
+    s = fcm.initialize_new_sampler(ctx, n, e, [9], simple=True)
+    o = orc.Sampler(n, e, 9)
+    fc = s.initial_flag_count
+    mn = [fc[0], fc[1]] + [c - 1 for c in fc[2:]]
+    mx = [fc[0], fc[1]] + [c + 1 for c in fc[2:]]
+    s.set_bounds(ds.Bounds(mn, mx))
+    o.set_bounds(mn, mx)
+    got, want = s.step_trace(4000, 0), o.steps(4000)
+    assert_trace_equal(got, want)
+    rej = ((want["flags"] >> 4) & 1) == 0
+    assert rej.sum() > 500
+    compare_chain(s, 0, o)
+    r = s.read(0)
+    assert ds.trim(r["flag_count"]) == fcm.flagser_count(n, r["edges"], ctx)
+    s.close()
+
+
+def test_clique_moves_are_refused_loudly(ctx, graphs):
+    n, e = graphs["counterexample_any_order"]
+    with pytest.raises(fcm.FcmError) as ei:
+        fcm.initialize_new_sampler(ctx, n, e, [0], simple=False)
+    assert ei.value.code == fcm._native.FCM_EUNSUPPORTED
+
+
+def test_c3_full_size_chains(ctx, graphs, expected):
+    # BASELINE config C3: ER n=2000 p=0.05, many chains; parity on sampled chains + invariants on all
+    n, e = graphs["c3_er_2000"]
+    nch = 256
+    s = fcm.initialize_new_sampler(ctx, n, e, list(range(nch)), simple=True)
+    assert s.initial_flag_count == expected["c3_er_2000"]["flag_count"]
+    steps = 3000
+    s.step(steps)
+    allr = s.read_all()
+    assert (allr["sampled"] == steps).all()
+    assert (allr["flag_counts"][:, 0] == 2000).all() and (allr["flag_counts"][:, 1] == 199938).all()
+    for k in (0, 100, 255):
+        o = orc.Sampler(n, e, k, nthreads=8)
+        o.steps(steps, trace=False)
+        compare_chain(s, k, o)
+    r = s.read(17)
+    assert ds.trim(r["flag_count"]) == fcm.flagser_count(n, r["edges"], ctx)
+    s.close()

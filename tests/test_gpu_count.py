@@ -1,0 +1,141 @@
+"""GPU: simplex counting through the C ABI, bit-exact against the golden vectors and the oracle."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_binding as orc
+import flag_complex_mcmc_b200 as fcm
+from flag_complex_mcmc_b200 import _native as N
+from tools import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def rand_graph(n, p, seed, pdouble=0.0):
+    r = np.random.default_rng(seed)
+    m = r.random((n, n)) < p
+    if pdouble:
+        m |= (m.T & (r.random((n, n)) < pdouble))
+    np.fill_diagonal(m, False)
+    a, b = np.nonzero(m)
+    e = np.stack([a, b], 1).astype(np.uint32)
+    return e[r.permutation(e.shape[0])]
+
+
+def test_golden_counts_stateless_abi(expected, graphs):
+    for name, (n, e) in graphs.items():
+        assert fcm.flagser_count(n, e) == expected[name]["flag_count"], name
+
+
+@pytest.mark.parametrize("kind", [0, 1])
+def test_golden_counts_both_kernels(kind, ctx, expected, graphs):
+    for name, (n, e) in graphs.items():
+        g = fcm.DeviceGraph(ctx, n, e)
+        g.set_kernel(kind)
+        assert g.flagser_count() == expected[name]["flag_count"], (name, kind)
+        g.close()
+        gn = fcm.DeviceGraph(ctx, n, e, normalised=True)
+        gn.set_kernel(kind)
+        assert gn.flagser_count() == expected[name]["ncliques"], (name, kind)
+        assert gn.nedges == len(fcm.undirected_edges(e))
+        gn.close()
+
+
+@pytest.mark.parametrize("kind", [0, 1])
+def test_shards_sum_to_whole_and_match_oracle_shards(kind, ctx, graphs):
+    n, e = graphs["c3_er_2000"]
+    g = fcm.DeviceGraph(ctx, n, e)
+    g.set_kernel(kind)
+    whole = g.count_shard(0, 1)
+    for nparts in (2, 3, 8):
+        tot = np.zeros(N.FCM_MAXD, dtype=np.uint64)
+        for part in range(nparts):
+            tot += g.count_shard(part, nparts)
+        assert np.array_equal(tot, whole), nparts
+    # shard = degree-descending order taken round-robin; recompute the same shard with the oracle
+    deg = np.bincount(e[:, 0], minlength=n)
+    order = np.argsort(-deg, kind="stable")
+    assert np.array_equal(g.count_shard(1, 4), orc.count_sources(n, e, order[1::4]))
+    g.close()
+
+
+@pytest.mark.parametrize("n,p,pd,seed", [(1, 0, 0, 0), (2, 1.0, 1.0, 1), (33, 0.3, 0.2, 2), (64, 0.5, 0.5, 3),
+                                         (65, 0.2, 0.0, 4), (130, 0.25, 0.1, 5), (300, 0.1, 0.05, 6),
+                                         (700, 0.3, 0.0, 7), (1500, 0.02, 0.02, 8)])
+def test_random_graphs_vs_oracle(n, p, pd, seed, ctx):
+    e = rand_graph(n, p, seed, pd)
+    want = orc.count(n, e, nthreads=8)
+    for kind in (0, 1):
+        g = fcm.DeviceGraph(ctx, n, e)
+        g.set_kernel(kind)
+        assert g.flagser_count() == want, (n, kind)
+        g.close()
+
+
+def test_bidirected_cliques_closed_form(ctx):
+    # complete bidirected K_m: every ordered (d+1)-tuple is a simplex: m!/(m-d-1)!
+    for m in (4, 7, 9):
+        e = np.array([(a, b) for a in range(m) for b in range(m) if a != b], dtype=np.uint32)
+        want = [int(np.prod(np.arange(m - d, m + 1, dtype=np.float64))) for d in range(m)]
+        for kind in (0, 1):
+            g = fcm.DeviceGraph(ctx, m, e)
+            g.set_kernel(kind)
+            assert g.flagser_count() == want, (m, kind)
+            g.close()
+
+
+def test_out_degree_beyond_tile_goes_to_dense_kernel(ctx):
+    # hub with 1300 out-neighbours (> 1024-column tile) over a sparse random graph
+    n = 1400
+    e = rand_graph(n, 0.01, 11)
+    hub = np.stack([np.zeros(1300, dtype=np.uint32), np.arange(1, 1301, dtype=np.uint32)], 1)
+    e = np.concatenate([e[e[:, 0] != 0], hub])
+    want = orc.count(n, e, nthreads=8)
+    g = fcm.DeviceGraph(ctx, n, e)
+    assert g.max_out_degree == 1300
+    assert g.flagser_count() == want
+    g.close()
+
+
+def test_edge_cases(ctx):
+    assert fcm.flagser_count(5, np.zeros((0, 2), dtype=np.uint32)) == [5]
+    assert fcm.flagser_count(0, np.zeros((0, 2), dtype=np.uint32)) == []
+    # duplicate lines collapse (edge *set*), order irrelevant
+    e = np.array([[0, 1], [0, 1], [1, 2], [0, 2], [0, 2]], dtype=np.uint32)
+    assert fcm.flagser_count(3, e) == [3, 3, 1]
+    # vertex id out of range / self loop -> loud error, not a wrong count
+    with pytest.raises(fcm.FcmError):
+        fcm.flagser_count(3, np.array([[0, 3]], dtype=np.uint32))
+    with pytest.raises(fcm.FcmError):
+        fcm.DeviceGraph(ctx, 3, np.array([[1, 1]], dtype=np.uint32))
+    L = N.lib()
+    sz = C.c_size_t()
+    assert not L.fcm_count_unweighted(3, 1, None, C.byref(sz))
+
+
+def test_deep_dimensions_transitive_tournament(ctx):
+    # transitive tournament on m vertices: every subset is a simplex -> counts are binomials
+    import math
+    m = 22
+    e = np.array([(a, b) for a in range(m) for b in range(a + 1, m)], dtype=np.uint32)
+    want = [math.comb(m, d + 1) for d in range(m)]
+    for kind in (0, 1):
+        g = fcm.DeviceGraph(ctx, m, e)
+        g.set_kernel(kind)
+        assert g.flagser_count() == want, kind
+        g.close()
+
+
+def test_c4_full_size_known_answer(ctx, expected):
+    n, e = synth.config("c4_geo_31346")
+    assert e.shape[0] == expected["c4_geo_31346"]["nedges"]
+    g = fcm.DeviceGraph(ctx, n, e)
+    got = g.flagser_count()
+    assert got == expected["c4_geo_31346"]["flag_count"]
+    # size-independent property: shards sum to the whole
+    tot = np.zeros(N.FCM_MAXD, dtype=np.uint64)
+    for part in range(8):
+        tot += g.count_shard(part, 8)
+    assert fcm.directed_scm.trim(tot) == got
+    g.close()
