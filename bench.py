@@ -1,0 +1,394 @@
+#!/usr/bin/env python
+"""bench.py — the hot path of flag-complex-mcmc on B200, measured.
+
+Headline metric (BASELINE.json): MCMC proposals/sec.  One *step* = `--proposals` iterations of
+the loop body of MCMCSampler::next (src/lib.rs:182-192) on every chain of the ensemble, i.e. one
+launch of chain_step_kernel.  Workload at every N: the C3 graph (ER n=2000, p=0.05, seed 1,
+E=199 938) with 4096 independent chains per GPU, `--simple` move mix — N=8 is exactly BASELINE
+config C5 (8x4096 chains, chains sharded per GPU, no data-path collective => weak scaling).
+The second metric of BASELINE.json (full-recount simplices/sec, config C4, sharded by source
+vertex + allreduce of the uint64 counts) rides in the same JSON line under "recount".
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
+  python bench.py --impl reference ...                           # CPU restatement of the reference
+
+Under torchrun (N>1) one process per GPU; the timed region is bracketed by a barrier and a device
+synchronize on both sides, timed with CUDA events on the launching stream, MAX over ranks.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "mcmc_proposals_per_sec"
+UNIT = "proposals/s"
+N_C3, W_C3 = 2000, 32                      # vertices, 64-bit words per adjacency row (ceil(n/64))
+
+
+def env_int(k, d):
+    try:
+        return int(os.environ.get(k, d))
+    except ValueError:
+        return d
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def prop_model_bytes(sumK, nonempty, W):
+    """Algorithmic bytes of the proposals: per non-empty proposal the K
+    neighbourhood rows of 8*W bytes, the nbhd list 4*(K-2) and <= 2 word updates (16 B)."""
+    return 8 * W * sumK + 4 * (sumK - 2 * nonempty) + 16 * nonempty
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ------------------------------------------------------------------------------------------------
+class Clocks:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.f = None
+        self.p = None
+
+    def start(self):
+        try:
+            self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if not self.p:
+            return out
+        try:
+            self.p.terminate()
+            self.p.wait(timeout=5)
+        except Exception:
+            pass
+        try:
+            self.f.flush()
+            self.f.seek(0)
+            rows = [ln.strip().split(",") for ln in self.f.read().splitlines() if ln.strip()]
+            sm = sorted(float(r[0]) for r in rows if len(r) >= 6)
+            if sm:
+                out["sm_mhz"] = sm[len(sm) // 2]
+                out["sm_max_mhz"] = float(rows[0][1])
+                names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+                for i, nm in enumerate(names):
+                    if any(r[2 + i].strip().lower().startswith("active") for r in rows if len(r) >= 6):
+                        out["reasons"].append(nm)
+                out["samples"] = len(sm)
+            self.f.close()
+            os.unlink(self.f.name)
+        except Exception:
+            pass
+        return out
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs (the oracle = C++ restatement of the reference CPU path; checker/baseline only)
+# ------------------------------------------------------------------------------------------------
+class CpuChains:
+    """`cores` independent reference-shaped chains, one per host thread (the reference runs one
+    process per seed); run(budget_s) advances each by the same number of proposals."""
+
+    def __init__(self, n, e, cores, first_seed=0):
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_binding as orc
+        self.cores = cores
+        self.samplers = [orc.Sampler(n, e, first_seed + k, 0.01, nthreads=cores) for k in range(cores)]
+        t0 = time.perf_counter()
+        self.samplers[0].steps(2000, trace=False)
+        self.rate1 = 2000 / max(time.perf_counter() - t0, 1e-6)      # one chain alone, proposals/s
+
+    def run(self, budget_s):
+        """-> (proposals/s over all threads, proposals, seconds)"""
+        per = max(int(self.rate1 * budget_s), 1000)
+        ths = [threading.Thread(target=lambda s=s: s.steps(per, trace=False)) for s in self.samplers]
+        t0 = time.perf_counter()
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        dt = time.perf_counter() - t0
+        return self.cores * per / dt, self.cores * per, dt
+
+    def close(self):
+        for s in self.samplers:
+            s.close()
+
+
+def cpu_recount(n, e, cores, stride):
+    """Bounded sample of the full recount: every `stride`-th source vertex of the degree-descending
+    order, dynamic over all host threads -> (simplices/s, simplices, seconds)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding as orc
+    deg = np.bincount(e[:, 0], minlength=n)
+    order = np.argsort(-deg, kind="stable").astype(np.uint32)
+    src = order[::stride]
+    t0 = time.perf_counter()
+    c = orc.count_sources_mt(n, e, src, cores)
+    dt = time.perf_counter() - t0
+    return int(c.sum()) / dt, int(c.sum()), dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm for the path (oracle port; the Rust crate
+    cannot be built here: no rustc, un-vendored crates) on all host cores, same config/metric."""
+    rank = env_int("RANK", 0)
+    if rank != 0:
+        return 0
+    from tools import synth
+    cores = os.cpu_count() or 1
+    n, e = synth.config("c3_er_2000")
+    cc = CpuChains(n, e, cores)
+    for _ in range(args.warmup):
+        cc.run(0.5)
+    t_all = 0.0
+    nprop = 0
+    for _ in range(args.steps):
+        v, cnt, dt = cc.run(4.0)
+        t_all += dt
+        nprop += cnt
+    cc.close()
+    value = nprop / t_all
+    sample = "%d chains (one per host thread) x %d proposals per step on the C3 graph, --simple mix" % (cores, nprop // max(args.steps, 1) // cores)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_all / max(args.steps, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": workload_config(args, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(args, ngpu):
+    return {"workload": "C5 shard of BASELINE.json: C3 graph (ER n=2000 p=0.05 seed 1, E=199938), "
+                        "%d chains per GPU x %d GPU(s), seeds 0..%d, --simple move mix [0.5,0.5,0,0], t=0.01"
+                        % (args.chains, ngpu, args.chains * ngpu - 1),
+            "chains_per_gpu": args.chains, "proposals_per_chain_per_step": args.proposals,
+            "parallelism": "chains sharded per GPU, no data-path collective",
+            "l2": "per-GPU chain state (adjacency rows + edge containers) is ~%.1f GB >> 126 MB L2; "
+                  "every step touches fresh random rows" % (args.chains * 5.2e-3)}
+
+
+# ------------------------------------------------------------------------------------------------
+# the CUDA path
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--chains", type=int, default=4096, help="chains per GPU")
+    ap.add_argument("--proposals", type=int, default=2000, help="proposals per chain per step")
+    ap.add_argument("--no-recount", action="store_true", help="skip the C4 recount leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--recount-graph", default="c4_geo_31346")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import flag_complex_mcmc_b200 as fcm
+    from tools import synth
+
+    world = env_int("WORLD_SIZE", 1)
+    rank = env_int("RANK", 0)
+    local = env_int("LOCAL_RANK", 0)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ngpu = world
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    ctx = fcm.Context(local)
+    peak, peak_src = measured_peak()
+
+    # ---- chains --------------------------------------------------------------------------------
+    n, e = synth.config("c3_er_2000")
+    seeds = np.arange(rank * args.chains, (rank + 1) * args.chains, dtype=np.uint64)
+    s = fcm.initialize_new_sampler(ctx, n, e, seeds, target_relaxation=0.01, simple=True)
+    P = args.proposals
+    for _ in range(args.warmup):
+        s.step(P)
+    ctx.synchronize()
+    st0 = s.read_all()
+    l0 = ctx.launches
+    clk = Clocks(local)
+    barrier()
+    clk.start()
+    ctx.timer_begin()
+    for _ in range(args.steps):
+        s.step(P)
+    ms = ctx.timer_end()
+    barrier()
+    launches = ctx.launches - l0
+    st1 = s.read_all()
+    ms_max = max_over_ranks(ms)
+    total_props = float(args.chains) * P * args.steps * ngpu
+    value = total_props / (ms_max * 1e-3)
+    sumK = st1["sumK"] - st0["sumK"]
+    nonempty = st1["nonempty"] - st0["nonempty"]
+    model_bytes = prop_model_bytes(sumK, nonempty, W_C3)       # this rank, whole timed region
+    kern_ms = ms / max(args.steps, 1)                          # one chain_step_kernel launch per step
+    achieved = model_bytes / max(args.steps, 1) / (kern_ms * 1e-3) / 1e9
+    accepted = int((st1["accepted"] - st0["accepted"]).sum())
+
+    # ---- e2e: through the public API with host buffers: step + read_all (D2H) every step ----------
+    h2d = 2 * 33 * 8 + 8                                       # bounds vectors + nproposals (kernel parameters)
+    d2h = 0
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        s.set_bounds(s.bounds)
+        s.step(P)
+        r = s.read_all()                                       # synchronous D2H of every chain's state
+        d2h = r["flag_counts"].nbytes + r["lens"].nbytes + r["sampled"].nbytes + r["accepted"].nbytes + 16
+    torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    clocks = clk.stop()
+    e2e_ms = max_over_ranks(e2e_ms)
+    e2e_value = total_props / (e2e_ms * 1e-3)
+    info = s.info()
+    s.close()
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": ngpu, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_max / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64", "data": "synthetic", "config": workload_config(args, ngpu),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "what": "MCMCSampler.set_bounds + step(P) + read_all() per step (flag_count, sampled, accepted of every chain to host)"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": "chain_step_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "model": "8*W*K + 4*(K-2) + 16 bytes per non-empty proposal (SURVEY 8d), W=%d, mean K=%.2f, "
+                              "non-empty fraction %.3f" % (W_C3, sumK / max(nonempty, 1), nonempty / (float(args.chains) * P * args.steps)),
+                     "kernel_ms": kern_ms},
+        "acceptance_ratio": accepted / (float(args.chains) * P * args.steps),
+        "bytes_per_chain": info["bytes_per_chain"],
+    }
+
+    # ---- full recount (C4), sharded by source vertex + allreduce --------------------------------
+    if not args.no_recount:
+        n4, e4 = synth.config(args.recount_graph)
+        g = fcm.DeviceGraph(ctx, n4, e4)
+        W4 = (n4 + 63) // 64
+        for _ in range(max(args.warmup, 1)):
+            g.count_shard(rank, ngpu)
+        barrier()
+        l0 = ctx.launches
+        ctx.timer_begin()
+        for _ in range(args.steps):
+            g.count_async(rank, ngpu)
+        rms = ctx.timer_end()
+        rl = ctx.launches - l0
+        barrier()
+        part = g.count_shard(rank, ngpu)
+        tot = torch.from_numpy(part.astype(np.int64)).cuda()
+        if dist is not None:
+            dist.all_reduce(tot)                               # int64 per-dimension counts over NCCL/NVLink
+        counts = [int(x) for x in tot.cpu().numpy()]
+        while counts and counts[-1] == 0:
+            counts.pop()
+        simplices = sum(counts)
+        rms_max = max_over_ranks(rms)
+        rvalue = simplices * args.steps / (rms_max * 1e-3)
+        rbytes = 8 * W4 * simplices                            # dense-row model, whole graph
+        # e2e: the precedent C ABI fcm_count_unweighted with the host edge list (H2D + build + count + D2H)
+        t0 = time.perf_counter()
+        if rank == 0:
+            c2 = fcm.flagser_count(n4, e4)
+            assert c2 == counts, (c2, counts)
+        re2e = time.perf_counter() - t0
+        line["recount"] = {
+            "metric": "full_recount_simplices_per_sec", "value": rvalue, "unit": "simplices/s", "graph": args.recount_graph,
+            "n": n4, "nedges": int(e4.shape[0]), "flag_count": counts, "simplices": simplices, "ms_per_count": rms_max / max(args.steps, 1),
+            "gpu_launches": int(rl), "sharding": "source vertices, degree-descending round-robin over %d rank(s) + allreduce(sum) of uint64[32]" % ngpu,
+            "e2e": {"value": simplices / re2e if rank == 0 else None, "unit": "simplices/s", "h2d_bytes_per_step": int(e4.nbytes),
+                    "d2h_bytes_per_step": 8 * len(counts), "what": "fcm_count_unweighted(host edge list) on one GPU: upload, build bit rows + CSR, count, download"},
+            "roofline": {"bound": "hbm", "kernel": "count_local_kernel", "achieved": rbytes * args.steps / (rms_max * 1e-3) / 1e9 / ngpu,
+                         "peak": peak, "unit": "GB/s", "frac": rbytes * args.steps / (rms_max * 1e-3) / 1e9 / ngpu / peak,
+                         "traffic": None, "peak_source": peak_src,
+                         "model": "8*ceil(n/64) bytes per enumerated simplex (dense-row model, SURVEY 8d); the block-local kernel "
+                                  "gathers each source's k x k tile once, so it may exceed 1.0"},
+        }
+        g.close()
+
+    # ---- CPU baseline beside it (rank 0, N=1 only) ---------------------------------------------
+    if rank == 0 and ngpu == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        cc = CpuChains(n, e, cores)
+        cc.run(0.5)
+        v, cnt, dt = cc.run(12.0)
+        cc.close()
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": "%d chains (one per host thread) x %d proposals on the C3 graph, %.1f s; C++ restatement "
+                                          "of the reference CPU path (oracle/), the Rust crate cannot be built here" % (cores, cnt // cores, dt)}
+        if not args.no_recount:
+            rv, rs, rdt = cpu_recount(n4, e4, cores, 4)
+            line["recount"]["cpu_baseline"] = {"value": rv, "unit": "simplices/s", "cores": cores, "kind": "port",
+                                               "sample": "every 4th source vertex (degree-descending order) of %s: %d simplices "
+                                                         "in %.2f s incl. bit-matrix build" % (args.recount_graph, rs, rdt)}
+    ctx.close()
+    if rank == 0:
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -580,6 +580,36 @@ int orc_count_sources(u32 n, u64 ne, const u32* edges, const u32* sources, u32 n
   return 0;
 }
 
+// same, sources shared dynamically between nthreads host threads (bounded CPU-baseline sample of a
+// large recount: bench.py counts every 4th source of the degree-descending order)
+int orc_count_sources_mt(u32 n, u64 ne, const u32* edges, const u32* sources, u32 nsrc, int nthreads, u64* out /*ORC_MAXD*/) {
+  BitRows m(n);
+  for (u64 i = 0; i < ne; i++) if (edges[2 * i] != edges[2 * i + 1]) m.set(edges[2 * i], edges[2 * i + 1]);
+  if (nthreads < 1) nthreads = 1;
+  std::vector<std::vector<u64>> part(nthreads);
+  std::atomic<u32> next(0);
+  std::vector<std::thread> th;
+  for (int t = 0; t < nthreads; t++)
+    th.emplace_back([&, t]() {
+      std::vector<u64>& c = part[t];
+      c.assign(1, 0);
+      std::vector<std::vector<u64>> scratch;
+      for (;;) {
+        u32 i = next.fetch_add(1);
+        if (i >= nsrc) break;
+        c[0]++;
+        count_rec(m, m.row(sources[i]), 1, c, scratch);
+      }
+    });
+  for (auto& t : th) t.join();
+  for (int i = 0; i < ORC_MAXD; i++) out[i] = 0;
+  for (auto& c : part) {
+    if ((int)c.size() > ORC_MAXD) return -1;
+    for (size_t i = 0; i < c.size(); i++) out[i] += c[i];
+  }
+  return 0;
+}
+
 // --- rand known-answer hooks --------------------------------------------------------------
 void orc_rng_seed(u64 seed, u64* s4) { Xoshiro256SS r = Xoshiro256SS::seed_from_u64(seed); memcpy(s4, r.s, 32); }
 u64 orc_rng_next(u64* s4) { Xoshiro256SS r; memcpy(r.s, s4, 32); u64 v = r.next_u64(); memcpy(s4, r.s, 32); return v; }
@@ -597,14 +627,16 @@ u64 orc_factorial(u64 x) { return factorial(x); }
 u64 orc_binomial(u64 n, u64 k) { return binomial(n, k); }
 int orc_calc_relax_de(const u64* sc, int len, u64* out) {
   std::vector<u64> v(sc, sc + len), r; if (!calc_relax_de(v, r)) return -1;
-  for (int i = 0; i < len; i++) out[i] = r[i]; return 0;
+  for (int i = 0; i < len; i++) out[i] = r[i];
+  return 0;
 }
 int orc_all_le(const u64* a, int na, const u64* b, int nb) {
   return all_le(std::vector<u64>(a, a + na), std::vector<u64>(b, b + nb));
 }
 int orc_intersect_sorted(const u32* a, int na, const u32* b, int nb, u32* out) {
   auto r = intersect_sorted(std::vector<Node>(a, a + na), std::vector<Node>(b, b + nb));
-  for (size_t i = 0; i < r.size(); i++) out[i] = r[i]; return (int)r.size();
+  for (size_t i = 0; i < r.size(); i++) out[i] = r[i];
+  return (int)r.size();
 }
 
 // --- sampler ----------------------------------------------------------------------------------

@@ -32,6 +32,7 @@ def lib():
     L.orc_read_flag.argtypes = [C.c_char_p, vp]
     L.orc_count.argtypes = [u32, u64, vp, i32, vp, P(i32)]
     L.orc_count_sources.argtypes = [u32, u64, vp, vp, u32, vp]
+    L.orc_count_sources_mt.argtypes = [u32, u64, vp, vp, u32, i32, vp]
     L.orc_ncliques.argtypes = [u32, u64, vp, i32, vp, P(i32)]
     L.orc_rng_seed.argtypes = [u64, vp]
     L.orc_rng_seed.restype = None
@@ -91,6 +92,15 @@ def count_sources(n, edges, sources):
     s = np.ascontiguousarray(np.asarray(sources, dtype=np.uint32))
     out = np.zeros(ORC_MAXD, dtype=np.uint64)
     rc = lib().orc_count_sources(int(n), e.shape[0], _p(e), _p(s), int(s.size), _p(out))
+    assert rc == 0
+    return out
+
+
+def count_sources_mt(n, edges, sources, nthreads):
+    e = _e(edges)
+    s = np.ascontiguousarray(np.asarray(sources, dtype=np.uint32))
+    out = np.zeros(ORC_MAXD, dtype=np.uint64)
+    rc = lib().orc_count_sources_mt(int(n), e.shape[0], _p(e), _p(s), int(s.size), int(nthreads), _p(out))
     assert rc == 0
     return out
 
