@@ -8,15 +8,27 @@
 // policy documented in oracle/fcm_oracle.cpp (struct EdgeSet): insertion-ordered index set,
 // sample = element at gen_range(0..len), remove = swap_remove, add = append.
 //
-// Per proposal a warp
-//   1. draws the move (uniform across lanes: every lane runs the same xoshiro256** stream),
-//   2. builds the neighbourhood = common undirected neighbours of every changed pair + endpoints
-//      (static CSR, the undirected graph is invariant under all moves),
-//   3. gathers the K x K induced adjacency from the chain's packed 64-bit rows in HBM: lane j probes
-//      column verts[j] of row verts[i], one ballot per 32 columns,
-//   4. counts the local directed simplices before and after the edits (one DFS root per lane,
-//      popc on K-bit candidate sets held as KW 64-bit words),
-//   5. updates flag_count, tests the bounds, and commits or reverts the container/bit edits.
+// Two ways to obtain `flag_count += post - pre` (src/lib.rs:63-77), identical results:
+//
+//   DELTA path (the hot one).  post - pre only involves simplices that contain a changed edge; all
+//   other simplices of the neighbourhood graph cancel.  A simplex through the edge u->v is
+//   (x.., u, y.., v, z..) with every other vertex w a common neighbour of u and v, tagged by where it
+//   may stand: X (w->u, w->v), Y (u->w, w->v) or Z (u->w, v->w).  The warp
+//     1. reads the static common-neighbour list C of the pair (c <= 64 entries),
+//     2. gathers, from the chain's packed adjacency rows in HBM, the four relation masks of C
+//        against u and v and the c x c adjacency among C (lane j probes column C[j] of row C[i],
+//        one ballot per row; 32 lanes read one 256-byte row => coalesced),
+//     3. counts the ordered cliques of the tagged graph by dimension: one DFS root per lane,
+//        candidate sets = three 64-bit masks (X,Y,Z), extension = AND with a shared-memory row +
+//        popc; the first levels live in registers (template recursion), deeper ones in a generic
+//        loop.  A flip costs two counts on ONE gather (pre: X,Y,Z; post: X,Y',Z with Y' = the
+//        middle set of v->u); a double-edge move is a removal count followed by an addition count.
+//   flag_count's length grows exactly as in the reference: a simplex of a dimension the complex did
+//   not have before must contain the new edge, so it is met by the addition count.
+//
+//   FULL path (neighbourhoods with a common-neighbour list > 64, and fcm_apply where pre/post are
+//   API-visible, src/bin/seo_bt_flip_only_once.rs:51-74): builds the K-vertex neighbourhood, gathers
+//   its K x K adjacency and counts all its simplices before and after the edits.
 #include "fcm_internal.cuh"
 
 #include <algorithm>
@@ -245,9 +257,16 @@ __device__ int local_count_any(const u64* M, int K, int KW, int lane, u64* out, 
 struct WarpSmem {
   u64 *M, *fc, *pre, *post;
   u32 *verts, *edits;
+  // delta path
+  u64 *A, *deep;                       // A[64]: adjacency among the common neighbours; deep[FCM_MAXD]
+  u32 *cv, *cv2;                       // cv[64], cv2[64]: common-neighbour lists (second: K of a double move)
+  int* dflag;                          // [0] deep counts used, [1] highest deep dimension of an added simplex, [2] error
 };
+#define FAST_C 64
 __host__ __device__ inline size_t warp_smem_bytes(u32 Kcap, u32 KWcap) {
-  return (size_t)Kcap * KWcap * 8 + 3 * FCM_MAXD * 8 + (size_t)Kcap * 4 + FCM_MAXEDIT * 2 * 4;
+  size_t full = (size_t)Kcap * KWcap * 8 + 3 * FCM_MAXD * 8 + (size_t)Kcap * 4 + FCM_MAXEDIT * 2 * 4;
+  full = (full + 7) & ~(size_t)7;
+  return full + FAST_C * 8 + FCM_MAXD * 8 + 2 * FAST_C * 4 + 16;
 }
 size_t fcm_chain_smem_per_warp(u32 Kcap, u32 KWcap) { return (warp_smem_bytes(Kcap, KWcap) + 15) & ~(size_t)15; }
 
@@ -259,13 +278,20 @@ __device__ __forceinline__ WarpSmem carve(unsigned char* base, u32 Kcap, u32 KWc
   s.post = s.pre + FCM_MAXD;
   s.verts = (u32*)(s.post + FCM_MAXD);
   s.edits = s.verts + Kcap;
+  size_t off = (size_t)((unsigned char*)(s.edits + FCM_MAXEDIT * 2) - base);
+  off = (off + 7) & ~(size_t)7;
+  s.A = (u64*)(base + off);
+  s.deep = s.A + FAST_C;
+  s.cv = (u32*)(s.deep + FCM_MAXD);
+  s.cv2 = s.cv + FAST_C;
+  s.dflag = (int*)(s.cv2 + FAST_C);
   return s;
 }
 
 // neighbourhood + pre/post local counts of the edits in s.edits (slot, add) — the two
 // flagser_count calls of State::apply_transition (src/lib.rs:62-71).  0 or an FCM_E* code.
-__device__ int transition_counts(const EnsParams& p, const Chain& c, const WarpSmem& s, int nedit,
-                                 int lane, int& K, int& prelen, int& postlen) {
+__device__ __noinline__ int transition_counts(const EnsParams& p, const Chain& c, const WarpSmem& s, int nedit,
+                                              int lane, int& K, int& prelen, int& postlen) {
   if (!build_nbhd(p, s.edits, nedit, s.verts, K, lane)) return FCM_ELIMIT;
   int KW = (K + 63) >> 6;
   KW = KW <= 1 ? 1 : KW <= 2 ? 2 : KW <= 4 ? 4 : 8;
@@ -286,6 +312,212 @@ __device__ int transition_counts(const EnsParams& p, const Chain& c, const WarpS
   return dimov ? FCM_EDIM : FCM_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// DELTA path
+// ---------------------------------------------------------------------------------------------------
+struct P3 { u64 x, y, z; };            // candidates by tag: before u / between u and v / after v
+__device__ __forceinline__ int popc3(const P3& p) { return __popcll(p.x) + __popcll(p.y) + __popcll(p.z); }
+// candidates left after appending vertex w (out-row a) with tag q: tags are non-decreasing along a simplex
+__device__ __forceinline__ P3 child3(const P3& p, u64 a, int q) {
+  P3 r;
+  r.x = q == 0 ? (p.x & a) : 0ULL;
+  r.y = q <= 1 ? (p.y & a) : 0ULL;
+  r.z = p.z & a;
+  return r;
+}
+
+// Common neighbours of the pair and their adjacency, gathered from the chain's rows.
+//   cv[j] = C[j];  A[i] = { j : C[i] -> C[j] };  in*/out* = { j : C[j] -> u|v } / { j : u|v -> C[j] }
+// myA0 / myA1 = A[lane] / A[lane + 32].  Returns false when the list does not fit (c > 64).
+struct Gathered { int c; u64 inU, outU, inV, outV, myA0, myA1; };
+__device__ __forceinline__ bool gather_pair(const EnsParams& p, const u64* adj, u32 pair, u32 u, u32 v,
+                                            u32* cv, u64* A, int lane, Gathered& g) {
+  const u64 o = __ldg(&p.nb_off[pair]);
+  const int c = (int)(__ldg(&p.nb_off[pair + 1]) - o);
+  g.c = c;
+  if (c > FAST_C) return false;
+  const bool v0 = lane < c, v1 = lane + 32 < c;
+  const u32 x0 = v0 ? __ldg(&p.nb_list[o + lane]) : 0u;
+  const u32 x1 = v1 ? __ldg(&p.nb_list[o + 32 + lane]) : 0u;
+  cv[lane] = x0;
+  cv[lane + 32] = x1;
+  const u32* a32 = (const u32*)adj;                     // the same rows as 32-bit words (little endian)
+  const u32 W32 = 2 * p.W;
+  const u32* ru = a32 + (u64)u * W32;
+  const u32* rv = a32 + (u64)v * W32;
+  const u32* r0 = a32 + (u64)x0 * W32;
+  const u32 w0 = x0 >> 5, s0 = x0 & 31;
+  // relations of slot 0 (loads first, ballots after the row loop is in flight)
+  const u32 lu0 = ru[w0], lv0 = rv[w0], li0u = r0[u >> 5], li0v = r0[v >> 5];
+  u32 lu1 = 0, lv1 = 0, li1u = 0, li1v = 0, w1 = 0, s1 = 0;
+  const bool two = c > 32;                              // warp-uniform
+  if (two) {
+    const u32* r1 = a32 + (u64)x1 * W32;
+    w1 = x1 >> 5; s1 = x1 & 31;
+    lu1 = ru[w1]; lv1 = rv[w1]; li1u = r1[u >> 5]; li1v = r1[v >> 5];
+  }
+  __syncwarp();
+  g.myA0 = 0; g.myA1 = 0;
+  for (int i0 = 0; i0 < c; i0 += 4) {                   // 4 rows in flight per iteration
+    u32 t0[4], t1[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int i = min(i0 + k, c - 1);
+      const u32* ri = a32 + (u64)cv[i] * W32;
+      t0[k] = ri[w0];
+      t1[k] = two ? ri[w1] : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int i = i0 + k;
+      if (i < c) {
+        u64 row = __ballot_sync(FULL, v0 && ((t0[k] >> s0) & 1u));
+        if (two) row |= (u64)__ballot_sync(FULL, v1 && ((t1[k] >> s1) & 1u)) << 32;
+        if (lane == 0) A[i] = row;
+        if (i == lane) g.myA0 = row;
+        if (i == lane + 32) g.myA1 = row;
+      }
+    }
+  }
+  g.outU = __ballot_sync(FULL, v0 && ((lu0 >> s0) & 1u));
+  g.outV = __ballot_sync(FULL, v0 && ((lv0 >> s0) & 1u));
+  g.inU = __ballot_sync(FULL, v0 && ((li0u >> (u & 31)) & 1u));
+  g.inV = __ballot_sync(FULL, v0 && ((li0v >> (v & 31)) & 1u));
+  if (two) {
+    g.outU |= (u64)__ballot_sync(FULL, v1 && ((lu1 >> s1) & 1u)) << 32;
+    g.outV |= (u64)__ballot_sync(FULL, v1 && ((lv1 >> s1) & 1u)) << 32;
+    g.inU |= (u64)__ballot_sync(FULL, v1 && ((li1u >> (u & 31)) & 1u)) << 32;
+    g.inV |= (u64)__ballot_sync(FULL, v1 && ((li1v >> (v & 31)) & 1u)) << 32;
+  }
+  __syncwarp();
+  return true;
+}
+
+// tuples of >= DELTA_SD+1 extra vertices: generic DFS, counts into the warp's shared deep[] (by
+// flag_count index).  p0 = candidates of a tuple of `size0` extra vertices (non-empty).
+#define DELTA_SD 3
+__device__ __noinline__ void deep_dfs(P3 p0, int size0, const u64* A, int sign, u64* deep, int* dflag) {
+  P3 P[FCM_MAXD];
+  u64 R[FCM_MAXD];
+  int Q[FCM_MAXD];
+  dflag[0] = 1;
+  int l = 0;
+  P[0] = p0;
+  for (;;) {
+    // entering level l: the tuple has size0 + l extra vertices; its children are simplices of
+    // size0 + l + 1 extra vertices + u + v  =>  flag_count index size0 + l + 2
+    const int d = size0 + l + 2;
+    if (d >= FCM_MAXD) { dflag[2] = FCM_EDIM; return; }
+    atomicAdd((unsigned long long*)&deep[d], (unsigned long long)(long long)(sign * popc3(P[l])));
+    if (sign > 0) atomicMax(&dflag[1], d);
+    Q[l] = 0;
+    R[l] = P[l].x;
+    for (;;) {                                          // next child of level l, or pop
+      while (R[l] == 0 && Q[l] < 2) { Q[l]++; R[l] = Q[l] == 1 ? P[l].y : P[l].z; }
+      if (R[l] == 0) {
+        if (l == 0) return;
+        --l;
+        continue;
+      }
+      const int w = __ffsll((long long)R[l]) - 1;
+      R[l] &= R[l] - 1;
+      const P3 ch = child3(P[l], A[w], Q[l]);
+      if (ch.x | ch.y | ch.z) { P[++l] = ch; break; }
+    }
+  }
+}
+
+// p = candidates of a tuple of L extra vertices (non-empty); cnt[k] is the number of simplices with
+// k + 2 extra vertices (flag_count index k + 3), k = 0..DELTA_SD-1, this lane's share
+template <int L>
+__device__ __forceinline__ void dfs_static(const P3& p, const u64* A, int sign, long long (&cnt)[DELTA_SD],
+                                           u64* deep, int* dflag) {
+  cnt[L - 1] += sign * popc3(p);
+#pragma unroll 1
+  for (int q = 0; q < 3; q++) {
+    u64 R = q == 0 ? p.x : q == 1 ? p.y : p.z;
+    while (R) {
+      const int w = __ffsll((long long)R) - 1;
+      R &= R - 1;
+      const P3 ch = child3(p, A[w], q);
+      if (ch.x | ch.y | ch.z) {
+        if constexpr (L < DELTA_SD) dfs_static<L + 1>(ch, A, sign, cnt, deep, dflag);
+        else deep_dfs(ch, L + 1, A, sign, deep, dflag);
+      }
+    }
+  }
+}
+
+// Number of simplices through the edge u->v by dimension, times `sign`, added to this lane's cnt[]
+// (and the warp's deep[]): X/Y/Z = the three tag masks over the gathered common neighbours.
+__device__ __forceinline__ void count_through_edge(const P3& p0, const Gathered& g, const u64* A, int lane, int sign,
+                                                   long long (&cnt)[DELTA_SD], u64* deep, int* dflag) {
+#pragma unroll 1
+  for (int slot = 0; slot < 2; slot++) {
+    const int w = lane + 32 * slot;
+    if (w >= g.c) break;
+    const u64 a = slot ? g.myA1 : g.myA0;
+    const u64 bit = 1ULL << w;
+#pragma unroll 1
+    for (int q = 0; q < 3; q++) {
+      const u64 m = q == 0 ? p0.x : q == 1 ? p0.y : p0.z;
+      if (!(m & bit)) continue;
+      const P3 ch = child3(p0, a, q);
+      if (ch.x | ch.y | ch.z) dfs_static<1>(ch, A, sign, cnt, deep, dflag);
+    }
+  }
+}
+
+// warp sum of one signed 64-bit value per lane
+__device__ __forceinline__ long long warp_sum_i64(long long v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+
+// Adds, to the flag_count entry this lane owns (index = lane), the warp totals of cnt[] (indices 3..)
+// and of the uniform triangle term tri (index 2).
+__device__ __forceinline__ void fold_counts(long long (&cnt)[DELTA_SD], long long tri, int lane, long long& delta) {
+  bool big = false;
+#pragma unroll
+  for (int k = 0; k < DELTA_SD; k++) big |= ((u64)(cnt[k] + (1LL << 25)) >> 26) != 0;
+  if (!__any_sync(FULL, big)) {
+#pragma unroll
+    for (int k = 0; k < DELTA_SD; k++) {
+      const int t = __reduce_add_sync(FULL, (int)cnt[k]);
+      if (lane == k + 3) delta += t;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < DELTA_SD; k++) {
+      const long long t = warp_sum_i64(cnt[k]);
+      if (lane == k + 3) delta += t;
+    }
+  }
+  if (lane == 2) delta += tri;
+}
+
+__device__ __forceinline__ bool in_sorted(const u32* s, int n, u32 key) {
+  int lo = 0, hi = n;
+  while (lo < hi) { int mid = (lo + hi) >> 1; if (s[mid] < key) lo = mid + 1; else hi = mid; }
+  return lo < n && s[lo] == key;
+}
+__device__ __forceinline__ bool in_list_warp(const u32* s, int n, u32 key, int lane) {
+  return __any_sync(FULL, (lane < n && s[lane] == key) || (lane + 32 < n && s[lane + 32] == key));
+}
+// |C1 u C2 u {a,b,x,y}|: State::edgeset_neighborhood's size for a double-edge move (src/lib.rs:99-111)
+__device__ __forceinline__ int union_size(const u32* l1, int c1, const u32* l2, int c2, u32 a, u32 b, u32 x, u32 y, int lane) {
+  int both = __popc(__ballot_sync(FULL, lane < c2 && in_sorted(l1, c1, l2[lane])));
+  if (c2 > 32) both += __popc(__ballot_sync(FULL, lane + 32 < c2 && in_sorted(l1, c1, l2[lane + 32])));
+  int K = c1 + c2 - both;
+  // endpoints: a, b are never in l1 (their own common neighbours), x, y never in l2
+  K += !in_list_warp(l2, c2, a, lane);
+  K += !in_list_warp(l2, c2, b, lane);
+  if (x != a && x != b) K += !in_list_warp(l1, c1, x, lane);
+  if (y != a && y != b) K += !in_list_warp(l1, c1, y, lane);
+  return K;
+}
+
 // Bounds::check (src/lib.rs:157-160) on the flag_count held one entry per lane
 __device__ __forceinline__ bool bounds_ok(const EnsParams& p, u64 f, int lane) {
   u64 lo = lane < p.nmin ? p.bmin[lane] : 0, hi = lane < p.nmax ? p.bmax[lane] : 0;
@@ -294,9 +526,18 @@ __device__ __forceinline__ bool bounds_ok(const EnsParams& p, u64 f, int lane) {
   return !__any_sync(FULL, bad);
 }
 
-__global__ void __launch_bounds__(128)
+__device__ __forceinline__ void set_adj_bit(const EnsParams& p, u64* adj, u32 from, u32 to, bool add, int lane) {
+  if (lane == 0) {
+    u64* w = &adj[(u64)from * p.W + (to >> 6)];
+    const u64 m = 1ULL << (to & 63);
+    *w = add ? (*w | m) : (*w & ~m);
+  }
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(128, 7)
 chain_step_kernel(const EnsParams p, u64 nsteps, fcm_trace_rec* __restrict__ trace, u32 trace_chain,
-                  u32 smem_per_warp) {
+                  u32 smem_per_warp, int force_full) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const u32 chain = blockIdx.x * (blockDim.x >> 5) + wib;
@@ -318,6 +559,9 @@ chain_step_kernel(const EnsParams p, u64 nsteps, fcm_trace_rec* __restrict__ tra
   u64 sampled = st->sampled, accepted = st->accepted, sumK = st->sumK, nonempty = st->nonempty;
   int err = 0;
   const bool tracing = trace != nullptr && chain == trace_chain;
+  s.deep[lane] = 0;
+  if (lane < 3) s.dflag[lane] = 0;
+  __syncwarp();
 
   for (u64 step = 0; step < nsteps; step++) {
     // ---- Transition::random_move: WeightedIndex<f64>::sample (src/lib.rs:210) ----
@@ -327,9 +571,10 @@ chain_step_kernel(const EnsParams p, u64 nsteps, fcm_trace_rec* __restrict__ tra
     int kind = (p.cum[0] <= chosen) + (p.cum[1] <= chosen) + (p.cum[2] <= chosen);
     int nedit = 0;
     u32 ta = 0, tb = 0, tdm0 = 0, tdm1 = 0;
+    u32 slot = 0, delme = 0;
     if (kind == 0) {                                   // single_edge_flip  src/lib.rs:292-299
       if (c.E) {
-        u32 slot = c.items[gen_range(g, c.E)];
+        slot = c.items[gen_range(g, c.E)];
         uint2 ft = slot_edge(p, slot);
         ta = ft.x; tb = ft.y;
         if (c.pos[slot ^ 1] == FCM_NONE) {
@@ -341,13 +586,12 @@ chain_step_kernel(const EnsParams p, u64 nsteps, fcm_trace_rec* __restrict__ tra
       if (c.ND) {
         if (2ULL * c.ND >= c.E) { err = FCM_EINVAL; break; }   // reference spins forever (FIXME :307)
         u32 dpair = c.dbl[gen_range(g, c.ND)];
-        u32 slot;
         for (;;) {
           slot = c.items[gen_range(g, c.E)];
           if (c.pos[slot ^ 1] == FCM_NONE) break;
         }
         bool first = g.next() < 0x8000000000000000ULL;  // gen_bool(0.5)
-        u32 delme = 2 * dpair + (first ? 1u : 0u);      // first: [min,max] = small -> big
+        delme = 2 * dpair + (first ? 1u : 0u);          // first: [min,max] = small -> big
         uint2 ft = slot_edge(p, slot), dm = slot_edge(p, delme);
         ta = ft.x; tb = ft.y; tdm0 = dm.x; tdm1 = dm.y;
         if (lane == 0) { s.edits[0] = slot ^ 1; s.edits[1] = 1; s.edits[2] = delme; s.edits[3] = 0; }
@@ -357,15 +601,89 @@ chain_step_kernel(const EnsParams p, u64 nsteps, fcm_trace_rec* __restrict__ tra
     __syncwarp();
 
     // ---- State::apply_transition  src/lib.rs:61-79 ----
-    int K = 0, prelen = 0, postlen = 0;
+    int K = 0, prelen = 0;
     u64 fnew = fc;
+    bool bit_cleared = false;                          // double move, delta path: delme's bit is already 0
     if (nedit) {
-      int rc = transition_counts(p, c, s, nedit, lane, K, prelen, postlen);
-      if (rc) { err = rc; break; }
-      u64 pr = lane < min(prelen, len) ? s.pre[lane] : 0;
-      if (__any_sync(FULL, fc < pr)) { err = FCM_EASSERT; break; }
-      len = max(len, postlen);
-      fnew = fc - pr + (lane < postlen ? s.post[lane] : 0);
+      bool done = false;
+      if (!force_full) {
+        long long cnt[DELTA_SD];
+#pragma unroll
+        for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
+        long long tri = 0, delta = 0;
+        int top = 0;                                   // highest flag_count index holding an added simplex
+        Gathered ga;
+        if (kind == 0) {
+          // a flip ta->tb => tb->ta: one gather, the counts through ta->tb leave, those through tb->ta come
+          if (gather_pair(p, c.adj, slot >> 1, ta, tb, s.cv, s.A, lane, ga)) {
+            const u64 X = ga.inU & ga.inV, Z = ga.outU & ga.outV;
+            const P3 post{X, ga.inU & ga.outV, Z}, pre{X, ga.outU & ga.inV, Z};
+            count_through_edge(post, ga, s.A, lane, +1, cnt, s.deep, s.dflag);
+#pragma unroll
+            for (int k = 0; k < DELTA_SD; k++) if (__any_sync(FULL, cnt[k] != 0)) top = k + 3;
+            if (post.x | post.y | post.z) top = max(top, 2);
+            count_through_edge(pre, ga, s.A, lane, -1, cnt, s.deep, s.dflag);
+            tri = (long long)__popcll(post.y) - (long long)__popcll(pre.y);
+            K = ga.c + 2;
+            top = max(top, 1);
+            done = true;
+          }
+        } else {
+          // double move: delme = tdm0->tdm1 leaves (counted in the graph before any edit), then
+          // tb->ta comes (counted in the final graph: delme's bit is cleared in between)
+          const u64 o2 = __ldg(&p.nb_off[delme >> 1]);
+          const int c2 = (int)(__ldg(&p.nb_off[(delme >> 1) + 1]) - o2);
+          const u64 o1 = __ldg(&p.nb_off[slot >> 1]);
+          const int c1 = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - o1);
+          if (c1 <= FAST_C && c2 <= FAST_C) {
+            gather_pair(p, c.adj, delme >> 1, tdm0, tdm1, s.cv2, s.A, lane, ga);
+            const P3 gone{ga.inU & ga.inV, ga.outU & ga.inV, ga.outU & ga.outV};
+            count_through_edge(gone, ga, s.A, lane, -1, cnt, s.deep, s.dflag);
+            tri = -(long long)popc3(gone);
+            set_adj_bit(p, c.adj, tdm0, tdm1, false, lane);
+            bit_cleared = true;
+            long long cntp[DELTA_SD];
+#pragma unroll
+            for (int k = 0; k < DELTA_SD; k++) cntp[k] = 0;
+            gather_pair(p, c.adj, slot >> 1, tb, ta, s.cv, s.A, lane, ga);
+            const P3 come{ga.inU & ga.inV, ga.outU & ga.inV, ga.outU & ga.outV};
+            count_through_edge(come, ga, s.A, lane, +1, cntp, s.deep, s.dflag);
+#pragma unroll
+            for (int k = 0; k < DELTA_SD; k++) { if (__any_sync(FULL, cntp[k] != 0)) top = k + 3; cnt[k] += cntp[k]; }
+            if (come.x | come.y | come.z) top = max(top, 2);
+            tri += (long long)popc3(come);
+            K = union_size(s.cv, c1, s.cv2, c2, ta, tb, tdm0, tdm1, lane);
+            top = max(top, 1);
+            done = true;
+          }
+        }
+        if (done) {
+          fold_counts(cnt, tri, lane, delta);
+          __syncwarp();
+          if (__any_sync(FULL, s.dflag[0] != 0)) {     // some lane went below the static levels
+            if (s.dflag[2]) { err = s.dflag[2]; break; }
+            delta += (long long)s.deep[lane];
+            top = max(top, s.dflag[1]);
+            __syncwarp();
+            s.deep[lane] = 0;
+            if (lane < 3) s.dflag[lane] = 0;
+            __syncwarp();
+          }
+          fnew = fc + (u64)delta;
+          if (__any_sync(FULL, (long long)fnew < 0)) { err = FCM_EASSERT; break; }
+          prelen = 0;                                  // the reverted length never exceeds len (see header)
+          len = max(len, top + 1);
+        }
+      }
+      if (!done) {
+        int postlen = 0;
+        int rc = transition_counts(p, c, s, nedit, lane, K, prelen, postlen);
+        if (rc) { err = rc; break; }
+        u64 pr = lane < min(prelen, len) ? s.pre[lane] : 0;
+        if (__any_sync(FULL, fc < pr)) { err = FCM_EASSERT; break; }
+        len = max(len, postlen);
+        fnew = fc - pr + (lane < postlen ? s.post[lane] : 0);
+      }
       for (int e = 0; e < nedit; e++) {
         if (s.edits[2 * e + 1]) c_add_edge(c, s.edits[2 * e], lane); else c_remove_edge(c, s.edits[2 * e], lane);
       }
@@ -387,6 +705,7 @@ chain_step_kernel(const EnsParams p, u64 nsteps, fcm_trace_rec* __restrict__ tra
       for (int e = 0; e < nedit; e++) {
         if (s.edits[2 * e + 1]) c_remove_edge(c, s.edits[2 * e], lane); else c_add_edge(c, s.edits[2 * e], lane);
       }
+      if (bit_cleared) set_adj_bit(p, c.adj, tdm0, tdm1, true, lane);
       len = max(len, prelen);
     }
     if (tracing && lane == 0) {
@@ -508,7 +827,7 @@ int fcm_chain_launch_step(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev,
   FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   u32 blocks = (e->p.nchains + wpb - 1) / wpb;
   chain_step_kernel<<<blocks, wpb * 32, smem, e->ctx->stream>>>(e->p, nsteps, trace_dev, trace_chain,
-                                                              (u32)e->smem_per_warp);
+                                                              (u32)e->smem_per_warp, e->force_full);
   e->ctx->launches++;
   FCM_CUDA(cudaGetLastError());
   return FCM_OK;

@@ -231,6 +231,13 @@ extern "C" int fcm_ensemble_set_bounds(fcm_ensemble* e, const uint64_t* mn, int 
   return copy_bounds(e->p, mn, nmin, mx, nmax);
 }
 
+extern "C" int fcm_ensemble_set_kernel(fcm_ensemble* e, int kind) {
+  REQUIRE(e, "ensemble is null");
+  REQUIRE(kind == 0 || kind == 1, "kernel kind must be 0 (auto: delta path) or 1 (full pre/post counts)");
+  e->force_full = kind;
+  return FCM_OK;
+}
+
 extern "C" int fcm_ensemble_info(const fcm_ensemble* e, uint32_t* n, uint64_t* npairs, uint32_t* nchains,
                                  uint32_t* maxc, uint64_t* bytes_per_chain) {
   REQUIRE(e, "ensemble is null");

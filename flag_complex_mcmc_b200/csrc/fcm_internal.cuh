@@ -102,6 +102,7 @@ struct fcm_ensemble {
   u64 bytes_per_chain = 0;
   size_t smem_per_warp = 0;
   int warps_per_block = 4;
+  int force_full = 0;                     // 1: every proposal through the full pre/post count path
   fcm_trace_rec* trace_dev = nullptr;
   u64 trace_cap = 0;
   u32* edit_dev = nullptr;                // FCM_MAXEDIT * 2 (slot, add)

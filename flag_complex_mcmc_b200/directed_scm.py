@@ -35,6 +35,15 @@ OEIS_A058298 = [2, 3, 6, 8, 12, 24, 30, 40, 60, 120, 144, 180, 240, 360, 720,
                 79833600, 95800320, 119750400, 159667200]     # src/util.rs:98-105
 
 
+def f64_as_usize(x):
+    """Rust `f64 as usize` (src/bin/sample.rs:90-91): saturating, NaN -> 0."""
+    if not (x > 0.0):
+        return 0
+    if x >= 18446744073709551616.0:
+        return U64
+    return int(x)
+
+
 # ---- util.rs -------------------------------------------------------------------------------------
 def all_le(a, b, z=0):
     """src/util.rs:53-63: element-wise a <= b with the shorter side padded by z."""
@@ -234,8 +243,8 @@ class Bounds:
     @staticmethod
     def target(flag_count, target_relaxation):
         """src/bin/sample.rs:89-92: exact for d < 2, floor(s*(1-+t)) in f64 for d >= 2."""
-        mn = [s if d < 2 else int(math.floor(float(s) * (1.0 - target_relaxation))) for d, s in enumerate(flag_count)]
-        mx = [s if d < 2 else int(math.floor(float(s) * (1.0 + target_relaxation))) for d, s in enumerate(flag_count)]
+        mn = [s if d < 2 else f64_as_usize(math.floor(float(s) * (1.0 - target_relaxation))) for d, s in enumerate(flag_count)]
+        mx = [s if d < 2 else f64_as_usize(math.floor(float(s) * (1.0 + target_relaxation))) for d, s in enumerate(flag_count)]
         return Bounds(mn, mx)
 
     @staticmethod
@@ -293,6 +302,10 @@ class MCMCSampler:
             sd = math.ceil(2.0 * E * math.log2(E)) if E > 0 else 0
             sample_distance = int(sd)
         self.sample_distance = int(sample_distance)
+
+    def set_kernel(self, kind):
+        """0 = delta path (default), 1 = full pre/post neighbourhood counts; identical results."""
+        check(lib().fcm_ensemble_set_kernel(self.h, int(kind)))
 
     # -- stepping --
     def step(self, nproposals):

@@ -122,6 +122,12 @@ int fcm_ensemble_destroy(fcm_ensemble* e);
 int fcm_ensemble_set_bounds(fcm_ensemble* e, const uint64_t* bounds_min, int nmin,
                             const uint64_t* bounds_max, int nmax);
 
+/* how a proposal's count change is computed: 0 = auto (delta path: only the simplices through the
+ * changed edges are enumerated; falls back per proposal when a common-neighbour list exceeds 64),
+ * 1 = always the full pre/post counts of the neighbourhood graph as the reference does them
+ * (src/lib.rs:63,71).  flag_count, accept/reject and the trace are identical. */
+int fcm_ensemble_set_kernel(fcm_ensemble* e, int kind);
+
 /* one record per proposal (optional trace; identical layout in oracle/fcm_oracle.cpp) */
 typedef struct fcm_trace_rec {
   uint32_t flags;              /* bits 0-1 move kind, bit 4 accepted, bit 5 empty transition */

@@ -639,6 +639,13 @@ int orc_intersect_sorted(const u32* a, int na, const u32* b, int nb, u32* out) {
   return (int)r.size();
 }
 
+// Rust `f64 as usize`: saturating, NaN -> 0 (the casts of src/bin/sample.rs:90-91)
+static inline u64 f64_as_usize(double x) {
+  if (!(x > 0.0)) return 0;
+  if (x >= 18446744073709551616.0) return ~0ULL;
+  return (u64)x;
+}
+
 // --- sampler ----------------------------------------------------------------------------------
 // mirrors initialize_new_sampler (src/bin/sample.rs:80-105).  move_weights = 4 doubles
 // ([0.5,0.5,0,0] for --simple).  sample_distance 0 => ceil(2 E log2 E).
@@ -651,8 +658,8 @@ void* orc_sampler_new(u32 n, u64 ne, const u32* edges, u64 seed, double target_r
   Bounds target;
   for (size_t d = 0; d < s->state.flag_count.size(); d++) {
     u64 sc = s->state.flag_count[d];
-    target.flag_count_min.push_back(d < 2 ? sc : (u64)std::floor((double)sc * (1. - target_relaxation)));
-    target.flag_count_max.push_back(d < 2 ? sc : (u64)std::floor((double)sc * (1. + target_relaxation)));
+    target.flag_count_min.push_back(d < 2 ? sc : f64_as_usize(std::floor((double)sc * (1. - target_relaxation))));
+    target.flag_count_max.push_back(d < 2 ? sc : f64_as_usize(std::floor((double)sc * (1. + target_relaxation))));
   }
   int rc = Bounds::calculate(s->state, target, s->bounds, nthreads);
   if (rc) { *err = rc; delete s; return nullptr; }

@@ -29,13 +29,16 @@ def compare_chain(s, chain, o):
     assert np.array_equal(r["edges"], w["edges"])        # container order, not just the set
 
 
+@pytest.mark.parametrize("kernel", [0, 1])
 @pytest.mark.parametrize("name,seed,steps", [("counterexample_seo_greedy_5_start", 0, 20000),
                                              ("counterexample_any_order", 3, 3000),
                                              ("bug_calc_relax_de", 1, 8000),
                                              ("c2_chunglu_279", 0, 20000)])
-def test_trace_parity_single_chain(name, seed, steps, ctx, graphs):
+def test_trace_parity_single_chain(name, seed, steps, kernel, ctx, graphs):
+    # kernel 0 = delta path (simplices through the changed edges only), 1 = full pre/post counts
     n, e = graphs[name]
     s = fcm.initialize_new_sampler(ctx, n, e, [seed], target_relaxation=0.01, simple=True)
+    s.set_kernel(kernel)
     o = orc.Sampler(n, e, seed, 0.01)
     w = o.read()
     assert s.bounds.flag_count_min == w["bounds_min"] and s.bounds.flag_count_max == w["bounds_max"]
@@ -51,11 +54,13 @@ def test_trace_parity_single_chain(name, seed, steps, ctx, graphs):
     s.close()
 
 
-def test_many_chains_match_per_seed_oracle(ctx):
+@pytest.mark.parametrize("kernel", [0, 1])
+def test_many_chains_match_per_seed_oracle(kernel, ctx):
     n = 120
     e = rand_graph(n, 0.12, 21, pdouble=0.3)
     seeds = list(range(40, 40 + 70))                      # 70 chains: partial last block
     s = fcm.initialize_new_sampler(ctx, n, e, seeds, target_relaxation=0.05, simple=True)
+    s.set_kernel(kernel)
     s.step(1500)
     s.step(500)
     allr = s.read_all()
@@ -151,10 +156,12 @@ def test_apply_revert_api(ctx, graphs):
     s.close()
 
 
-def test_rejections_happen_and_revert_restores(ctx, graphs):
+@pytest.mark.parametrize("kernel", [0, 1])
+def test_rejections_happen_and_revert_restores(kernel, ctx, graphs):
     # tight hand-set bounds: most flips are rejected; state must stay consistent
     n, e = graphs["c2_chunglu_279"]
     s = fcm.initialize_new_sampler(ctx, n, e, [9], simple=True)
+    s.set_kernel(kernel)
     o = orc.Sampler(n, e, 9)
     fc = s.initial_flag_count
     mn = [fc[0], fc[1]] + [c - 1 for c in fc[2:]]
@@ -196,3 +203,40 @@ def test_c3_full_size_chains(ctx, graphs, expected):
     r = s.read(17)
     assert ds.trim(r["flag_count"]) == fcm.flagser_count(n, r["edges"], ctx)
     s.close()
+
+
+@pytest.mark.parametrize("n,p,pd,steps,minlen", [(30, 0.3, 0.5, 1500, 6), (50, 0.25, 0.8, 1000, 7), (12, 0.7, 0.2, 600, 8)])
+def test_delta_path_deep_and_double_heavy(n, p, pd, steps, minlen, ctx):
+    # dense graphs with many double edges: common neighbours carry several tags and the simplices
+    # through an edge go beyond the delta path's register levels.  Loose bounds so that chains move;
+    # delta path, full path and oracle are compared proposal by proposal.
+    e = rand_graph(n, p, 1000 + n, pdouble=pd)
+    o = orc.Sampler(n, e, 7, 0.9, nthreads=8)
+    want = o.steps(steps)
+    assert len(o.read()["flag_count"]) >= minlen         # >= 7: beyond the register levels (index > 5)
+    for kernel in (0, 1):
+        s = fcm.initialize_new_sampler(ctx, n, e, [7], target_relaxation=0.9, simple=True)
+        s.set_kernel(kernel)
+        assert_trace_equal(s.step_trace(steps, 0), want)
+        compare_chain(s, 0, o)
+        r = s.read(0)
+        assert ds.trim(r["flag_count"]) == fcm.flagser_count(n, r["edges"], ctx)
+        s.close()
+
+
+def test_delta_path_flag_count_length_growth(ctx):
+    # transitive tournament with one edge reversed: flipping it back creates a simplex of a dimension
+    # the complex did not have, so flag_count must grow in length exactly as src/lib.rs:72-74 does
+    m = 6
+    e = [(a, b) for a in range(m) for b in range(a + 1, m)]
+    e[e.index((0, m - 1))] = (m - 1, 0)
+    e = np.array(e, dtype=np.uint32)
+    for seed in range(6):
+        o = orc.Sampler(m, e, seed, 5.0)
+        want = o.steps(400)
+        for kernel in (0, 1):
+            s = fcm.initialize_new_sampler(ctx, m, e, [seed], target_relaxation=5.0, simple=True)
+            s.set_kernel(kernel)
+            assert_trace_equal(s.step_trace(400, 0), want)
+            compare_chain(s, 0, o)                         # flag_count incl. its length (trailing zeros)
+            s.close()
