@@ -176,7 +176,7 @@ __device__ void gather_local(const EnsParams& p, const u64* adj, const u32* vert
 #pragma unroll 4
     for (int i = 0; i < K; i++) {
       const u64* row = adj + (u64)verts[i] * p.W;
-      bool bit = have && ((row[gw] >> gs) & 1ULL);
+      bool bit = have && ((__ldcg(&row[gw]) >> gs) & 1ULL);
       u32 b = __ballot_sync(FULL, bit);
       if (lane == 0) M32[i * 2 * KW + c] = b;
     }
@@ -258,15 +258,16 @@ struct WarpSmem {
   u64 *M, *fc, *pre, *post;
   u32 *verts, *edits;
   // delta path
-  u64 *A, *deep;                       // A[64]: adjacency among the common neighbours; deep[FCM_MAXD]
-  u32 *cv, *cv2;                       // cv[64], cv2[64]: common-neighbour lists (second: K of a double move)
+  u64 *A, *deep;                       // A[64+4]: adjacency among the common neighbours; deep[FCM_MAXD]
+  u32 *cv, *cv2, *rowoff;              // cv/cv2[64]: common-neighbour lists of the two pairs; rowoff[64]: their row offsets
   int* dflag;                          // [0] deep counts used, [1] highest deep dimension of an added simplex, [2] error
 };
 #define FAST_C 64
 __host__ __device__ inline size_t warp_smem_bytes(u32 Kcap, u32 KWcap) {
   size_t full = (size_t)Kcap * KWcap * 8 + 3 * FCM_MAXD * 8 + (size_t)Kcap * 4 + FCM_MAXEDIT * 2 * 4;
   full = (full + 7) & ~(size_t)7;
-  return full + FAST_C * 8 + FCM_MAXD * 8 + 2 * FAST_C * 4 + 16;
+  full = (full + 15) & ~(size_t)15;
+  return full + (FAST_C + 4) * 8 + FCM_MAXD * 8 + 3 * FAST_C * 4 + 16;
 }
 size_t fcm_chain_smem_per_warp(u32 Kcap, u32 KWcap) { return (warp_smem_bytes(Kcap, KWcap) + 15) & ~(size_t)15; }
 
@@ -279,10 +280,11 @@ __device__ __forceinline__ WarpSmem carve(unsigned char* base, u32 Kcap, u32 KWc
   s.verts = (u32*)(s.post + FCM_MAXD);
   s.edits = s.verts + Kcap;
   size_t off = (size_t)((unsigned char*)(s.edits + FCM_MAXEDIT * 2) - base);
-  off = (off + 7) & ~(size_t)7;
+  off = (off + 15) & ~(size_t)15;
   s.A = (u64*)(base + off);
-  s.deep = s.A + FAST_C;
-  s.cv = (u32*)(s.deep + FCM_MAXD);
+  s.deep = s.A + FAST_C + 4;
+  s.rowoff = (u32*)(s.deep + FCM_MAXD);                // 16-byte aligned: read four at a time
+  s.cv = s.rowoff + FAST_C;
   s.cv2 = s.cv + FAST_C;
   s.dflag = (int*)(s.cv2 + FAST_C);
   return s;
@@ -315,105 +317,91 @@ __device__ __noinline__ int transition_counts(const EnsParams& p, const Chain& c
 // ---------------------------------------------------------------------------------------------------
 // DELTA path
 // ---------------------------------------------------------------------------------------------------
-struct P3 { u64 x, y, z; };            // candidates by tag: before u / between u and v / after v
-__device__ __forceinline__ int popc3(const P3& p) { return __popcll(p.x) + __popcll(p.y) + __popcll(p.z); }
-// candidates left after appending vertex w (out-row a) with tag q: tags are non-decreasing along a simplex
-__device__ __forceinline__ P3 child3(const P3& p, u64 a, int q) {
-  P3 r;
-  r.x = q == 0 ? (p.x & a) : 0ULL;
-  r.y = q <= 1 ? (p.y & a) : 0ULL;
-  r.z = p.z & a;
-  return r;
-}
+#define DELTA_SD 3                     // tuple sizes 1..3 are walked in registers, deeper ones generically
+__device__ __forceinline__ int popc_m(u32 x) { return __popc(x); }
+__device__ __forceinline__ int popc_m(u64 x) { return __popcll(x); }
+__device__ __forceinline__ int low_m(u32 x) { return __ffs((int)x) - 1; }
+__device__ __forceinline__ int low_m(u64 x) { return __ffsll((long long)x) - 1; }
 
-// Common neighbours of the pair and their adjacency, gathered from the chain's rows.
-//   cv[j] = C[j];  A[i] = { j : C[i] -> C[j] };  in*/out* = { j : C[j] -> u|v } / { j : u|v -> C[j] }
-// myA0 / myA1 = A[lane] / A[lane + 32].  Returns false when the list does not fit (c > 64).
-struct Gathered { int c; u64 inU, outU, inV, outV, myA0, myA1; };
-__device__ __forceinline__ bool gather_pair(const EnsParams& p, const u64* adj, u32 pair, u32 u, u32 v,
-                                            u32* cv, u64* A, int lane, Gathered& g) {
-  const u64 o = __ldg(&p.nb_off[pair]);
-  const int c = (int)(__ldg(&p.nb_off[pair + 1]) - o);
-  g.c = c;
-  if (c > FAST_C) return false;
-  const bool v0 = lane < c, v1 = lane + 32 < c;
-  const u32 x0 = v0 ? __ldg(&p.nb_list[o + lane]) : 0u;
-  const u32 x1 = v1 ? __ldg(&p.nb_list[o + 32 + lane]) : 0u;
-  cv[lane] = x0;
-  cv[lane + 32] = x1;
-  const u32* a32 = (const u32*)adj;                     // the same rows as 32-bit words (little endian)
+// Common neighbours C of the pair and their adjacency, gathered from the chain's rows (32-bit words,
+// L2-cached loads: a row is touched once per proposal and is rewritten by RED atomics on accept).
+//   list[j] = C[j];  A[i] = { j : C[i] -> C[j] };  in*/out* = { j : C[j] -> u|v } / { j : u|v -> C[j] }
+// The caller has checked c <= FAST_C.
+struct Gathered { int c; u64 inU, outU, inV, outV; };
+__device__ __forceinline__ void gather_pair(const EnsParams& p, const u32* a32, u64 o, int c, u32 u, u32 v,
+                                            u32* list, u32* rowoff, u64* A, int lane, Gathered& g) {
   const u32 W32 = 2 * p.W;
-  const u32* ru = a32 + (u64)u * W32;
-  const u32* rv = a32 + (u64)v * W32;
-  const u32* r0 = a32 + (u64)x0 * W32;
-  const u32 w0 = x0 >> 5, s0 = x0 & 31;
-  // relations of slot 0 (loads first, ballots after the row loop is in flight)
-  const u32 lu0 = ru[w0], lv0 = rv[w0], li0u = r0[u >> 5], li0v = r0[v >> 5];
-  u32 lu1 = 0, lv1 = 0, li1u = 0, li1v = 0, w1 = 0, s1 = 0;
-  const bool two = c > 32;                              // warp-uniform
-  if (two) {
-    const u32* r1 = a32 + (u64)x1 * W32;
-    w1 = x1 >> 5; s1 = x1 & 31;
-    lu1 = ru[w1]; lv1 = rv[w1]; li1u = r1[u >> 5]; li1v = r1[v >> 5];
+  const int ncs = (c + 31) >> 5;                        // column slots: lanes hold C[lane], C[lane + 32]
+  const int cpad = (c + 3) & ~3;                        // rows are walked four at a time
+  g.c = c; g.inU = g.outU = g.inV = g.outV = 0;
+  for (int cs = 0; cs < ncs; cs++) {
+    const int j = cs * 32 + lane;
+    const u32 x = j < c ? __ldg(&p.nb_list[o + j]) : 0u;
+    list[j] = x;
+    rowoff[j] = x * W32;                                // word offset of row x (n*W*2 < 2^32 is checked at create)
   }
   __syncwarp();
-  g.myA0 = 0; g.myA1 = 0;
-  for (int i0 = 0; i0 < c; i0 += 4) {                   // 4 rows in flight per iteration
-    u32 t0[4], t1[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-      const int i = min(i0 + k, c - 1);
-      const u32* ri = a32 + (u64)cv[i] * W32;
-      t0[k] = ri[w0];
-      t1[k] = two ? ri[w1] : 0u;
-    }
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-      const int i = i0 + k;
-      if (i < c) {
-        u64 row = __ballot_sync(FULL, v0 && ((t0[k] >> s0) & 1u));
-        if (two) row |= (u64)__ballot_sync(FULL, v1 && ((t1[k] >> s1) & 1u)) << 32;
-        if (lane == 0) A[i] = row;
-        if (i == lane) g.myA0 = row;
-        if (i == lane + 32) g.myA1 = row;
+  const u32* ru = a32 + u * W32;
+  const u32* rv = a32 + v * W32;
+#pragma unroll 1
+  for (int cs = 0; cs < ncs; cs++) {
+    const int j = cs * 32 + lane;
+    const u32 x = list[j];
+    const u32 w = x >> 5;
+    const u32 m = j < c ? 1u << (x & 31) : 0u;          // 0 for idle lanes: never votes
+    const u32* rx = a32 + rowoff[j];
+    const u32 lu = __ldcg(&ru[w]), lv = __ldcg(&rv[w]);
+    const u32 xu = __ldcg(&rx[u >> 5]), xv = __ldcg(&rx[v >> 5]);
+    u32* A32 = (u32*)A + cs;
+#pragma unroll 1
+    for (int i0 = 0; i0 < cpad; i0 += 4) {
+      const uint4 ro = *(const uint4*)&rowoff[i0];      // rows past c read offset 0 (row 0): never used
+      const u32 t0 = __ldcg(&a32[ro.x + w]), t1 = __ldcg(&a32[ro.y + w]);
+      const u32 t2 = __ldcg(&a32[ro.z + w]), t3 = __ldcg(&a32[ro.w + w]);
+      const u32 b0 = __ballot_sync(FULL, t0 & m), b1 = __ballot_sync(FULL, t1 & m);
+      const u32 b2 = __ballot_sync(FULL, t2 & m), b3 = __ballot_sync(FULL, t3 & m);
+      if (lane == 0) {
+        if (cs == 0) { A[i0] = b0; A[i0 + 1] = b1; A[i0 + 2] = b2; A[i0 + 3] = b3; }
+        else { A32[2 * i0] = b0; A32[2 * i0 + 2] = b1; A32[2 * i0 + 4] = b2; A32[2 * i0 + 6] = b3; }
       }
     }
-  }
-  g.outU = __ballot_sync(FULL, v0 && ((lu0 >> s0) & 1u));
-  g.outV = __ballot_sync(FULL, v0 && ((lv0 >> s0) & 1u));
-  g.inU = __ballot_sync(FULL, v0 && ((li0u >> (u & 31)) & 1u));
-  g.inV = __ballot_sync(FULL, v0 && ((li0v >> (v & 31)) & 1u));
-  if (two) {
-    g.outU |= (u64)__ballot_sync(FULL, v1 && ((lu1 >> s1) & 1u)) << 32;
-    g.outV |= (u64)__ballot_sync(FULL, v1 && ((lv1 >> s1) & 1u)) << 32;
-    g.inU |= (u64)__ballot_sync(FULL, v1 && ((li1u >> (u & 31)) & 1u)) << 32;
-    g.inV |= (u64)__ballot_sync(FULL, v1 && ((li1v >> (v & 31)) & 1u)) << 32;
+    const int sh = 32 * cs;
+    g.outU |= (u64)__ballot_sync(FULL, lu & m) << sh;
+    g.outV |= (u64)__ballot_sync(FULL, lv & m) << sh;
+    g.inU |= (u64)__ballot_sync(FULL, m && ((xu >> (u & 31)) & 1u)) << sh;
+    g.inV |= (u64)__ballot_sync(FULL, m && ((xv >> (v & 31)) & 1u)) << sh;
   }
   __syncwarp();
-  return true;
 }
 
-// tuples of >= DELTA_SD+1 extra vertices: generic DFS, counts into the warp's shared deep[] (by
-// flag_count index).  p0 = candidates of a tuple of `size0` extra vertices (non-empty).
-#define DELTA_SD 3
-__device__ __noinline__ void deep_dfs(P3 p0, int size0, const u64* A, int sign, u64* deep, int* dflag) {
-  P3 P[FCM_MAXD];
-  u64 R[FCM_MAXD];
+// local index of vertex x in list[0..c) or -1 (warp-uniform)
+__device__ __forceinline__ int list_index(const u32* list, int c, u32 x, int lane) {
+  u32 b = __ballot_sync(FULL, lane < c && list[lane] == x);
+  if (b) return __ffs(b) - 1;
+  if (c > 32) { b = __ballot_sync(FULL, lane + 32 < c && list[lane + 32] == x); if (b) return 32 + __ffs(b) - 1; }
+  return -1;
+}
+
+// tuples of more than DELTA_SD extra vertices: generic DFS, counts into the warp's shared deep[] (by
+// flag_count index).  (px,py,pz) = candidates of a tuple of `size0` extra vertices (non-empty).
+__device__ __noinline__ void deep_dfs(u64 px, u64 py, u64 pz, int size0, const u64* A, int sign, u64* deep, int* dflag) {
+  u64 PX[FCM_MAXD], PY[FCM_MAXD], PZ[FCM_MAXD], R[FCM_MAXD];
   int Q[FCM_MAXD];
   dflag[0] = 1;
   int l = 0;
-  P[0] = p0;
+  PX[0] = px; PY[0] = py; PZ[0] = pz;
   for (;;) {
-    // entering level l: the tuple has size0 + l extra vertices; its children are simplices of
+    // entering level l: the tuple has size0 + l extra vertices; each candidate closes a simplex of
     // size0 + l + 1 extra vertices + u + v  =>  flag_count index size0 + l + 2
     const int d = size0 + l + 2;
     if (d >= FCM_MAXD) { dflag[2] = FCM_EDIM; return; }
-    atomicAdd((unsigned long long*)&deep[d], (unsigned long long)(long long)(sign * popc3(P[l])));
+    const int pc = __popcll(PX[l]) + __popcll(PY[l]) + __popcll(PZ[l]);
+    atomicAdd((unsigned long long*)&deep[d], (unsigned long long)(long long)(sign * pc));
     if (sign > 0) atomicMax(&dflag[1], d);
     Q[l] = 0;
-    R[l] = P[l].x;
+    R[l] = PX[l];
     for (;;) {                                          // next child of level l, or pop
-      while (R[l] == 0 && Q[l] < 2) { Q[l]++; R[l] = Q[l] == 1 ? P[l].y : P[l].z; }
+      while (R[l] == 0 && Q[l] < 2) { Q[l]++; R[l] = Q[l] == 1 ? PY[l] : PZ[l]; }
       if (R[l] == 0) {
         if (l == 0) return;
         --l;
@@ -421,80 +409,54 @@ __device__ __noinline__ void deep_dfs(P3 p0, int size0, const u64* A, int sign, 
       }
       const int w = __ffsll((long long)R[l]) - 1;
       R[l] &= R[l] - 1;
-      const P3 ch = child3(P[l], A[w], Q[l]);
-      if (ch.x | ch.y | ch.z) { P[++l] = ch; break; }
+      const u64 a = A[w];
+      const u64 cx = Q[l] == 0 ? (PX[l] & a) : 0ULL, cy = Q[l] <= 1 ? (PY[l] & a) : 0ULL, cz = PZ[l] & a;
+      if (cx | cy | cz) { ++l; PX[l] = cx; PY[l] = cy; PZ[l] = cz; break; }
     }
   }
 }
 
-// p = candidates of a tuple of L extra vertices (non-empty); cnt[k] is the number of simplices with
-// k + 2 extra vertices (flag_count index k + 3), k = 0..DELTA_SD-1, this lane's share
-template <int L>
-__device__ __forceinline__ void dfs_static(const P3& p, const u64* A, int sign, long long (&cnt)[DELTA_SD],
-                                           u64* deep, int* dflag) {
-  cnt[L - 1] += sign * popc3(p);
+// (px,py,pz) = candidates (by tag) of a tuple of L extra vertices, non-empty.  cnt[k] = this lane's
+// signed number of simplices with k + 2 extra vertices (flag_count index k + 3).  |cnt| cannot
+// overflow: at most 64^3 tuples at the register levels, each adding <= 192.
+template <int L, typename M>
+__device__ __forceinline__ void walk(M px, M py, M pz, const u64* A, int sign, int (&cnt)[DELTA_SD], u64* deep, int* dflag) {
+  cnt[L - 1] += sign * (popc_m(px) + popc_m(py) + popc_m(pz));
 #pragma unroll 1
   for (int q = 0; q < 3; q++) {
-    u64 R = q == 0 ? p.x : q == 1 ? p.y : p.z;
+    M R = q == 0 ? px : q == 1 ? py : pz;
+    const M kx = q == 0 ? px : (M)0, ky = q <= 1 ? py : (M)0;   // tags never decrease along a simplex
     while (R) {
-      const int w = __ffsll((long long)R) - 1;
+      const int w = low_m(R);
       R &= R - 1;
-      const P3 ch = child3(p, A[w], q);
-      if (ch.x | ch.y | ch.z) {
-        if constexpr (L < DELTA_SD) dfs_static<L + 1>(ch, A, sign, cnt, deep, dflag);
-        else deep_dfs(ch, L + 1, A, sign, deep, dflag);
+      const M a = (M)A[w];
+      const M cx = kx & a, cy = ky & a, cz = pz & a;
+      if (cx | cy | cz) {
+        if constexpr (L < DELTA_SD) walk<L + 1, M>(cx, cy, cz, A, sign, cnt, deep, dflag);
+        else deep_dfs(cx, cy, cz, L + 1, A, sign, deep, dflag);
       }
     }
   }
 }
 
-// Number of simplices through the edge u->v by dimension, times `sign`, added to this lane's cnt[]
-// (and the warp's deep[]): X/Y/Z = the three tag masks over the gathered common neighbours.
-__device__ __forceinline__ void count_through_edge(const P3& p0, const Gathered& g, const u64* A, int lane, int sign,
-                                                   long long (&cnt)[DELTA_SD], u64* deep, int* dflag) {
+// Simplices through the edge u->v with >= 2 extra vertices, by dimension, times `sign`: one root
+// (extra vertex) per lane; (X,Y,Z) = who may stand before u / between u and v / after v.
+template <typename M>
+__device__ __forceinline__ void count_through_edge(M X, M Y, M Z, int c, const u64* A, int lane, int sign,
+                                                   int (&cnt)[DELTA_SD], u64* deep, int* dflag) {
 #pragma unroll 1
-  for (int slot = 0; slot < 2; slot++) {
-    const int w = lane + 32 * slot;
-    if (w >= g.c) break;
-    const u64 a = slot ? g.myA1 : g.myA0;
-    const u64 bit = 1ULL << w;
+  for (int w = lane; w < c; w += 32) {
+    const M a = (M)A[w];
+    const M bit = (M)1 << w;
+    const M zx = Z & a, yx = Y & a, xx = X & a;
 #pragma unroll 1
-    for (int q = 0; q < 3; q++) {
-      const u64 m = q == 0 ? p0.x : q == 1 ? p0.y : p0.z;
+    for (int q = 0; q < 3; q++) {                       // the tags this root may carry
+      const M m = q == 0 ? X : q == 1 ? Y : Z;
       if (!(m & bit)) continue;
-      const P3 ch = child3(p0, a, q);
-      if (ch.x | ch.y | ch.z) dfs_static<1>(ch, A, sign, cnt, deep, dflag);
+      const M cx = q == 0 ? xx : (M)0, cy = q <= 1 ? yx : (M)0;
+      if (cx | cy | zx) walk<1, M>(cx, cy, zx, A, sign, cnt, deep, dflag);
     }
   }
-}
-
-// warp sum of one signed 64-bit value per lane
-__device__ __forceinline__ long long warp_sum_i64(long long v) {
-#pragma unroll
-  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
-  return v;
-}
-
-// Adds, to the flag_count entry this lane owns (index = lane), the warp totals of cnt[] (indices 3..)
-// and of the uniform triangle term tri (index 2).
-__device__ __forceinline__ void fold_counts(long long (&cnt)[DELTA_SD], long long tri, int lane, long long& delta) {
-  bool big = false;
-#pragma unroll
-  for (int k = 0; k < DELTA_SD; k++) big |= ((u64)(cnt[k] + (1LL << 25)) >> 26) != 0;
-  if (!__any_sync(FULL, big)) {
-#pragma unroll
-    for (int k = 0; k < DELTA_SD; k++) {
-      const int t = __reduce_add_sync(FULL, (int)cnt[k]);
-      if (lane == k + 3) delta += t;
-    }
-  } else {
-#pragma unroll
-    for (int k = 0; k < DELTA_SD; k++) {
-      const long long t = warp_sum_i64(cnt[k]);
-      if (lane == k + 3) delta += t;
-    }
-  }
-  if (lane == 2) delta += tri;
 }
 
 __device__ __forceinline__ bool in_sorted(const u32* s, int n, u32 key) {
@@ -502,19 +464,16 @@ __device__ __forceinline__ bool in_sorted(const u32* s, int n, u32 key) {
   while (lo < hi) { int mid = (lo + hi) >> 1; if (s[mid] < key) lo = mid + 1; else hi = mid; }
   return lo < n && s[lo] == key;
 }
-__device__ __forceinline__ bool in_list_warp(const u32* s, int n, u32 key, int lane) {
-  return __any_sync(FULL, (lane < n && s[lane] == key) || (lane + 32 < n && s[lane + 32] == key));
-}
 // |C1 u C2 u {a,b,x,y}|: State::edgeset_neighborhood's size for a double-edge move (src/lib.rs:99-111)
 __device__ __forceinline__ int union_size(const u32* l1, int c1, const u32* l2, int c2, u32 a, u32 b, u32 x, u32 y, int lane) {
   int both = __popc(__ballot_sync(FULL, lane < c2 && in_sorted(l1, c1, l2[lane])));
   if (c2 > 32) both += __popc(__ballot_sync(FULL, lane + 32 < c2 && in_sorted(l1, c1, l2[lane + 32])));
   int K = c1 + c2 - both;
   // endpoints: a, b are never in l1 (their own common neighbours), x, y never in l2
-  K += !in_list_warp(l2, c2, a, lane);
-  K += !in_list_warp(l2, c2, b, lane);
-  if (x != a && x != b) K += !in_list_warp(l1, c1, x, lane);
-  if (y != a && y != b) K += !in_list_warp(l1, c1, y, lane);
+  K += list_index(l2, c2, a, lane) < 0;
+  K += list_index(l2, c2, b, lane) < 0;
+  if (x != a && x != b) K += list_index(l1, c1, x, lane) < 0;
+  if (y != a && y != b) K += list_index(l1, c1, y, lane) < 0;
   return K;
 }
 
@@ -526,17 +485,15 @@ __device__ __forceinline__ bool bounds_ok(const EnsParams& p, u64 f, int lane) {
   return !__any_sync(FULL, bad);
 }
 
-__device__ __forceinline__ void set_adj_bit(const EnsParams& p, u64* adj, u32 from, u32 to, bool add, int lane) {
-  if (lane == 0) {
-    u64* w = &adj[(u64)from * p.W + (to >> 6)];
-    const u64 m = 1ULL << (to & 63);
-    *w = add ? (*w | m) : (*w & ~m);
-  }
-  __syncwarp();
+// adjacency bit from->to of the chain, no return value needed (RED at L2; rows are read with ld.cg)
+__device__ __forceinline__ void red_adj_bit(const EnsParams& p, u32* a32, u32 from, u32 to, bool add) {
+  u32* w = a32 + (u64)from * (2 * p.W) + (to >> 5);
+  const u32 m = 1u << (to & 31);
+  if (add) atomicOr(w, m); else atomicAnd(w, ~m);
 }
 
 __global__ void __launch_bounds__(128, 7)
-chain_step_kernel(const EnsParams p, u64 nsteps, fcm_trace_rec* __restrict__ trace, u32 trace_chain,
+chain_step_kernel(const EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ trace, u32 trace_chain,
                   u32 smem_per_warp, int force_full) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -553,164 +510,179 @@ chain_step_kernel(const EnsParams p, u64 nsteps, fcm_trace_rec* __restrict__ tra
   c.dbl = p.dbl + (u64)chain * p.npairs;
   c.dblpos = p.dblpos + (u64)chain * p.npairs;
   c.E = st->E; c.ND = st->ND;
+  u32* const a32 = (u32*)c.adj;
   Rng g{st->rng[0], st->rng[1], st->rng[2], st->rng[3]};
   u64 fc = st->flag_count[lane];                       // lane d owns flag_count[d]
   int len = st->fc_len;
-  u64 sampled = st->sampled, accepted = st->accepted, sumK = st->sumK, nonempty = st->nonempty;
+  u32 accepted = 0, sumK = 0, nonempty = 0;            // per launch (nsteps <= 2^24: the host splits longer runs)
   int err = 0;
   const bool tracing = trace != nullptr && chain == trace_chain;
   s.deep[lane] = 0;
   if (lane < 3) s.dflag[lane] = 0;
   __syncwarp();
 
-  for (u64 step = 0; step < nsteps; step++) {
+  u32 step = 0;
+  for (; step < nsteps; step++) {
     // ---- Transition::random_move: WeightedIndex<f64>::sample (src/lib.rs:210) ----
-    u64 r = g.next();
-    double v = __longlong_as_double((long long)((r >> 12) | 0x3ff0000000000000ULL)) - 1.0;
-    double chosen = __dadd_rn(__dmul_rn(v, p.scale), 0.0);
-    int kind = (p.cum[0] <= chosen) + (p.cum[1] <= chosen) + (p.cum[2] <= chosen);
-    int nedit = 0;
-    u32 ta = 0, tb = 0, tdm0 = 0, tdm1 = 0;
-    u32 slot = 0, delme = 0;
-    if (kind == 0) {                                   // single_edge_flip  src/lib.rs:292-299
+    const u64 r = g.next();
+    const double v = __longlong_as_double((long long)((r >> 12) | 0x3ff0000000000000ULL)) - 1.0;
+    const double chosen = __dadd_rn(__dmul_rn(v, p.scale), 0.0);
+    const int kind = (p.cum[0] <= chosen) + (p.cum[1] <= chosen) + (p.cum[2] <= chosen);
+    if (kind > 1) { err = FCM_EUNSUPPORTED; break; }
+    // ---- single_edge_flip (src/lib.rs:292-299) / double_edge_move (:304-325): the draws ----
+    bool live = false;                                  // a non-empty transition
+    u32 idx = 0, slot = 0, didx = 0, dpair = 0, delme = 0, last = 0;
+    if (kind == 0) {
       if (c.E) {
-        slot = c.items[gen_range(g, c.E)];
-        uint2 ft = slot_edge(p, slot);
-        ta = ft.x; tb = ft.y;
-        if (c.pos[slot ^ 1] == FCM_NONE) {
-          if (lane == 0) { s.edits[0] = slot; s.edits[1] = 0; s.edits[2] = slot ^ 1; s.edits[3] = 1; }
-          nedit = 2;
-        }
+        idx = (u32)gen_range(g, c.E);
+        slot = c.items[idx];
+        last = c.items[c.E - 1];
+        live = c.pos[slot ^ 1] == FCM_NONE;             // the reverse edge exists: empty transition
       }
-    } else if (kind == 1) {                            // double_edge_move  src/lib.rs:304-325
-      if (c.ND) {
-        if (2ULL * c.ND >= c.E) { err = FCM_EINVAL; break; }   // reference spins forever (FIXME :307)
-        u32 dpair = c.dbl[gen_range(g, c.ND)];
-        for (;;) {
-          slot = c.items[gen_range(g, c.E)];
-          if (c.pos[slot ^ 1] == FCM_NONE) break;
-        }
-        bool first = g.next() < 0x8000000000000000ULL;  // gen_bool(0.5)
-        delme = 2 * dpair + (first ? 1u : 0u);          // first: [min,max] = small -> big
-        uint2 ft = slot_edge(p, slot), dm = slot_edge(p, delme);
-        ta = ft.x; tb = ft.y; tdm0 = dm.x; tdm1 = dm.y;
-        if (lane == 0) { s.edits[0] = slot ^ 1; s.edits[1] = 1; s.edits[2] = delme; s.edits[3] = 0; }
-        nedit = 2;
-      }
-    } else { err = FCM_EUNSUPPORTED; break; }
-    __syncwarp();
+    } else if (c.ND) {
+      if (2ULL * c.ND >= c.E) { err = FCM_EINVAL; break; }     // reference spins forever (FIXME :307)
+      didx = (u32)gen_range(g, c.ND);
+      dpair = c.dbl[didx];
+      do {
+        idx = (u32)gen_range(g, c.E);
+        slot = c.items[idx];
+      } while (c.pos[slot ^ 1] != FCM_NONE);
+      const bool first = g.next() < 0x8000000000000000ULL;     // gen_bool(0.5)
+      delme = 2 * dpair + (first ? 1u : 0u);                   // first: [min,max] = small -> big
+      live = true;
+    }
+    u32 ta = 0, tb = 0, tdm0 = 0, tdm1 = 0;
+    if (kind == 0 ? c.E != 0 : live) { const uint2 ft = slot_edge(p, slot); ta = ft.x; tb = ft.y; }
+    if (kind == 1 && live) { const uint2 dm = slot_edge(p, delme); tdm0 = dm.x; tdm1 = dm.y; }
 
-    // ---- State::apply_transition  src/lib.rs:61-79 ----
-    int K = 0, prelen = 0;
+    // ---- State::apply_transition  src/lib.rs:61-79: flag_count += post - pre ----
+    int K = 0;
     u64 fnew = fc;
-    bool bit_cleared = false;                          // double move, delta path: delme's bit is already 0
-    if (nedit) {
-      bool done = false;
-      if (!force_full) {
-        long long cnt[DELTA_SD];
+    if (live) {
+      // phase 0 = the edge that comes (flip: tb->ta; double move: tb->ta as well), phase 1 = the edge
+      // that goes (flip: ta->tb, same pair; double move: delme = tdm0->tdm1)
+      const u32 pair0 = slot >> 1, pair1 = kind == 0 ? pair0 : (delme >> 1);
+      const u64 o0 = __ldg(&p.nb_off[pair0]), o1 = __ldg(&p.nb_off[pair1]);
+      const int c0 = (int)(__ldg(&p.nb_off[pair0 + 1]) - o0), c1 = (int)(__ldg(&p.nb_off[pair1 + 1]) - o1);
+      if (!force_full && c0 <= FAST_C && c1 <= FAST_C) {
+        int cnt[DELTA_SD];
 #pragma unroll
         for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
-        long long tri = 0, delta = 0;
-        int top = 0;                                   // highest flag_count index holding an added simplex
+        int tri = 0, top = 1;
         Gathered ga;
-        if (kind == 0) {
-          // a flip ta->tb => tb->ta: one gather, the counts through ta->tb leave, those through tb->ta come
-          if (gather_pair(p, c.adj, slot >> 1, ta, tb, s.cv, s.A, lane, ga)) {
-            const u64 X = ga.inU & ga.inV, Z = ga.outU & ga.outV;
-            const P3 post{X, ga.inU & ga.outV, Z}, pre{X, ga.outU & ga.inV, Z};
-            count_through_edge(post, ga, s.A, lane, +1, cnt, s.deep, s.dflag);
-#pragma unroll
-            for (int k = 0; k < DELTA_SD; k++) if (__any_sync(FULL, cnt[k] != 0)) top = k + 3;
-            if (post.x | post.y | post.z) top = max(top, 2);
-            count_through_edge(pre, ga, s.A, lane, -1, cnt, s.deep, s.dflag);
-            tri = (long long)__popcll(post.y) - (long long)__popcll(pre.y);
-            K = ga.c + 2;
-            top = max(top, 1);
-            done = true;
+#pragma unroll 1
+        for (int ph = 0; ph < 2; ph++) {
+          int sign = 1;
+          u64 X, Y, Z;
+          if (ph == 1) sign = -1;
+          if (ph == 0 || kind == 1)
+            gather_pair(p, a32, ph ? o1 : o0, ph ? c1 : c0, ph ? tdm0 : tb, ph ? tdm1 : ta, ph ? s.cv2 : s.cv,
+                        s.rowoff, s.A, lane, ga);
+          else {                                        // the flip's going edge: same pair, roles of u and v swapped
+            const u64 t = ga.inU; ga.inU = ga.inV; ga.inV = t;
+            const u64 t2 = ga.outU; ga.outU = ga.outV; ga.outV = t2;
           }
-        } else {
-          // double move: delme = tdm0->tdm1 leaves (counted in the graph before any edit), then
-          // tb->ta comes (counted in the final graph: delme's bit is cleared in between)
-          const u64 o2 = __ldg(&p.nb_off[delme >> 1]);
-          const int c2 = (int)(__ldg(&p.nb_off[(delme >> 1) + 1]) - o2);
-          const u64 o1 = __ldg(&p.nb_off[slot >> 1]);
-          const int c1 = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - o1);
-          if (c1 <= FAST_C && c2 <= FAST_C) {
-            gather_pair(p, c.adj, delme >> 1, tdm0, tdm1, s.cv2, s.A, lane, ga);
-            const P3 gone{ga.inU & ga.inV, ga.outU & ga.inV, ga.outU & ga.outV};
-            count_through_edge(gone, ga, s.A, lane, -1, cnt, s.deep, s.dflag);
-            tri = -(long long)popc3(gone);
-            set_adj_bit(p, c.adj, tdm0, tdm1, false, lane);
-            bit_cleared = true;
-            long long cntp[DELTA_SD];
-#pragma unroll
-            for (int k = 0; k < DELTA_SD; k++) cntp[k] = 0;
-            gather_pair(p, c.adj, slot >> 1, tb, ta, s.cv, s.A, lane, ga);
-            const P3 come{ga.inU & ga.inV, ga.outU & ga.inV, ga.outU & ga.outV};
-            count_through_edge(come, ga, s.A, lane, +1, cntp, s.deep, s.dflag);
-#pragma unroll
-            for (int k = 0; k < DELTA_SD; k++) { if (__any_sync(FULL, cntp[k] != 0)) top = k + 3; cnt[k] += cntp[k]; }
-            if (come.x | come.y | come.z) top = max(top, 2);
-            tri += (long long)popc3(come);
-            K = union_size(s.cv, c1, s.cv2, c2, ta, tb, tdm0, tdm1, lane);
-            top = max(top, 1);
-            done = true;
+          if (ph == 0 && kind == 1) {
+            // the double move's count of the coming edge sees the graph without delme: take that bit out
+            const int ip = tdm0 == tb ? -2 : tdm0 == ta ? -3 : list_index(s.cv, c0, tdm0, lane);
+            const int iq = tdm1 == tb ? -2 : tdm1 == ta ? -3 : list_index(s.cv, c0, tdm1, lane);
+            if (ip != -1 && iq != -1) {
+              if (ip >= 0 && iq >= 0) { if (lane == 0) s.A[ip] &= ~(1ULL << iq); __syncwarp(); }
+              else if (ip >= 0) { if (iq == -2) ga.inU &= ~(1ULL << ip); else ga.inV &= ~(1ULL << ip); }
+              else if (iq >= 0) { if (ip == -2) ga.outU &= ~(1ULL << iq); else ga.outV &= ~(1ULL << iq); }
+            }
+          }
+          X = ga.inU & ga.inV; Y = ga.outU & ga.inV; Z = ga.outU & ga.outV;
+          tri += sign * (__popcll(X) + __popcll(Y) + __popcll(Z));
+          if (ga.c <= 32) count_through_edge<u32>((u32)X, (u32)Y, (u32)Z, ga.c, s.A, lane, sign, cnt, s.deep, s.dflag);
+          else count_through_edge<u64>(X, Y, Z, ga.c, s.A, lane, sign, cnt, s.deep, s.dflag);
+          if (ph == 0) {
+            const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : (X | Y | Z) ? 2 : 1;
+            top = __reduce_max_sync(FULL, mytop);
           }
         }
-        if (done) {
-          fold_counts(cnt, tri, lane, delta);
+        long long delta = 0;
+#pragma unroll
+        for (int k = 0; k < DELTA_SD; k++) {
+          const int t = __reduce_add_sync(FULL, cnt[k]);
+          if (lane == k + 3) delta = t;
+        }
+        if (lane == 2) delta = tri;
+        __syncwarp();
+        if (__any_sync(FULL, s.dflag[0] != 0)) {       // some lane went below the register levels
+          if (s.dflag[2]) { err = s.dflag[2]; break; }
+          delta += (long long)s.deep[lane];
+          top = max(top, s.dflag[1]);
           __syncwarp();
-          if (__any_sync(FULL, s.dflag[0] != 0)) {     // some lane went below the static levels
-            if (s.dflag[2]) { err = s.dflag[2]; break; }
-            delta += (long long)s.deep[lane];
-            top = max(top, s.dflag[1]);
-            __syncwarp();
-            s.deep[lane] = 0;
-            if (lane < 3) s.dflag[lane] = 0;
-            __syncwarp();
-          }
-          fnew = fc + (u64)delta;
-          if (__any_sync(FULL, (long long)fnew < 0)) { err = FCM_EASSERT; break; }
-          prelen = 0;                                  // the reverted length never exceeds len (see header)
-          len = max(len, top + 1);
+          s.deep[lane] = 0;
+          if (lane < 3) s.dflag[lane] = 0;
+          __syncwarp();
         }
-      }
-      if (!done) {
-        int postlen = 0;
-        int rc = transition_counts(p, c, s, nedit, lane, K, prelen, postlen);
+        fnew = fc + (u64)delta;
+        if (__any_sync(FULL, (long long)fnew < 0)) { err = FCM_EASSERT; break; }
+        len = max(len, top + 1);
+        K = kind == 0 ? c0 + 2 : union_size(s.cv, c0, s.cv2, c1, ta, tb, tdm0, tdm1, lane);
+      } else {
+        if (lane == 0) {
+          if (kind == 0) { s.edits[0] = slot; s.edits[1] = 0; s.edits[2] = slot ^ 1; s.edits[3] = 1; }
+          else { s.edits[0] = slot ^ 1; s.edits[1] = 1; s.edits[2] = delme; s.edits[3] = 0; }
+        }
+        __syncwarp();
+        int prelen = 0, postlen = 0;
+        const int rc = transition_counts(p, c, s, 2, lane, K, prelen, postlen);
         if (rc) { err = rc; break; }
-        u64 pr = lane < min(prelen, len) ? s.pre[lane] : 0;
+        const u64 pr = lane < min(prelen, len) ? s.pre[lane] : 0;
         if (__any_sync(FULL, fc < pr)) { err = FCM_EASSERT; break; }
-        len = max(len, postlen);
+        len = max(len, max(postlen, prelen));
         fnew = fc - pr + (lane < postlen ? s.post[lane] : 0);
-      }
-      for (int e = 0; e < nedit; e++) {
-        if (s.edits[2 * e + 1]) c_add_edge(c, s.edits[2 * e], lane); else c_remove_edge(c, s.edits[2 * e], lane);
       }
       sumK += K;
       nonempty++;
-    } else {
-      // empty transition: pre = post = count of the empty graph (length 0), state unchanged
     }
-    sampled++;
+    // ---- Bounds::check, then keep or revert_transition (src/lib.rs:186-191, 81-95) ----
     const bool ok = bounds_ok(p, fnew, lane);
-    if (ok) {
-      accepted++;
-      if (nedit) {
-        for (int e = 0; e < nedit; e++) c_set_bit(p, c, s.edits[2 * e], s.edits[2 * e + 1] != 0, lane);
-        __syncwarp();
-        fc = fnew;
+    accepted += ok;
+    if (live) {
+      // The edge containers after apply (+ revert): both orders of events are replayed in closed form.
+      if (kind == 0) {
+        // remove slot (swap_remove: the last element moves into its hole), append slot^1; a revert
+        // appends slot again and removes slot^1: either way `fin` ends up last
+        const u32 fin = ok ? slot ^ 1 : slot;
+        if (lane == 0) {
+          c.items[idx] = last; c.pos[last] = idx;
+          c.pos[fin ^ 1] = FCM_NONE;
+          c.items[c.E - 1] = fin; c.pos[fin] = c.E - 1;
+          if (ok) { red_adj_bit(p, a32, ta, tb, false); red_adj_bit(p, a32, tb, ta, true); }
+        }
+      } else {
+        const u32 add = slot ^ 1, pairA = slot >> 1;
+        const u32 q = c.pos[delme];
+        if (ok) {
+          // append add (pairA turns double), swap_remove delme: add moves into delme's hole; dpair leaves
+          // the double set and pairA, just appended there, moves into its hole
+          if (lane == 0) {
+            c.items[q] = add; c.pos[add] = q; c.pos[delme] = FCM_NONE;
+            c.dbl[didx] = pairA; c.dblpos[pairA] = didx; c.dblpos[dpair] = FCM_NONE;
+            red_adj_bit(p, a32, tb, ta, true); red_adj_bit(p, a32, tdm0, tdm1, false);
+          }
+        } else {
+          // ... then the revert removes add again (the old last elements move into the holes) and
+          // appends delme / dpair at the ends
+          const u32 last0 = c.items[c.E - 1], lastd0 = c.dbl[c.ND - 1];
+          if (lane == 0) {
+            c.items[q] = last0; c.pos[last0] = q;
+            c.items[c.E - 1] = delme; c.pos[delme] = c.E - 1;
+            c.dbl[didx] = lastd0; c.dblpos[lastd0] = didx;
+            c.dbl[c.ND - 1] = dpair; c.dblpos[dpair] = c.ND - 1;
+          }
+        }
       }
-    } else if (nedit) {                                // revert_transition  src/lib.rs:81-95
-      for (int e = 0; e < nedit; e++) {
-        if (s.edits[2 * e + 1]) c_remove_edge(c, s.edits[2 * e], lane); else c_add_edge(c, s.edits[2 * e], lane);
-      }
-      if (bit_cleared) set_adj_bit(p, c.adj, tdm0, tdm1, true, lane);
-      len = max(len, prelen);
+      __syncwarp();
+      if (ok) fc = fnew;
     }
     if (tracing && lane == 0) {
       fcm_trace_rec tr;
-      tr.flags = (u32)kind | (ok ? FCM_TR_ACCEPT : 0u) | (nedit ? 0u : FCM_TR_EMPTY);
+      tr.flags = (u32)kind | (ok ? FCM_TR_ACCEPT : 0u) | (live ? 0u : FCM_TR_EMPTY);
       tr.a = ta; tr.b = tb; tr.dm0 = tdm0; tr.dm1 = tdm1; tr.K = (u32)K; tr.draws = 0; tr.pad = 0;
       trace[step] = tr;
     }
@@ -719,8 +691,8 @@ chain_step_kernel(const EnsParams p, u64 nsteps, fcm_trace_rec* __restrict__ tra
   st->flag_count[lane] = fc;
   if (lane == 0) {
     st->rng[0] = g.s0; st->rng[1] = g.s1; st->rng[2] = g.s2; st->rng[3] = g.s3;
-    st->E = c.E; st->ND = c.ND; st->fc_len = len;
-    st->sampled = sampled; st->accepted = accepted; st->sumK = sumK; st->nonempty = nonempty;
+    st->fc_len = len;
+    st->sampled += step; st->accepted += accepted; st->sumK += sumK; st->nonempty += nonempty;
     st->err = err;
   }
 }
@@ -826,9 +798,13 @@ int fcm_chain_launch_step(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev,
   size_t smem = e->smem_per_warp * wpb;
   FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   u32 blocks = (e->p.nchains + wpb - 1) / wpb;
-  chain_step_kernel<<<blocks, wpb * 32, smem, e->ctx->stream>>>(e->p, nsteps, trace_dev, trace_chain,
-                                                              (u32)e->smem_per_warp, e->force_full);
-  e->ctx->launches++;
+  const u64 chunk = 1ULL << 24;                         // the kernel's per-launch counters are 32-bit
+  for (u64 done = 0; done < nsteps; done += chunk) {
+    const u32 now = (u32)std::min<u64>(chunk, nsteps - done);
+    chain_step_kernel<<<blocks, wpb * 32, smem, e->ctx->stream>>>(e->p, now, trace_dev ? trace_dev + done : nullptr,
+                                                                trace_chain, (u32)e->smem_per_warp, e->force_full);
+    e->ctx->launches++;
+  }
   FCM_CUDA(cudaGetLastError());
   return FCM_OK;
 }
