@@ -130,7 +130,7 @@ __device__ bool build_nbhd(const EnsParams& p, const u32* edits, int nedit, u32*
     bool seen = false;
     for (int f = 0; f < e; f++) seen |= (edits[2 * f] >> 1) == pair;
     if (seen) continue;                                // same list, same endpoints: nothing new
-    const u64 o = p.nb_off[pair];
+    const u32 o = p.nb_off[pair];
     const int c = (int)(p.nb_off[pair + 1] - o);
     const int K0 = K;
     for (int base = 0; base < c; base += 32) {
@@ -254,39 +254,50 @@ __device__ int local_count_any(const u64* M, int K, int KW, int lane, u64* out, 
   }
 }
 
+// Per-warp shared memory.  The delta path's arrays sit at fixed offsets (the hot loop keeps one base
+// register); behind them one region serves either as the cp.async staging tile or as the full
+// path's arrays (a proposal takes one path or the other).
+#define FAST_C 64                      // longest common-neighbour list the delta path takes
+#define NARROW_C 32                    // staged gather: one column per lane
+#define TILE_WORDS 1024
+#define SM_A 0                         // u64[FAST_C + 4]  adjacency among the common neighbours
+#define SM_DEEP 544                    // u64[FCM_MAXD]    counts below the register levels, by flag_count index
+#define SM_ROWOFF 800                  // u32[64]          row offsets of the two lists
+#define SM_CV 1056                     // u32[64]          common neighbours of the coming pair
+#define SM_CV2 1312                    // u32[64]          ... of the going pair (double move)
+#define SM_FLAG 1568                   // int[12]          see FL_*
+#define SM_TILE 1616
+enum { FL_DEEP = 0, FL_TOP = 1, FL_ERR = 2, FL_RC = 3, FL_K = 4, FL_LEN = 5 };
 struct WarpSmem {
   u64 *M, *fc, *pre, *post;
   u32 *verts, *edits;
-  // delta path
-  u64 *A, *deep;                       // A[64+4]: adjacency among the common neighbours; deep[FCM_MAXD]
-  u32 *cv, *cv2, *rowoff;              // cv/cv2[64]: common-neighbour lists of the two pairs; rowoff[64]: their row offsets
-  int* dflag;                          // [0] deep counts used, [1] highest deep dimension of an added simplex, [2] error
+  u64 *A, *deep;
+  u32 *cv, *cv2, *rowoff;
+  int* dflag;
+  u32* tile;
 };
-#define FAST_C 64
 __host__ __device__ inline size_t warp_smem_bytes(u32 Kcap, u32 KWcap) {
   size_t full = (size_t)Kcap * KWcap * 8 + 3 * FCM_MAXD * 8 + (size_t)Kcap * 4 + FCM_MAXEDIT * 2 * 4;
-  full = (full + 7) & ~(size_t)7;
-  full = (full + 15) & ~(size_t)15;
-  return full + (FAST_C + 4) * 8 + FCM_MAXD * 8 + 3 * FAST_C * 4 + 16;
+  if (full < TILE_WORDS * 4) full = TILE_WORDS * 4;
+  return SM_TILE + full;
 }
 size_t fcm_chain_smem_per_warp(u32 Kcap, u32 KWcap) { return (warp_smem_bytes(Kcap, KWcap) + 15) & ~(size_t)15; }
 
 __device__ __forceinline__ WarpSmem carve(unsigned char* base, u32 Kcap, u32 KWcap) {
   WarpSmem s;
-  s.M = (u64*)base;
+  s.A = (u64*)(base + SM_A);
+  s.deep = (u64*)(base + SM_DEEP);
+  s.rowoff = (u32*)(base + SM_ROWOFF);
+  s.cv = (u32*)(base + SM_CV);
+  s.cv2 = (u32*)(base + SM_CV2);
+  s.dflag = (int*)(base + SM_FLAG);
+  s.tile = (u32*)(base + SM_TILE);
+  s.M = (u64*)(base + SM_TILE);
   s.fc = s.M + (size_t)Kcap * KWcap;
   s.pre = s.fc + FCM_MAXD;
   s.post = s.pre + FCM_MAXD;
   s.verts = (u32*)(s.post + FCM_MAXD);
   s.edits = s.verts + Kcap;
-  size_t off = (size_t)((unsigned char*)(s.edits + FCM_MAXEDIT * 2) - base);
-  off = (off + 15) & ~(size_t)15;
-  s.A = (u64*)(base + off);
-  s.deep = s.A + FAST_C + 4;
-  s.rowoff = (u32*)(s.deep + FCM_MAXD);                // 16-byte aligned: read four at a time
-  s.cv = s.rowoff + FAST_C;
-  s.cv2 = s.cv + FAST_C;
-  s.dflag = (int*)(s.cv2 + FAST_C);
   return s;
 }
 
@@ -328,7 +339,7 @@ __device__ __forceinline__ int low_m(u64 x) { return __ffsll((long long)x) - 1; 
 //   list[j] = C[j];  A[i] = { j : C[i] -> C[j] };  in*/out* = { j : C[j] -> u|v } / { j : u|v -> C[j] }
 // The caller has checked c <= FAST_C.
 struct Gathered { int c; u64 inU, outU, inV, outV; };
-__device__ __forceinline__ void gather_pair(const EnsParams& p, const u32* a32, u64 o, int c, u32 u, u32 v,
+__device__ __forceinline__ void gather_pair(const EnsParams& p, const u32* a32, u32 o, int c, u32 u, u32 v,
                                             u32* list, u32* rowoff, u64* A, int lane, Gathered& g) {
   const u32 W32 = 2 * p.W;
   const int ncs = (c + 31) >> 5;                        // column slots: lanes hold C[lane], C[lane + 32]
@@ -492,33 +503,185 @@ __device__ __forceinline__ void red_adj_bit(const EnsParams& p, u32* a32, u32 fr
   if (add) atomicOr(w, m); else atomicAnd(w, ~m);
 }
 
+// ---- staged gather for lists of <= 32 common neighbours (one column per lane) -----------------------
+// All row words of the pair are requested at once with cp.async (no registers held, one memory
+// round trip for the whole gather) into the warp's tile: word (i, lane) = row C[i], the 32-bit word
+// holding column C[lane].  stage_issue only issues; stage_finish turns the tile into bit rows.
+__device__ __forceinline__ void cp_async4(u32 saddr, const void* g) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(saddr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+struct Narrow { u32 m, lu, lv, xu, xv; };               // this lane's column mask and relation words
+// x = C[lane] (0 beyond c).  rowoff[0..32) and list[0..32) are this pair's.
+__device__ __forceinline__ void stage_issue(const EnsParams& p, const u32* a32, u32 x, int c, u32 u, u32 v,
+                                            u32* list, u32* rowoff, u32* tile, int lane, Narrow& nb) {
+  const u32 W32 = 2 * p.W;
+  list[lane] = x;
+  rowoff[lane] = x * W32;                               // rows past c: offset 0, copied but never read
+  __syncwarp();
+  const u32 w = x >> 5;
+  nb.m = lane < c ? 1u << (x & 31) : 0u;
+  const u32* rx = a32 + x * W32;
+  nb.lu = a32[u * W32 + w]; nb.lv = a32[v * W32 + w];
+  nb.xu = rx[u >> 5]; nb.xv = rx[v >> 5];
+  if (lane < c) {
+    u32 dst = (u32)__cvta_generic_to_shared(tile + lane);
+    const u32* src = a32 + w;
+    const u32 pitch = 4u * (u32)c;
+    const int cpad = (c + 3) & ~3;
+#pragma unroll 1
+    for (int i0 = 0; i0 < cpad; i0 += 4) {
+      const uint4 ro = *(const uint4*)&rowoff[i0];
+      cp_async4(dst, src + ro.x); dst += pitch;
+      cp_async4(dst, src + ro.y); dst += pitch;
+      cp_async4(dst, src + ro.z); dst += pitch;
+      cp_async4(dst, src + ro.w); dst += pitch;
+    }
+  }
+  cp_async_commit();
+}
+__device__ __forceinline__ void stage_finish(const u32* tile, int c, const Narrow& nb, u32 u, u32 v, u64* A, int lane,
+                                             Gathered& g) {
+  const u32* col = tile + min(lane, max(c - 1, 0));     // idle lanes re-read a valid word; their mask is 0
+  u32 row = 0;
+  const int c4 = c & ~3;
+  int i = 0;
+#pragma unroll 1
+  for (; i < c4; i += 4) {
+    const u32 t0 = col[i * c], t1 = col[(i + 1) * c], t2 = col[(i + 2) * c], t3 = col[(i + 3) * c];
+    const u32 b0 = __ballot_sync(FULL, t0 & nb.m), b1 = __ballot_sync(FULL, t1 & nb.m);
+    const u32 b2 = __ballot_sync(FULL, t2 & nb.m), b3 = __ballot_sync(FULL, t3 & nb.m);
+    const int d = lane - i;
+    if ((u32)d < 4u) row = d == 0 ? b0 : d == 1 ? b1 : d == 2 ? b2 : b3;
+  }
+  for (; i < c; i++) {
+    const u32 b = __ballot_sync(FULL, col[i * c] & nb.m);
+    if (lane == i) row = b;
+  }
+  A[lane] = row;
+  g.c = c;
+  g.outU = __ballot_sync(FULL, nb.lu & nb.m);
+  g.outV = __ballot_sync(FULL, nb.lv & nb.m);
+  g.inU = __ballot_sync(FULL, nb.m && ((nb.xu >> (u & 31)) & 1u));
+  g.inV = __ballot_sync(FULL, nb.m && ((nb.xv >> (v & 31)) & 1u));
+  __syncwarp();
+}
+
+// the double move's count of the coming edge u->v sees the graph without delme = d0->d1: take that bit
+// out of the gathered view (list/A/ga are the coming pair's)
+__device__ __forceinline__ void drop_edge_from_view(const u32* list, int c, u32 u, u32 v, u32 d0, u32 d1, u64* A,
+                                                    int lane, Gathered& ga) {
+  const int ip = d0 == u ? -2 : d0 == v ? -3 : list_index(list, c, d0, lane);
+  const int iq = d1 == u ? -2 : d1 == v ? -3 : list_index(list, c, d1, lane);
+  if (ip == -1 || iq == -1) return;
+  if (ip >= 0 && iq >= 0) { if (lane == 0) A[ip] &= ~(1ULL << iq); __syncwarp(); }
+  else if (ip >= 0) { if (iq == -2) ga.inU &= ~(1ULL << ip); else ga.inV &= ~(1ULL << ip); }
+  else if (iq >= 0) { if (ip == -2) ga.outU &= ~(1ULL << iq); else ga.outV &= ~(1ULL << iq); }
+}
+
+// Delta of a proposal whose lists need two column slots (32 < c <= 64): register gathers, one pair
+// after the other.  Cold path: the warp totals go to deep[] / dflag[] like the counts of the deep
+// levels (the caller folds them in), K to dflag[FL_K].
+__device__ __noinline__ void delta_wide(const EnsParams& p, const u32* a32, unsigned char* wb, int kind, u32 ta, u32 tb,
+                                        u32 tdm0, u32 tdm1, u32 o0, int c0, u32 o1, int c1, int lane) {
+  const WarpSmem s = carve(wb, p.Kcap, p.KWcap);
+  int cnt[DELTA_SD];
+#pragma unroll
+  for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
+  int tri = 0, top = 1;
+  Gathered ga;
+#pragma unroll 1
+  for (int ph = 0; ph < 2; ph++) {
+    const int sign = ph ? -1 : 1;
+    if (ph == 0 || kind == 1)
+      gather_pair(p, a32, ph ? o1 : o0, ph ? c1 : c0, ph ? tdm0 : tb, ph ? tdm1 : ta, ph ? s.cv2 : s.cv, s.rowoff, s.A, lane, ga);
+    else {                                              // the flip's going edge: same pair, roles of u and v swapped
+      const u64 t = ga.inU; ga.inU = ga.inV; ga.inV = t;
+      const u64 t2 = ga.outU; ga.outU = ga.outV; ga.outV = t2;
+    }
+    if (ph == 0 && kind == 1) drop_edge_from_view(s.cv, c0, tb, ta, tdm0, tdm1, s.A, lane, ga);
+    const u64 X = ga.inU & ga.inV, Y = ga.outU & ga.inV, Z = ga.outU & ga.outV;
+    tri += sign * (__popcll(X) + __popcll(Y) + __popcll(Z));
+    count_through_edge<u64>(X, Y, Z, ga.c, s.A, lane, sign, cnt, s.deep, s.dflag);
+    if (ph == 0) {
+      const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : (X | Y | Z) ? 2 : 1;
+      top = __reduce_max_sync(FULL, mytop);
+    }
+    __syncwarp();
+  }
+  const int K = kind == 0 ? c0 + 2 : union_size(s.cv, c0, s.cv2, c1, ta, tb, tdm0, tdm1, lane);
+#pragma unroll
+  for (int k = 0; k < DELTA_SD; k++) {
+    const int t = __reduce_add_sync(FULL, cnt[k]);
+    if (lane == 0) s.deep[k + 3] += (u64)(long long)t;
+  }
+  if (lane == 0) {
+    s.deep[2] += (u64)(long long)tri;
+    s.dflag[FL_DEEP] = 1;
+    s.dflag[FL_TOP] = max(s.dflag[FL_TOP], top);
+    s.dflag[FL_K] = K;
+  }
+  __syncwarp();
+}
+
+// Full pre/post counts of the neighbourhood graph (lists longer than FAST_C, or forced): returns this
+// lane's new flag_count entry; dflag[FL_RC] = status, dflag[FL_K] = |nbhd|, dflag[FL_LEN] = new length.
+__device__ __noinline__ u64 full_path(const EnsParams& p, u32* cb, unsigned char* wb, u32 slot0, u32 add0, u32 slot1,
+                                      u32 add1, u64 fc, int len, int lane) {
+  const WarpSmem s = carve(wb, p.Kcap, p.KWcap);
+  Chain c;
+  c.adj = (u64*)cb; c.items = cb + p.off_items; c.pos = cb + p.off_pos; c.dbl = cb + p.off_dbl; c.dblpos = cb + p.off_dblpos;
+  c.E = 0; c.ND = 0;
+  if (lane == 0) { s.edits[0] = slot0; s.edits[1] = add0; s.edits[2] = slot1; s.edits[3] = add1; }
+  __syncwarp();
+  int K = 0, prelen = 0, postlen = 0;
+  int rc = transition_counts(p, c, s, 2, lane, K, prelen, postlen);
+  u64 fnew = fc;
+  if (!rc) {
+    const u64 pr = lane < min(prelen, len) ? s.pre[lane] : 0;
+    if (__any_sync(FULL, fc < pr)) rc = FCM_EASSERT;
+    else fnew = fc - pr + (lane < postlen ? s.post[lane] : 0);
+  }
+  if (lane == 0) { s.dflag[FL_RC] = rc; s.dflag[FL_K] = K; s.dflag[FL_LEN] = max(len, max(postlen, prelen)); }
+  __syncwarp();
+  return fnew;
+}
+
 __global__ void __launch_bounds__(128, 7)
-chain_step_kernel(const EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ trace, u32 trace_chain,
+chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ trace, u32 trace_chain,
                   u32 smem_per_warp, int force_full) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  const u32 chain = blockIdx.x * (blockDim.x >> 5) + wib;
+  const int lane = threadIdx.x & 31;
+  const u32 chain = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (chain >= p.nchains) return;
-  WarpSmem s = carve(smem_raw + (size_t)wib * smem_per_warp, p.Kcap, p.KWcap);
-  ChainState* st = &p.st[chain];
+  unsigned char* const wb = smem_raw + (size_t)(threadIdx.x >> 5) * smem_per_warp;
+  u64* const sA = (u64*)(wb + SM_A);
+  u64* const sdeep = (u64*)(wb + SM_DEEP);
+  u32* const srowoff = (u32*)(wb + SM_ROWOFF);
+  u32* const scv = (u32*)(wb + SM_CV);
+  u32* const scv2 = (u32*)(wb + SM_CV2);
+  int* const sflag = (int*)(wb + SM_FLAG);
+  u32* const stile = (u32*)(wb + SM_TILE);
+  ChainState* const st = &p.st[chain];
   if (st->err) return;
-  Chain c;
-  const u64 nslots = 2 * p.npairs;
-  c.adj = p.adj + (u64)chain * p.n * p.W;
-  c.items = p.items + (u64)chain * nslots;
-  c.pos = p.pos + (u64)chain * nslots;
-  c.dbl = p.dbl + (u64)chain * p.npairs;
-  c.dblpos = p.dblpos + (u64)chain * p.npairs;
-  c.E = st->E; c.ND = st->ND;
-  u32* const a32 = (u32*)c.adj;
+  // the chain's block: adjacency rows (as 32-bit words) | items | pos | dbl | dblpos
+  u32* const cb = (u32*)p.adj + (u64)chain * p.stride32;
+#define ITEMS(i) cb[p.off_items + (i)]
+#define POS(i) cb[p.off_pos + (i)]
+#define DBL(i) cb[p.off_dbl + (i)]
+#define DBLPOS(i) cb[p.off_dblpos + (i)]
+  const u32 E = st->E, ND = st->ND;                    // both moves keep |E| and the number of double pairs
+  const u32 W32 = 2 * p.W;
   Rng g{st->rng[0], st->rng[1], st->rng[2], st->rng[3]};
   u64 fc = st->flag_count[lane];                       // lane d owns flag_count[d]
   int len = st->fc_len;
   u32 accepted = 0, sumK = 0, nonempty = 0;            // per launch (nsteps <= 2^24: the host splits longer runs)
   int err = 0;
-  const bool tracing = trace != nullptr && chain == trace_chain;
-  s.deep[lane] = 0;
-  if (lane < 3) s.dflag[lane] = 0;
+  sdeep[lane] = 0;
+  if (lane < 12) sflag[lane] = 0;
   __syncwarp();
 
   u32 step = 0;
@@ -529,78 +692,113 @@ chain_step_kernel(const EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ tra
     const double chosen = __dadd_rn(__dmul_rn(v, p.scale), 0.0);
     const int kind = (p.cum[0] <= chosen) + (p.cum[1] <= chosen) + (p.cum[2] <= chosen);
     if (kind > 1) { err = FCM_EUNSUPPORTED; break; }
-    // ---- single_edge_flip (src/lib.rs:292-299) / double_edge_move (:304-325): the draws ----
+    // ---- single_edge_flip (src/lib.rs:292-299) / double_edge_move (:304-325): the draws.  Loads are
+    //      written in the order they become issuable so that independent ones overlap. ----
     bool live = false;                                  // a non-empty transition
-    u32 idx = 0, slot = 0, didx = 0, dpair = 0, delme = 0, last = 0;
+    bool sampled_edge = false;
+    u32 idx = 0, slot = 0, didx = 0, dpair = 0, delme = 0, last = 0, qpos = 0;
+    u32 oA = 0, oD = 0;
+    int cA = 0, cD = 0;
+    uint2 abA = make_uint2(0, 0), abD = make_uint2(0, 0);
     if (kind == 0) {
-      if (c.E) {
-        idx = (u32)gen_range(g, c.E);
-        slot = c.items[idx];
-        last = c.items[c.E - 1];
-        live = c.pos[slot ^ 1] == FCM_NONE;             // the reverse edge exists: empty transition
+      if (E) {
+        idx = (u32)gen_range(g, E);
+        slot = ITEMS(idx);
+        last = ITEMS(E - 1);
+        const u32 rev = POS(slot ^ 1);
+        abA = __ldg(&p.pair_ab[slot >> 1]);
+        oA = __ldg(&p.nb_off[slot >> 1]);
+        cA = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - oA);
+        live = rev == FCM_NONE;                         // the reverse edge exists: empty transition
+        sampled_edge = true;
       }
-    } else if (c.ND) {
-      if (2ULL * c.ND >= c.E) { err = FCM_EINVAL; break; }     // reference spins forever (FIXME :307)
-      didx = (u32)gen_range(g, c.ND);
-      dpair = c.dbl[didx];
-      do {
-        idx = (u32)gen_range(g, c.E);
-        slot = c.items[idx];
-      } while (c.pos[slot ^ 1] != FCM_NONE);
+    } else if (ND) {
+      if (2ULL * ND >= E) { err = FCM_EINVAL; break; }         // reference spins forever (FIXME :307)
+      didx = (u32)gen_range(g, ND);
+      idx = (u32)gen_range(g, E);                       // the next draw does not depend on the loaded pair
+      dpair = DBL(didx);
+      slot = ITEMS(idx);
+      abD = __ldg(&p.pair_ab[dpair]);
+      oD = __ldg(&p.nb_off[dpair]);
+      cD = (int)(__ldg(&p.nb_off[dpair + 1]) - oD);
+      for (;;) {
+        const u32 rev = POS(slot ^ 1);
+        abA = __ldg(&p.pair_ab[slot >> 1]);
+        oA = __ldg(&p.nb_off[slot >> 1]);
+        cA = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - oA);
+        if (rev == FCM_NONE) break;
+        idx = (u32)gen_range(g, E);
+        slot = ITEMS(idx);
+      }
       const bool first = g.next() < 0x8000000000000000ULL;     // gen_bool(0.5)
       delme = 2 * dpair + (first ? 1u : 0u);                   // first: [min,max] = small -> big
+      qpos = POS(delme);                                       // needed when the containers are updated
       live = true;
+      sampled_edge = true;
     }
+    // (ta,tb) = the sampled single edge, (tdm0,tdm1) = delme; dir 0 of a slot = big -> small
     u32 ta = 0, tb = 0, tdm0 = 0, tdm1 = 0;
-    if (kind == 0 ? c.E != 0 : live) { const uint2 ft = slot_edge(p, slot); ta = ft.x; tb = ft.y; }
-    if (kind == 1 && live) { const uint2 dm = slot_edge(p, delme); tdm0 = dm.x; tdm1 = dm.y; }
+    if (sampled_edge) { ta = (slot & 1) ? abA.y : abA.x; tb = (slot & 1) ? abA.x : abA.y; }
+    if (kind == 1 && live) { tdm0 = (delme & 1) ? abD.y : abD.x; tdm1 = (delme & 1) ? abD.x : abD.y; }
 
     // ---- State::apply_transition  src/lib.rs:61-79: flag_count += post - pre ----
     int K = 0;
     u64 fnew = fc;
+    // the edge that comes is tb->ta for both moves; the edge that goes is ta->tb (flip) or delme
+    const u32 gu = kind == 0 ? ta : tdm0, gv = kind == 0 ? tb : tdm1;
+    const u32 igo = gu * W32 + (gv >> 5), icome = tb * W32 + (ta >> 5);
+    u32 vgo = 0, vcome = 0;
     if (live) {
-      // phase 0 = the edge that comes (flip: tb->ta; double move: tb->ta as well), phase 1 = the edge
-      // that goes (flip: ta->tb, same pair; double move: delme = tdm0->tdm1)
-      const u32 pair0 = slot >> 1, pair1 = kind == 0 ? pair0 : (delme >> 1);
-      const u64 o0 = __ldg(&p.nb_off[pair0]), o1 = __ldg(&p.nb_off[pair1]);
-      const int c0 = (int)(__ldg(&p.nb_off[pair0 + 1]) - o0), c1 = (int)(__ldg(&p.nb_off[pair1 + 1]) - o1);
-      if (!force_full && c0 <= FAST_C && c1 <= FAST_C) {
-        int cnt[DELTA_SD];
+      vgo = cb[igo]; vcome = cb[icome];                 // early: rewritten on accept without a stall
+      int cnt[DELTA_SD];
 #pragma unroll
-        for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
-        int tri = 0, top = 1;
+      for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
+      int tri = 0, top = 1;
+      const int cB = kind == 0 ? 0 : cD;
+      const int tileA_words = ((cA + 3) & ~3) * cA;
+      if (!force_full && cA <= NARROW_C && cB <= NARROW_C && tileA_words + ((cB + 3) & ~3) * cB <= TILE_WORDS) {
+        // hot path: both gathers are in flight together
+        const u32 xA = lane < cA ? __ldg(&p.nb_list[oA + lane]) : 0u;
+        const u32 xD = lane < cB ? __ldg(&p.nb_list[oD + lane]) : 0u;
+        Narrow nA, nD;
+        stage_issue(p, cb, xA, cA, tb, ta, scv, srowoff, stile, lane, nA);
+        if (kind == 1) stage_issue(p, cb, xD, cD, tdm0, tdm1, scv2, srowoff + 32, stile + tileA_words, lane, nD);
         Gathered ga;
 #pragma unroll 1
         for (int ph = 0; ph < 2; ph++) {
-          int sign = 1;
-          u64 X, Y, Z;
-          if (ph == 1) sign = -1;
-          if (ph == 0 || kind == 1)
-            gather_pair(p, a32, ph ? o1 : o0, ph ? c1 : c0, ph ? tdm0 : tb, ph ? tdm1 : ta, ph ? s.cv2 : s.cv,
-                        s.rowoff, s.A, lane, ga);
-          else {                                        // the flip's going edge: same pair, roles of u and v swapped
+          const int sign = ph ? -1 : 1;
+          if (ph == 0 || kind == 1) {
+            if (ph == 0 && kind == 1) cp_async_wait<1>(); else cp_async_wait<0>();
+            __syncwarp();
+            if (ph == 0) stage_finish(stile, cA, nA, tb, ta, sA, lane, ga);
+            else stage_finish(stile + tileA_words, cD, nD, tdm0, tdm1, sA, lane, ga);
+            if (ph == 0 && kind == 1) drop_edge_from_view(scv, cA, tb, ta, tdm0, tdm1, sA, lane, ga);
+          } else {                                      // the flip's going edge: same pair, roles of u and v swapped
             const u64 t = ga.inU; ga.inU = ga.inV; ga.inV = t;
             const u64 t2 = ga.outU; ga.outU = ga.outV; ga.outV = t2;
           }
-          if (ph == 0 && kind == 1) {
-            // the double move's count of the coming edge sees the graph without delme: take that bit out
-            const int ip = tdm0 == tb ? -2 : tdm0 == ta ? -3 : list_index(s.cv, c0, tdm0, lane);
-            const int iq = tdm1 == tb ? -2 : tdm1 == ta ? -3 : list_index(s.cv, c0, tdm1, lane);
-            if (ip != -1 && iq != -1) {
-              if (ip >= 0 && iq >= 0) { if (lane == 0) s.A[ip] &= ~(1ULL << iq); __syncwarp(); }
-              else if (ip >= 0) { if (iq == -2) ga.inU &= ~(1ULL << ip); else ga.inV &= ~(1ULL << ip); }
-              else if (iq >= 0) { if (ip == -2) ga.outU &= ~(1ULL << iq); else ga.outV &= ~(1ULL << iq); }
-            }
-          }
-          X = ga.inU & ga.inV; Y = ga.outU & ga.inV; Z = ga.outU & ga.outV;
-          tri += sign * (__popcll(X) + __popcll(Y) + __popcll(Z));
-          if (ga.c <= 32) count_through_edge<u32>((u32)X, (u32)Y, (u32)Z, ga.c, s.A, lane, sign, cnt, s.deep, s.dflag);
-          else count_through_edge<u64>(X, Y, Z, ga.c, s.A, lane, sign, cnt, s.deep, s.dflag);
+          const u32 X = (u32)(ga.inU & ga.inV), Y = (u32)(ga.outU & ga.inV), Z = (u32)(ga.outU & ga.outV);
+          tri += sign * (__popc(X) + __popc(Y) + __popc(Z));
+          count_through_edge<u32>(X, Y, Z, ga.c, sA, lane, sign, cnt, sdeep, sflag);
           if (ph == 0) {
             const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : (X | Y | Z) ? 2 : 1;
             top = __reduce_max_sync(FULL, mytop);
           }
+          __syncwarp();
         }
+        K = kind == 0 ? cA + 2 : union_size(scv, cA, scv2, cD, ta, tb, tdm0, tdm1, lane);
+      } else if (!force_full && cA <= FAST_C && cB <= FAST_C) {
+        delta_wide(p, cb, wb, kind, ta, tb, tdm0, tdm1, oA, cA, oD, cD, lane);
+        K = sflag[FL_K];
+      } else {
+        const u32 s0 = kind == 0 ? slot : slot ^ 1, s1 = kind == 0 ? slot ^ 1 : delme;
+        fnew = full_path(p, cb, wb, s0, kind == 0 ? 0u : 1u, s1, kind == 0 ? 1u : 0u, fc, len, lane);
+        if (sflag[FL_RC]) { err = sflag[FL_RC]; break; }
+        K = sflag[FL_K];
+        len = sflag[FL_LEN];
+        top = -1;                                       // flag_count is already new
+      }
+      if (top >= 0) {
         long long delta = 0;
 #pragma unroll
         for (int k = 0; k < DELTA_SD; k++) {
@@ -608,33 +806,18 @@ chain_step_kernel(const EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ tra
           if (lane == k + 3) delta = t;
         }
         if (lane == 2) delta = tri;
-        __syncwarp();
-        if (__any_sync(FULL, s.dflag[0] != 0)) {       // some lane went below the register levels
-          if (s.dflag[2]) { err = s.dflag[2]; break; }
-          delta += (long long)s.deep[lane];
-          top = max(top, s.dflag[1]);
+        if (__any_sync(FULL, sflag[FL_DEEP] != 0)) {   // counts below the register levels (or the wide path's)
+          if (sflag[FL_ERR]) { err = sflag[FL_ERR]; break; }
+          delta += (long long)sdeep[lane];
+          top = max(top, sflag[FL_TOP]);
           __syncwarp();
-          s.deep[lane] = 0;
-          if (lane < 3) s.dflag[lane] = 0;
+          sdeep[lane] = 0;
+          if (lane < 3) sflag[lane] = 0;
           __syncwarp();
         }
         fnew = fc + (u64)delta;
         if (__any_sync(FULL, (long long)fnew < 0)) { err = FCM_EASSERT; break; }
         len = max(len, top + 1);
-        K = kind == 0 ? c0 + 2 : union_size(s.cv, c0, s.cv2, c1, ta, tb, tdm0, tdm1, lane);
-      } else {
-        if (lane == 0) {
-          if (kind == 0) { s.edits[0] = slot; s.edits[1] = 0; s.edits[2] = slot ^ 1; s.edits[3] = 1; }
-          else { s.edits[0] = slot ^ 1; s.edits[1] = 1; s.edits[2] = delme; s.edits[3] = 0; }
-        }
-        __syncwarp();
-        int prelen = 0, postlen = 0;
-        const int rc = transition_counts(p, c, s, 2, lane, K, prelen, postlen);
-        if (rc) { err = rc; break; }
-        const u64 pr = lane < min(prelen, len) ? s.pre[lane] : 0;
-        if (__any_sync(FULL, fc < pr)) { err = FCM_EASSERT; break; }
-        len = max(len, max(postlen, prelen));
-        fnew = fc - pr + (lane < postlen ? s.post[lane] : 0);
       }
       sumK += K;
       nonempty++;
@@ -649,44 +832,54 @@ chain_step_kernel(const EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ tra
         // appends slot again and removes slot^1: either way `fin` ends up last
         const u32 fin = ok ? slot ^ 1 : slot;
         if (lane == 0) {
-          c.items[idx] = last; c.pos[last] = idx;
-          c.pos[fin ^ 1] = FCM_NONE;
-          c.items[c.E - 1] = fin; c.pos[fin] = c.E - 1;
-          if (ok) { red_adj_bit(p, a32, ta, tb, false); red_adj_bit(p, a32, tb, ta, true); }
+          ITEMS(idx) = last; POS(last) = idx;
+          POS(fin ^ 1) = FCM_NONE;
+          ITEMS(E - 1) = fin; POS(fin) = E - 1;
         }
       } else {
         const u32 add = slot ^ 1, pairA = slot >> 1;
-        const u32 q = c.pos[delme];
         if (ok) {
           // append add (pairA turns double), swap_remove delme: add moves into delme's hole; dpair leaves
           // the double set and pairA, just appended there, moves into its hole
           if (lane == 0) {
-            c.items[q] = add; c.pos[add] = q; c.pos[delme] = FCM_NONE;
-            c.dbl[didx] = pairA; c.dblpos[pairA] = didx; c.dblpos[dpair] = FCM_NONE;
-            red_adj_bit(p, a32, tb, ta, true); red_adj_bit(p, a32, tdm0, tdm1, false);
+            ITEMS(qpos) = add; POS(add) = qpos; POS(delme) = FCM_NONE;
+            DBL(didx) = pairA; DBLPOS(pairA) = didx; DBLPOS(dpair) = FCM_NONE;
           }
         } else {
           // ... then the revert removes add again (the old last elements move into the holes) and
           // appends delme / dpair at the ends
-          const u32 last0 = c.items[c.E - 1], lastd0 = c.dbl[c.ND - 1];
+          const u32 last0 = ITEMS(E - 1), lastd0 = DBL(ND - 1);
           if (lane == 0) {
-            c.items[q] = last0; c.pos[last0] = q;
-            c.items[c.E - 1] = delme; c.pos[delme] = c.E - 1;
-            c.dbl[didx] = lastd0; c.dblpos[lastd0] = didx;
-            c.dbl[c.ND - 1] = dpair; c.dblpos[dpair] = c.ND - 1;
+            ITEMS(qpos) = last0; POS(last0) = qpos;
+            ITEMS(E - 1) = delme; POS(delme) = E - 1;
+            DBL(didx) = lastd0; DBLPOS(lastd0) = didx;
+            DBL(ND - 1) = dpair; DBLPOS(dpair) = ND - 1;
           }
         }
       }
+      if (ok) {
+        // adjacency bits: gu->gv leaves, tb->ta comes (plain stores of the words read above: the
+        // rows are read through this SM's L1, which its own stores keep coherent)
+        if (lane == 0) {
+          const u32 mgo = 1u << (gv & 31), mcome = 1u << (ta & 31);
+          if (igo == icome) cb[igo] = (vgo & ~mgo) | mcome;
+          else { cb[igo] = vgo & ~mgo; cb[icome] = vcome | mcome; }
+        }
+        fc = fnew;
+      }
       __syncwarp();
-      if (ok) fc = fnew;
     }
-    if (tracing && lane == 0) {
+    if (trace != nullptr && chain == trace_chain && lane == 0) {
       fcm_trace_rec tr;
       tr.flags = (u32)kind | (ok ? FCM_TR_ACCEPT : 0u) | (live ? 0u : FCM_TR_EMPTY);
       tr.a = ta; tr.b = tb; tr.dm0 = tdm0; tr.dm1 = tdm1; tr.K = (u32)K; tr.draws = 0; tr.pad = 0;
       trace[step] = tr;
     }
   }
+#undef ITEMS
+#undef POS
+#undef DBL
+#undef DBLPOS
   __syncwarp();
   st->flag_count[lane] = fc;
   if (lane == 0) {
@@ -707,11 +900,11 @@ __global__ void chain_apply_kernel(const EnsParams p, u32 chain, const u32* __re
   ChainState* st = &p.st[chain];
   Chain c;
   const u64 nslots = 2 * p.npairs;
-  c.adj = p.adj + (u64)chain * p.n * p.W;
-  c.items = p.items + (u64)chain * nslots;
-  c.pos = p.pos + (u64)chain * nslots;
-  c.dbl = p.dbl + (u64)chain * p.npairs;
-  c.dblpos = p.dblpos + (u64)chain * p.npairs;
+  c.adj = (u64*)((u32*)p.adj + (u64)chain * p.stride32);
+  c.items = p.items + (u64)chain * p.stride32;
+  c.pos = p.pos + (u64)chain * p.stride32;
+  c.dbl = p.dbl + (u64)chain * p.stride32;
+  c.dblpos = p.dblpos + (u64)chain * p.stride32;
   c.E = st->E; c.ND = st->ND;
   u64 fc = st->flag_count[lane];
   int len = st->fc_len;
@@ -779,16 +972,10 @@ int fcm_chain_launch_replicate(fcm_ensemble* e) {
   const EnsParams& p = e->p;
   cudaStream_t s = e->ctx->stream;
   if (p.nchains <= 1) return FCM_OK;
-  auto blocks = [&](u64 cnt) { return (int)std::min<u64>((cnt + 255) / 256, (u64)e->ctx->sm_count * 8); };
-  u64 nslots = 2 * p.npairs;
-  if ((u64)p.n * p.W) { replicate_kernel<u64><<<blocks((u64)p.n * p.W), 256, 0, s>>>(p.adj, (u64)p.n * p.W, p.nchains); e->ctx->launches++; }
-  if (nslots) {
-    replicate_kernel<u32><<<blocks(nslots), 256, 0, s>>>(p.items, nslots, p.nchains);
-    replicate_kernel<u32><<<blocks(nslots), 256, 0, s>>>(p.pos, nslots, p.nchains);
-    replicate_kernel<u32><<<blocks(p.npairs), 256, 0, s>>>(p.dbl, p.npairs, p.nchains);
-    replicate_kernel<u32><<<blocks(p.npairs), 256, 0, s>>>(p.dblpos, p.npairs, p.nchains);
-    e->ctx->launches += 4;
-  }
+  const u64 words = p.stride32;                         // chain 0's block -> every other chain's
+  int blocks = (int)std::min<u64>((words + 255) / 256, (u64)e->ctx->sm_count * 8);
+  replicate_kernel<u32><<<blocks, 256, 0, s>>>((u32*)p.adj, words, p.nchains);
+  e->ctx->launches++;
   FCM_CUDA(cudaGetLastError());
   return FCM_OK;
 }

@@ -146,7 +146,7 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     for (int t = 0; t < nthreads; t++) th.emplace_back([&, t]() { for (u32 v = t; v < n; v += nthreads) std::sort(und[v].begin(), und[v].end()); });
     for (auto& t : th) t.join();
   }
-  std::vector<u64> nb_off(p.npairs + 1, 0);
+  std::vector<u64> nb_off(p.npairs + 1, 0);   // 64-bit while summing; uploaded as u32
   auto intersect = [&](u32 a, u32 b, u32* outp) -> u32 {
     const std::vector<u32>&A = und[a], &B = und[b];
     size_t i = 0, j = 0; u32 c = 0;
@@ -182,16 +182,25 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   // ---- device memory ----
   const u64 nslots = 2 * p.npairs;
   const u64 adjw = (u64)n * p.W;
-  e->bytes_per_chain = adjw * 8 + nslots * 8 + p.npairs * 8 + sizeof(ChainState);
-  uint2* d_pair; u64* d_off; u32* d_list;
+  e->bytes_per_chain = adjw * 8 + nslots * 8 + p.npairs * 8 + sizeof(ChainState);   // before padding
+  uint2* d_pair; u32* d_off; u32* d_list;
+  if (nb_off[p.npairs] > 0xffffffffULL) { fcm_set_error("common-neighbour lists hold %llu entries (> 2^32)", (unsigned long long)nb_off[p.npairs]); return fail(FCM_ELIMIT); }
+  std::vector<u32> nb_off32(nb_off.begin(), nb_off.end());
   if ((rc = dev_alloc(e, &d_pair, p.npairs))) return fail(rc);
   if ((rc = dev_alloc(e, &d_off, p.npairs + 1))) return fail(rc);
   if ((rc = dev_alloc(e, &d_list, nb_list.size()))) return fail(rc);
-  if ((rc = dev_alloc(e, &p.adj, adjw * nchains))) return fail(rc);
-  if ((rc = dev_alloc(e, &p.items, nslots * nchains))) return fail(rc);
-  if ((rc = dev_alloc(e, &p.pos, nslots * nchains))) return fail(rc);
-  if ((rc = dev_alloc(e, &p.dbl, p.npairs * nchains))) return fail(rc);
-  if ((rc = dev_alloc(e, &p.dblpos, p.npairs * nchains))) return fail(rc);
+  {
+    // one block per chain: [adj | items | pos | dbl | dblpos], block stride padded to 128 bytes
+    const u64 w_adj = adjw * 2, w_total = w_adj + 2 * nslots + 2 * p.npairs;
+    if (w_total > 0xfffffff0ULL) { fcm_set_error("graph too large: a chain's state exceeds 2^32 words"); return fail(FCM_ELIMIT); }
+    p.stride32 = (w_total + 31) & ~31ULL;
+    p.off_items = (u32)w_adj; p.off_pos = (u32)(w_adj + nslots);
+    p.off_dbl = (u32)(w_adj + 2 * nslots); p.off_dblpos = (u32)(w_adj + 2 * nslots + p.npairs);
+    u32* blk = nullptr;
+    if ((rc = dev_alloc(e, &blk, p.stride32 * nchains))) return fail(rc);
+    p.adj = (u64*)blk; p.items = blk + p.off_items; p.pos = blk + p.off_pos;
+    p.dbl = blk + p.off_dbl; p.dblpos = blk + p.off_dblpos;
+  }
   if ((rc = dev_alloc(e, &p.st, (size_t)nchains))) return fail(rc);
   if ((rc = dev_alloc(e, &e->edit_dev, (size_t)FCM_MAXEDIT * 2))) return fail(rc);
   if ((rc = dev_alloc(e, &e->io_dev, (size_t)2 * FCM_MAXD + 8))) return fail(rc);
@@ -206,7 +215,7 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     E_CUDA(cudaMemcpyAsync(p.dbl, dbl.data(), p.npairs * 4, cudaMemcpyHostToDevice, s));
     E_CUDA(cudaMemcpyAsync(p.dblpos, dblpos.data(), p.npairs * 4, cudaMemcpyHostToDevice, s));
   }
-  E_CUDA(cudaMemcpyAsync(d_off, nb_off.data(), (p.npairs + 1) * 8, cudaMemcpyHostToDevice, s));
+  E_CUDA(cudaMemcpyAsync(d_off, nb_off32.data(), (p.npairs + 1) * 4, cudaMemcpyHostToDevice, s));
   E_CUDA(cudaMemcpyAsync(d_list, nb_list.data(), nb_list.size() * 4, cudaMemcpyHostToDevice, s));
   if (adjw) E_CUDA(cudaMemcpyAsync(p.adj, adj.data(), adjw * 8, cudaMemcpyHostToDevice, s));
   std::vector<ChainState> st(nchains);
@@ -322,7 +331,7 @@ extern "C" int fcm_ensemble_read(fcm_ensemble* e, uint32_t chain, uint64_t* fc, 
   if (rng_out) memcpy(rng_out, c.rng, 32);
   if (edges_out && c.E) {
     std::vector<u32> items(c.E);
-    FCM_CUDA(cudaMemcpyAsync(items.data(), e->p.items + (u64)chain * 2 * e->p.npairs, (size_t)c.E * 4, cudaMemcpyDeviceToHost, e->ctx->stream));
+    FCM_CUDA(cudaMemcpyAsync(items.data(), e->p.items + (u64)chain * e->p.stride32, (size_t)c.E * 4, cudaMemcpyDeviceToHost, e->ctx->stream));
     FCM_CUDA(cudaStreamSynchronize(e->ctx->stream));
     for (u32 i = 0; i < c.E; i++) {
       uint2 ab = e->pair_ab_host[items[i] >> 1];

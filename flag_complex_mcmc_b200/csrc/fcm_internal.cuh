@@ -77,14 +77,17 @@ struct EnsParams {
   u32 maxc, Kcap, KWcap;
   // static, shared by all chains
   const uint2* pair_ab;             // pair id -> (big, small)
-  const u64* nb_off;                // npairs + 1
+  const u32* nb_off;                // npairs + 1 (total list length < 2^32 is checked at create)
   const u32* nb_list;               // common undirected neighbours, ascending
-  // per chain (chain-major)
-  u64* adj;                         // nchains * n * W
-  u32* items;                       // nchains * 2*npairs  (directed-edge slots in container order)
-  u32* pos;                         // nchains * 2*npairs  (slot -> index in items | NONE)
-  u32* dbl;                         // nchains * npairs    (pair ids in container order)
-  u32* dblpos;                      // nchains * npairs
+  // per chain: one block of stride32 32-bit words = [adj | items | pos | dbl | dblpos]; the pointers
+  // below are chain 0's, chain k's are stride32 words further (one base register per chain)
+  u64 stride32;
+  u32 off_items, off_pos, off_dbl, off_dblpos;   // word offsets inside a block (adj is at 0)
+  u64* adj;                         // n * W        packed 64-bit out-neighbour rows
+  u32* items;                       // 2*npairs     directed-edge slots in container order
+  u32* pos;                         // 2*npairs     slot -> index in items | NONE
+  u32* dbl;                         // npairs       pair ids in container order
+  u32* dblpos;                      // npairs
   ChainState* st;                   // nchains
   // settings
   u64 bmin[FCM_MAXB], bmax[FCM_MAXB];
