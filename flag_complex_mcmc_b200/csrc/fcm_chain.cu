@@ -266,8 +266,13 @@ __device__ int local_count_any(const u64* M, int K, int KW, int lane, u64* out, 
 #define SM_CV 1056                     // u32[64]          common neighbours of the coming pair
 #define SM_CV2 1312                    // u32[64]          ... of the going pair (double move)
 #define SM_FLAG 1568                   // int[12]          see FL_*
-#define SM_TILE 1616
-enum { FL_DEEP = 0, FL_TOP = 1, FL_ERR = 2, FL_RC = 3, FL_K = 4, FL_LEN = 5 };
+#define SM_AT 1616                     // u32[32]          hot path: rows of the tagged graph
+#define SM_SRC 1744                    // u32[32]          hot path: source vertex of each extra tagged copy
+#define SM_PARK 1872                   // u32[16]          a sampled proposal handed to cold_step, see PK_*
+#define SM_TILE 1936
+enum { FL_DEEP = 0, FL_TOP = 1, FL_ERR = 2, FL_RC = 3, FL_K = 4, FL_LEN = 5, FL_OVF = 6 };
+enum { PK_KIND = 0, PK_SLOT, PK_DELME, PK_IDX, PK_DIDX, PK_DPAIR, PK_LAST, PK_QPOS, PK_TA, PK_TB, PK_TDM0, PK_TDM1,
+       PK_CA, PK_CD, PK_OA, PK_OD };
 struct WarpSmem {
   u64 *M, *fc, *pre, *post;
   u32 *verts, *edits;
@@ -582,6 +587,128 @@ __device__ __forceinline__ void drop_edge_from_view(const u32* list, int c, u32 
   else if (iq >= 0) { if (ip == -2) ga.outU &= ~(1ULL << iq); else ga.outV &= ~(1ULL << iq); }
 }
 
+// ---- hot path (lists of <= 32 common neighbours, tagged graph of <= 32 vertices) ----------------------
+// hot_issue: every word the pair needs is requested with cp.async, nothing is held in registers:
+//   tile rows 0..cpad-1 : row C[i], the word holding column C[lane]
+//   tile rows cpad..+3  : row u and row v at that word; row C[lane] at the words of u and of v
+__device__ __forceinline__ int hot_tile_words(int c) { return (((c + 3) & ~3) + 4) * c; }
+__device__ __forceinline__ void hot_issue(const u32* cb, u32 W32, u32 x, int c, u32 u, u32 v, u32* list, u32* rowoff,
+                                          u32* tile, int lane) {
+  list[lane] = x;
+  rowoff[lane] = x * W32;                               // lanes past c hold row 0: copied for the padding rows only
+  __syncwarp();
+  if (lane < c) {
+    u32 dst = (u32)__cvta_generic_to_shared(tile + lane);
+    const u32* src = cb + (x >> 5);
+    const u32 pitch = 4u * (u32)c;
+    const int cpad = (c + 3) & ~3;
+#pragma unroll 1
+    for (int i0 = 0; i0 < cpad; i0 += 4) {
+      const uint4 ro = *(const uint4*)&rowoff[i0];
+      cp_async4(dst, src + ro.x); dst += pitch;
+      cp_async4(dst, src + ro.y); dst += pitch;
+      cp_async4(dst, src + ro.z); dst += pitch;
+      cp_async4(dst, src + ro.w); dst += pitch;
+    }
+    const u32* rx = cb + x * W32;
+    cp_async4(dst, src + u * W32); dst += pitch;
+    cp_async4(dst, src + v * W32); dst += pitch;
+    cp_async4(dst, rx + (u >> 5)); dst += pitch;
+    cp_async4(dst, rx + (v >> 5));
+  }
+  cp_async_commit();
+}
+// hot_finish: tile -> A32[i] = { j : C[i] -> C[j] } and the four relation masks
+struct G32 { u32 inU, outU, inV, outV; };
+__device__ __forceinline__ G32 hot_finish(const u32* tile, int c, const u32* list, u32 u, u32 v, u32* A32, int lane) {
+  const u32 x = list[lane];
+  const u32 m = lane < c ? 1u << (x & 31) : 0u;         // idle lanes never vote
+  const u32* col = tile + min(lane, max(c - 1, 0));
+  const int cpad = (c + 3) & ~3;
+#pragma unroll 1
+  for (int i = 0; i < cpad; i += 4) {                   // the padding rows give rows that nobody reads
+    const u32 t0 = col[i * c], t1 = col[(i + 1) * c], t2 = col[(i + 2) * c], t3 = col[(i + 3) * c];
+    uint4 b;
+    b.x = __ballot_sync(FULL, t0 & m); b.y = __ballot_sync(FULL, t1 & m);
+    b.z = __ballot_sync(FULL, t2 & m); b.w = __ballot_sync(FULL, t3 & m);
+    if (lane == 0) *(uint4*)&A32[i] = b;
+  }
+  const u32* rel = col + cpad * c;
+  const u32 lu = rel[0], lv = rel[c], xu = rel[2 * c], xv = rel[3 * c];
+  G32 g;
+  g.outU = __ballot_sync(FULL, lu & m);
+  g.outV = __ballot_sync(FULL, lv & m);
+  g.inU = __ballot_sync(FULL, m && ((xu >> (u & 31)) & 1u));
+  g.inV = __ballot_sync(FULL, m && ((xv >> (v & 31)) & 1u));
+  __syncwarp();
+  return g;
+}
+// the double move's coming edge u->v is counted in the graph without delme = d0->d1
+__device__ __forceinline__ void hot_drop_edge(const u32* list, int c, u32 u, u32 v, u32 d0, u32 d1, u32* A32, int lane, G32& g) {
+  const int ip = d0 == u ? -2 : d0 == v ? -3 : list_index(list, c, d0, lane);
+  const int iq = d1 == u ? -2 : d1 == v ? -3 : list_index(list, c, d1, lane);
+  if (ip == -1 || iq == -1) return;
+  if (ip >= 0 && iq >= 0) { if (lane == 0) A32[ip] &= ~(1u << iq); __syncwarp(); }
+  else if (ip >= 0) { if (iq == -2) g.inU &= ~(1u << ip); else g.inV &= ~(1u << ip); }
+  else if (iq >= 0) { if (ip == -2) g.outU &= ~(1u << iq); else g.outV &= ~(1u << iq); }
+}
+// Tagged graph.  A common neighbour w of u and v can stand before u (tag X: w->u, w->v), between them
+// (Y: u->w->v; Y2: v->w->u, the other direction of the same pair, used by a flip) or after v (Z).
+// A vertex gets one bit per tag it carries: its first tag on its own bit (< c), further tags on
+// extra bits c.. (vertices doubly joined to u or v).  Along a simplex tags never decrease and Y, Y2
+// never meet, so with AT[t] = (out-neighbours of t's vertex, expanded to all their tagged copies) &
+// (copies whose tag may follow t's) the simplices through the edge are the ordered cliques of AT:
+// plain single-mask candidate sets.  Returns false when there are more than 32 tagged copies.
+struct Tagged { u32 come, go, row; };                  // root sets of the two counts; this lane's row
+__device__ __forceinline__ bool hot_tag(const G32& g, int c, bool flip, const u32* A32, u32* AT, u32* src, int lane,
+                                        Tagged& t) {
+  const u32 X = g.inU & g.inV, Y = g.outU & g.inV, Y2 = flip ? (g.inU & g.outV) : 0u, Z = g.outU & g.outV;
+  const u32 eY = Y & X, eY2 = Y2 & (X | Y), eZ = Z & (X | Y | Y2);
+  const int nY = __popc(eY), nY2 = __popc(eY2), nZ = __popc(eZ), ne = nY + nY2 + nZ;
+  if (c + ne > 32) return false;
+  const u32 below = (1u << lane) - 1, bit = 1u << lane;
+  u32 TY = Y & ~X, TY2 = Y2 & ~(X | Y), TZ = Z & ~(X | Y | Y2);
+  u32 a = A32[lane];                                    // rows past c are padding (never selected below)
+  if (ne) {
+    if (eY & bit) src[__popc(eY & below)] = lane;
+    if (eY2 & bit) src[nY + __popc(eY2 & below)] = lane;
+    if (eZ & bit) src[nY + nY2 + __popc(eZ & below)] = lane;
+    TY |= ((1u << nY) - 1) << c;
+    TY2 |= ((1u << nY2) - 1) << (c + nY);
+    TZ |= ((1u << nZ) - 1) << (c + nY + nY2);
+    __syncwarp();
+    if (lane >= c && lane < c + ne) a = A32[src[lane - c]];
+    for (int k = 0; k < ne; k++) a |= ((a >> src[k]) & 1u) << (c + k);
+  }
+  const u32 allow = (X & bit) ? (X | TY | TY2 | TZ) : (TY & bit) ? (TY | TZ) : (TY2 & bit) ? (TY2 | TZ) : (TZ & bit) ? TZ : 0u;
+  t.row = a & allow;
+  AT[lane] = t.row;
+  t.come = X | TY | TZ;
+  t.go = X | TY2 | TZ;
+  __syncwarp();
+  return true;
+}
+// Ordered cliques of the tagged graph with >= 2 vertices, rooted at this lane's tagged vertex:
+// cnt[k] += sign * (number with k + 2 vertices) (flag_count index k + 3).  Sets *ovf when a clique of
+// more than DELTA_SD + 1 vertices exists (the proposal is then redone by cold_step).
+__device__ __forceinline__ void hot_count(u32 roots, u32 row, const u32* AT, int lane, int sign, int (&cnt)[DELTA_SD], int* ovf) {
+  if (!((roots >> lane) & 1u)) return;
+  const u32 P1 = row & roots;
+  cnt[0] += sign * __popc(P1);
+  for (u32 R1 = P1; R1; R1 &= R1 - 1) {
+    const u32 P2 = P1 & AT[__ffs((int)R1) - 1];
+    if (!P2) continue;
+    cnt[1] += sign * __popc(P2);
+    for (u32 R2 = P2; R2; R2 &= R2 - 1) {
+      const u32 P3 = P2 & AT[__ffs((int)R2) - 1];
+      if (!P3) continue;
+      cnt[2] += sign * __popc(P3);
+      for (u32 R3 = P3; R3; R3 &= R3 - 1)
+        if (P3 & AT[__ffs((int)R3) - 1]) *ovf = 1;
+    }
+  }
+}
+
 // Delta of a proposal whose lists need two column slots (32 < c <= 64): register gathers, one pair
 // after the other.  Cold path: the warp totals go to deep[] / dflag[] like the counts of the deep
 // levels (the caller folds them in), K to dflag[FL_K].
@@ -650,6 +777,116 @@ __device__ __noinline__ u64 full_path(const EnsParams& p, u32* cb, unsigned char
   return fnew;
 }
 
+// The edge containers after apply (+ revert), replayed in closed form (both moves keep |E| and the
+// number of double pairs).  Lane 0 stores.
+//   flip : remove slot (swap_remove: the last element moves into its hole), append slot^1; a revert
+//          appends slot again and removes slot^1: either way `fin` ends up last.
+//   move : append add = slot^1 (its pair turns double), swap_remove delme: add moves into delme's hole;
+//          dpair leaves the double set and add's pair, just appended there, moves into its hole.  A revert
+//          removes add again (the old last elements move into the holes) and appends delme / dpair.
+__device__ __forceinline__ void update_containers(const EnsParams& p, u32* cb, int kind, bool ok, u32 slot, u32 delme, u32 idx,
+                                                  u32 didx, u32 dpair, u32 last, u32 qpos, u32 E, u32 ND, int lane) {
+  u32* const items = cb + p.off_items;
+  u32* const pos = cb + p.off_pos;
+  u32* const dbl = cb + p.off_dbl;
+  u32* const dblpos = cb + p.off_dblpos;
+  if (kind == 0) {
+    const u32 fin = ok ? slot ^ 1 : slot;
+    if (lane == 0) {
+      items[idx] = last; pos[last] = idx;
+      pos[fin ^ 1] = FCM_NONE;
+      items[E - 1] = fin; pos[fin] = E - 1;
+    }
+  } else if (ok) {
+    const u32 add = slot ^ 1, pairA = slot >> 1;
+    if (lane == 0) {
+      items[qpos] = add; pos[add] = qpos; pos[delme] = FCM_NONE;
+      dbl[didx] = pairA; dblpos[pairA] = didx; dblpos[dpair] = FCM_NONE;
+    }
+  } else {
+    const u32 last0 = items[E - 1], lastd0 = dbl[ND - 1];
+    if (lane == 0) {
+      items[qpos] = last0; pos[last0] = qpos;
+      items[E - 1] = delme; pos[delme] = E - 1;
+      dbl[didx] = lastd0; dblpos[lastd0] = didx;
+      dbl[ND - 1] = dpair; dblpos[dpair] = ND - 1;
+    }
+  }
+}
+// adjacency bits of an accepted move: gu->gv leaves, cu->cv comes.  Plain stores: the rows are read
+// through this SM's L1 (cp.async.ca), which its own stores keep coherent.
+__device__ __forceinline__ void update_adjacency(u32* cb, u32 W32, u32 gu, u32 gv, u32 cu, u32 cv, int lane) {
+  if (lane == 0) {
+    const u32 igo = gu * W32 + (gv >> 5), icome = cu * W32 + (cv >> 5);
+    const u32 mgo = 1u << (gv & 31), mcome = 1u << (cv & 31);
+    if (igo == icome) cb[igo] = (cb[igo] & ~mgo) | mcome;
+    else { cb[igo] &= ~mgo; cb[icome] |= mcome; }
+  }
+}
+
+// One sampled proposal (parked in shared memory by the hot loop) finished by the general code:
+// two-slot lists (32 < c <= 64), more than 32 tagged copies, simplices beyond the register levels,
+// lists beyond FAST_C (full path) or a forced full path.  Reads and writes the chain's state in HBM.
+__device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned char* wb, int lane, fcm_trace_rec* tr_out,
+                                      int force_full) {
+  const u32* park = (const u32*)(wb + SM_PARK);
+  u64* const sdeep = (u64*)(wb + SM_DEEP);
+  int* const sflag = (int*)(wb + SM_FLAG);
+  const int kind = (int)park[PK_KIND];
+  const u32 slot = park[PK_SLOT], delme = park[PK_DELME], idx = park[PK_IDX], didx = park[PK_DIDX], dpair = park[PK_DPAIR];
+  const u32 last = park[PK_LAST], qpos = park[PK_QPOS], ta = park[PK_TA], tb = park[PK_TB], tdm0 = park[PK_TDM0], tdm1 = park[PK_TDM1];
+  const int cA = (int)park[PK_CA], cD = (int)park[PK_CD];
+  const u32 oA = park[PK_OA], oD = park[PK_OD];
+  ChainState* const st = &p.st[chain];
+  u32* const cb = (u32*)p.adj + (u64)chain * p.stride32;
+  const u32 W32 = 2 * p.W;
+  const u64 fc = st->flag_count[lane];
+  int len = st->fc_len;
+  const u32 E = st->E, ND = st->ND;
+  int err = 0, K = 0;
+  u64 fnew = fc;
+  const int cB = kind == 0 ? 0 : cD;
+  if (lane < 8) sflag[lane] = 0;
+  sdeep[lane] = 0;
+  __syncwarp();
+  if (!force_full && cA <= FAST_C && cB <= FAST_C) {
+    delta_wide(p, cb, wb, kind, ta, tb, tdm0, tdm1, oA, cA, oD, cD, lane);
+    if (sflag[FL_ERR]) err = sflag[FL_ERR];
+    fnew = fc + sdeep[lane];
+    if (__any_sync(FULL, (long long)fnew < 0)) err = FCM_EASSERT;
+    len = max(len, sflag[FL_TOP] + 1);
+    K = sflag[FL_K];
+    __syncwarp();
+    sdeep[lane] = 0;
+    if (lane < 8) sflag[lane] = 0;
+    __syncwarp();
+  } else {
+    const u32 s0 = kind == 0 ? slot : slot ^ 1, s1 = kind == 0 ? slot ^ 1 : delme;
+    fnew = full_path(p, cb, wb, s0, kind == 0 ? 0u : 1u, s1, kind == 0 ? 1u : 0u, fc, len, lane);
+    if (sflag[FL_RC]) err = sflag[FL_RC];
+    K = sflag[FL_K];
+    len = sflag[FL_LEN];
+  }
+  if (err) { if (lane == 0) st->err = err; return err; }
+  const bool ok = bounds_ok(p, fnew, lane);
+  update_containers(p, cb, kind, ok, slot, delme, idx, didx, dpair, last, qpos, E, ND, lane);
+  if (ok) update_adjacency(cb, W32, kind == 0 ? ta : tdm0, kind == 0 ? tb : tdm1, tb, ta, lane);
+  __syncwarp();
+  if (ok) st->flag_count[lane] = fnew;
+  if (lane == 0) {
+    st->fc_len = len;
+    st->sampled += 1; st->accepted += ok; st->sumK += (u64)K; st->nonempty += 1;
+    if (tr_out) {
+      fcm_trace_rec tr;
+      tr.flags = (u32)kind | (ok ? FCM_TR_ACCEPT : 0u);
+      tr.a = ta; tr.b = tb; tr.dm0 = tdm0; tr.dm1 = tdm1; tr.K = (u32)K; tr.draws = 0; tr.pad = 0;
+      *tr_out = tr;
+    }
+  }
+  __syncwarp();
+  return 0;
+}
+
 __global__ void __launch_bounds__(128, 7)
 chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ trace, u32 trace_chain,
                   u32 smem_per_warp, int force_full) {
@@ -658,12 +895,14 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
   const u32 chain = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (chain >= p.nchains) return;
   unsigned char* const wb = smem_raw + (size_t)(threadIdx.x >> 5) * smem_per_warp;
-  u64* const sA = (u64*)(wb + SM_A);
-  u64* const sdeep = (u64*)(wb + SM_DEEP);
+  u32* const sA32 = (u32*)(wb + SM_A);
   u32* const srowoff = (u32*)(wb + SM_ROWOFF);
   u32* const scv = (u32*)(wb + SM_CV);
   u32* const scv2 = (u32*)(wb + SM_CV2);
   int* const sflag = (int*)(wb + SM_FLAG);
+  u32* const sAT = (u32*)(wb + SM_AT);
+  u32* const ssrc = (u32*)(wb + SM_SRC);
+  u32* const spark = (u32*)(wb + SM_PARK);
   u32* const stile = (u32*)(wb + SM_TILE);
   ChainState* const st = &p.st[chain];
   if (st->err) return;
@@ -672,222 +911,191 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
 #define ITEMS(i) cb[p.off_items + (i)]
 #define POS(i) cb[p.off_pos + (i)]
 #define DBL(i) cb[p.off_dbl + (i)]
-#define DBLPOS(i) cb[p.off_dblpos + (i)]
   const u32 E = st->E, ND = st->ND;                    // both moves keep |E| and the number of double pairs
   const u32 W32 = 2 * p.W;
-  Rng g{st->rng[0], st->rng[1], st->rng[2], st->rng[3]};
-  u64 fc = st->flag_count[lane];                       // lane d owns flag_count[d]
-  int len = st->fc_len;
-  u32 accepted = 0, sumK = 0, nonempty = 0;            // per launch (nsteps <= 2^24: the host splits longer runs)
-  int err = 0;
-  sdeep[lane] = 0;
   if (lane < 12) sflag[lane] = 0;
+  ((u64*)(wb + SM_DEEP))[lane] = 0;
   __syncwarp();
+  if (trace != nullptr && chain != trace_chain) trace = nullptr;
 
   u32 step = 0;
-  for (; step < nsteps; step++) {
-    // ---- Transition::random_move: WeightedIndex<f64>::sample (src/lib.rs:210) ----
-    const u64 r = g.next();
-    const double v = __longlong_as_double((long long)((r >> 12) | 0x3ff0000000000000ULL)) - 1.0;
-    const double chosen = __dadd_rn(__dmul_rn(v, p.scale), 0.0);
-    const int kind = (p.cum[0] <= chosen) + (p.cum[1] <= chosen) + (p.cum[2] <= chosen);
-    if (kind > 1) { err = FCM_EUNSUPPORTED; break; }
-    // ---- single_edge_flip (src/lib.rs:292-299) / double_edge_move (:304-325): the draws.  Loads are
-    //      written in the order they become issuable so that independent ones overlap. ----
-    bool live = false;                                  // a non-empty transition
-    bool sampled_edge = false;
-    u32 idx = 0, slot = 0, didx = 0, dpair = 0, delme = 0, last = 0, qpos = 0;
-    u32 oA = 0, oD = 0;
-    int cA = 0, cD = 0;
-    uint2 abA = make_uint2(0, 0), abD = make_uint2(0, 0);
-    if (kind == 0) {
-      if (E) {
-        idx = (u32)gen_range(g, E);
+  while (step < nsteps) {
+    // ---- hot stretch: chain state in registers until a proposal needs the general code ----
+    Rng g{st->rng[0], st->rng[1], st->rng[2], st->rng[3]};
+    u64 fc = st->flag_count[lane];                     // lane d owns flag_count[d]
+    int len = st->fc_len;
+    u32 accepted = 0, sumK = 0, nonempty = 0;          // per stretch (nsteps <= 2^24: the host splits longer runs)
+    const u32 step0 = step;
+    int err = 0;
+    bool cold = false;
+    for (; step < nsteps; step++) {
+      // ---- Transition::random_move: WeightedIndex<f64>::sample (src/lib.rs:210) ----
+      const u64 r = g.next();
+      const double v = __longlong_as_double((long long)((r >> 12) | 0x3ff0000000000000ULL)) - 1.0;
+      const double chosen = __dadd_rn(__dmul_rn(v, p.scale), 0.0);
+      const int kind = (p.cum[0] <= chosen) + (p.cum[1] <= chosen) + (p.cum[2] <= chosen);
+      if (kind > 1) { err = FCM_EUNSUPPORTED; break; }
+      // ---- single_edge_flip (src/lib.rs:292-299) / double_edge_move (:304-325): the draws.  Loads are
+      //      written in the order they become issuable so that independent ones overlap. ----
+      bool live = false;                                // a non-empty transition
+      bool sampled_edge = false;
+      u32 idx = 0, slot = 0, didx = 0, dpair = 0, delme = 0, last = 0, qpos = 0;
+      u32 oA = 0, oD = 0;
+      int cA = 0, cD = 0;
+      uint2 abA = make_uint2(0, 0), abD = make_uint2(0, 0);
+      if (kind == 0) {
+        if (E) {
+          idx = (u32)gen_range(g, E);
+          slot = ITEMS(idx);
+          last = ITEMS(E - 1);
+          const u32 rev = POS(slot ^ 1);
+          abA = __ldg(&p.pair_ab[slot >> 1]);
+          oA = __ldg(&p.nb_off[slot >> 1]);
+          cA = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - oA);
+          live = rev == FCM_NONE;                       // the reverse edge exists: empty transition
+          sampled_edge = true;
+        }
+      } else if (ND) {
+        if (2ULL * ND >= E) { err = FCM_EINVAL; break; }       // reference spins forever (FIXME :307)
+        didx = (u32)gen_range(g, ND);
+        idx = (u32)gen_range(g, E);                     // the next draw does not depend on the loaded pair
+        dpair = DBL(didx);
         slot = ITEMS(idx);
-        last = ITEMS(E - 1);
-        const u32 rev = POS(slot ^ 1);
-        abA = __ldg(&p.pair_ab[slot >> 1]);
-        oA = __ldg(&p.nb_off[slot >> 1]);
-        cA = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - oA);
-        live = rev == FCM_NONE;                         // the reverse edge exists: empty transition
+        abD = __ldg(&p.pair_ab[dpair]);
+        oD = __ldg(&p.nb_off[dpair]);
+        cD = (int)(__ldg(&p.nb_off[dpair + 1]) - oD);
+        for (;;) {
+          const u32 rev = POS(slot ^ 1);
+          abA = __ldg(&p.pair_ab[slot >> 1]);
+          oA = __ldg(&p.nb_off[slot >> 1]);
+          cA = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - oA);
+          if (rev == FCM_NONE) break;
+          idx = (u32)gen_range(g, E);
+          slot = ITEMS(idx);
+        }
+        const bool first = g.next() < 0x8000000000000000ULL;   // gen_bool(0.5)
+        delme = 2 * dpair + (first ? 1u : 0u);                 // first: [min,max] = small -> big
+        qpos = POS(delme);                                     // needed when the containers are updated
+        live = true;
         sampled_edge = true;
       }
-    } else if (ND) {
-      if (2ULL * ND >= E) { err = FCM_EINVAL; break; }         // reference spins forever (FIXME :307)
-      didx = (u32)gen_range(g, ND);
-      idx = (u32)gen_range(g, E);                       // the next draw does not depend on the loaded pair
-      dpair = DBL(didx);
-      slot = ITEMS(idx);
-      abD = __ldg(&p.pair_ab[dpair]);
-      oD = __ldg(&p.nb_off[dpair]);
-      cD = (int)(__ldg(&p.nb_off[dpair + 1]) - oD);
-      for (;;) {
-        const u32 rev = POS(slot ^ 1);
-        abA = __ldg(&p.pair_ab[slot >> 1]);
-        oA = __ldg(&p.nb_off[slot >> 1]);
-        cA = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - oA);
-        if (rev == FCM_NONE) break;
-        idx = (u32)gen_range(g, E);
-        slot = ITEMS(idx);
-      }
-      const bool first = g.next() < 0x8000000000000000ULL;     // gen_bool(0.5)
-      delme = 2 * dpair + (first ? 1u : 0u);                   // first: [min,max] = small -> big
-      qpos = POS(delme);                                       // needed when the containers are updated
-      live = true;
-      sampled_edge = true;
-    }
-    // (ta,tb) = the sampled single edge, (tdm0,tdm1) = delme; dir 0 of a slot = big -> small
-    u32 ta = 0, tb = 0, tdm0 = 0, tdm1 = 0;
-    if (sampled_edge) { ta = (slot & 1) ? abA.y : abA.x; tb = (slot & 1) ? abA.x : abA.y; }
-    if (kind == 1 && live) { tdm0 = (delme & 1) ? abD.y : abD.x; tdm1 = (delme & 1) ? abD.x : abD.y; }
+      // (ta,tb) = the sampled single edge, (tdm0,tdm1) = delme; dir 0 of a slot = big -> small
+      u32 ta = 0, tb = 0, tdm0 = 0, tdm1 = 0;
+      if (sampled_edge) { ta = (slot & 1) ? abA.y : abA.x; tb = (slot & 1) ? abA.x : abA.y; }
+      if (kind == 1 && live) { tdm0 = (delme & 1) ? abD.y : abD.x; tdm1 = (delme & 1) ? abD.x : abD.y; }
 
-    // ---- State::apply_transition  src/lib.rs:61-79: flag_count += post - pre ----
-    int K = 0;
-    u64 fnew = fc;
-    // the edge that comes is tb->ta for both moves; the edge that goes is ta->tb (flip) or delme
-    const u32 gu = kind == 0 ? ta : tdm0, gv = kind == 0 ? tb : tdm1;
-    const u32 igo = gu * W32 + (gv >> 5), icome = tb * W32 + (ta >> 5);
-    u32 vgo = 0, vcome = 0;
-    if (live) {
-      vgo = cb[igo]; vcome = cb[icome];                 // early: rewritten on accept without a stall
-      int cnt[DELTA_SD];
+      // ---- State::apply_transition  src/lib.rs:61-79: flag_count += post - pre ----
+      int K = 0;
+      u64 fnew = fc;
+      // the edge that comes is tb->ta for both moves; the edge that goes is ta->tb (flip) or delme
+      const u32 gu = kind == 0 ? ta : tdm0, gv = kind == 0 ? tb : tdm1;
+      const u32 igo = gu * W32 + (gv >> 5), icome = tb * W32 + (ta >> 5);
+      u32 vgo = 0, vcome = 0;
+      if (live) {
+        const int cB = kind == 0 ? 0 : cD;
+        const int wordsA = hot_tile_words(cA);
+        cold = force_full || cA > NARROW_C || cB > NARROW_C || wordsA + hot_tile_words(cB) > TILE_WORDS;
+        int cnt[DELTA_SD];
 #pragma unroll
-      for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
-      int tri = 0, top = 1;
-      const int cB = kind == 0 ? 0 : cD;
-      const int tileA_words = ((cA + 3) & ~3) * cA;
-      if (!force_full && cA <= NARROW_C && cB <= NARROW_C && tileA_words + ((cB + 3) & ~3) * cB <= TILE_WORDS) {
-        // hot path: both gathers are in flight together
-        const u32 xA = lane < cA ? __ldg(&p.nb_list[oA + lane]) : 0u;
-        const u32 xD = lane < cB ? __ldg(&p.nb_list[oD + lane]) : 0u;
-        Narrow nA, nD;
-        stage_issue(p, cb, xA, cA, tb, ta, scv, srowoff, stile, lane, nA);
-        if (kind == 1) stage_issue(p, cb, xD, cD, tdm0, tdm1, scv2, srowoff + 32, stile + tileA_words, lane, nD);
-        Gathered ga;
+        for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
+        int tri = 0, top = 1;
+        if (!cold) {
+          vgo = cb[igo]; vcome = cb[icome];             // early: rewritten on accept without a stall
+          // both gathers are in flight together
+          const u32 xA = lane < cA ? __ldg(&p.nb_list[oA + lane]) : 0u;
+          const u32 xD = lane < cB ? __ldg(&p.nb_list[oD + lane]) : 0u;
+          hot_issue(cb, W32, xA, cA, tb, ta, scv, srowoff, stile, lane);
+          if (kind == 1) hot_issue(cb, W32, xD, cD, tdm0, tdm1, scv2, srowoff + 32, stile + wordsA, lane);
+          Tagged t;
 #pragma unroll 1
-        for (int ph = 0; ph < 2; ph++) {
-          const int sign = ph ? -1 : 1;
-          if (ph == 0 || kind == 1) {
-            if (ph == 0 && kind == 1) cp_async_wait<1>(); else cp_async_wait<0>();
+          for (int ph = 0; ph < 2 && !cold; ph++) {
+            const int sign = ph ? -1 : 1;
+            if (ph == 0 || kind == 1) {
+              if (ph == 0 && kind == 1) cp_async_wait<1>(); else cp_async_wait<0>();
+              __syncwarp();
+              G32 ga = ph == 0 ? hot_finish(stile, cA, scv, tb, ta, sA32, lane)
+                               : hot_finish(stile + wordsA, cD, scv2, tdm0, tdm1, sA32, lane);
+              if (ph == 0 && kind == 1) hot_drop_edge(scv, cA, tb, ta, tdm0, tdm1, sA32, lane, ga);
+              if (!hot_tag(ga, ph ? cD : cA, kind == 0, sA32, sAT, ssrc, lane, t)) { cold = true; break; }
+            }
+            const u32 roots = (ph == 1 && kind == 0) ? t.go : t.come;
+            tri += sign * __popc(roots);
+            hot_count(roots, t.row, sAT, lane, sign, cnt, &sflag[FL_OVF]);
+            if (ph == 0) {
+              const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : roots ? 2 : 1;
+              top = __reduce_max_sync(FULL, mytop);
+            }
             __syncwarp();
-            if (ph == 0) stage_finish(stile, cA, nA, tb, ta, sA, lane, ga);
-            else stage_finish(stile + tileA_words, cD, nD, tdm0, tdm1, sA, lane, ga);
-            if (ph == 0 && kind == 1) drop_edge_from_view(scv, cA, tb, ta, tdm0, tdm1, sA, lane, ga);
-          } else {                                      // the flip's going edge: same pair, roles of u and v swapped
-            const u64 t = ga.inU; ga.inU = ga.inV; ga.inV = t;
-            const u64 t2 = ga.outU; ga.outU = ga.outV; ga.outV = t2;
           }
-          const u32 X = (u32)(ga.inU & ga.inV), Y = (u32)(ga.outU & ga.inV), Z = (u32)(ga.outU & ga.outV);
-          tri += sign * (__popc(X) + __popc(Y) + __popc(Z));
-          count_through_edge<u32>(X, Y, Z, ga.c, sA, lane, sign, cnt, sdeep, sflag);
-          if (ph == 0) {
-            const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : (X | Y | Z) ? 2 : 1;
-            top = __reduce_max_sync(FULL, mytop);
+          cp_async_wait<0>();
+          if (sflag[FL_OVF]) { cold = true; __syncwarp(); if (lane == 0) sflag[FL_OVF] = 0; }
+        }
+        if (cold) {
+          // hand the sampled proposal to the general code (nothing of the chain was modified yet)
+          if (lane == 0) {
+            spark[PK_KIND] = (u32)kind; spark[PK_SLOT] = slot; spark[PK_DELME] = delme; spark[PK_IDX] = idx;
+            spark[PK_DIDX] = didx; spark[PK_DPAIR] = dpair; spark[PK_LAST] = last; spark[PK_QPOS] = qpos;
+            spark[PK_TA] = ta; spark[PK_TB] = tb; spark[PK_TDM0] = tdm0; spark[PK_TDM1] = tdm1;
+            spark[PK_CA] = (u32)cA; spark[PK_CD] = (u32)cD; spark[PK_OA] = oA; spark[PK_OD] = oD;
           }
           __syncwarp();
+          break;
         }
         K = kind == 0 ? cA + 2 : union_size(scv, cA, scv2, cD, ta, tb, tdm0, tdm1, lane);
-      } else if (!force_full && cA <= FAST_C && cB <= FAST_C) {
-        delta_wide(p, cb, wb, kind, ta, tb, tdm0, tdm1, oA, cA, oD, cD, lane);
-        K = sflag[FL_K];
-      } else {
-        const u32 s0 = kind == 0 ? slot : slot ^ 1, s1 = kind == 0 ? slot ^ 1 : delme;
-        fnew = full_path(p, cb, wb, s0, kind == 0 ? 0u : 1u, s1, kind == 0 ? 1u : 0u, fc, len, lane);
-        if (sflag[FL_RC]) { err = sflag[FL_RC]; break; }
-        K = sflag[FL_K];
-        len = sflag[FL_LEN];
-        top = -1;                                       // flag_count is already new
-      }
-      if (top >= 0) {
         long long delta = 0;
 #pragma unroll
         for (int k = 0; k < DELTA_SD; k++) {
-          const int t = __reduce_add_sync(FULL, cnt[k]);
-          if (lane == k + 3) delta = t;
+          const int tot = __reduce_add_sync(FULL, cnt[k]);
+          if (lane == k + 3) delta = tot;
         }
         if (lane == 2) delta = tri;
-        if (__any_sync(FULL, sflag[FL_DEEP] != 0)) {   // counts below the register levels (or the wide path's)
-          if (sflag[FL_ERR]) { err = sflag[FL_ERR]; break; }
-          delta += (long long)sdeep[lane];
-          top = max(top, sflag[FL_TOP]);
-          __syncwarp();
-          sdeep[lane] = 0;
-          if (lane < 3) sflag[lane] = 0;
-          __syncwarp();
-        }
         fnew = fc + (u64)delta;
         if (__any_sync(FULL, (long long)fnew < 0)) { err = FCM_EASSERT; break; }
         len = max(len, top + 1);
+        sumK += K;
+        nonempty++;
       }
-      sumK += K;
-      nonempty++;
-    }
-    // ---- Bounds::check, then keep or revert_transition (src/lib.rs:186-191, 81-95) ----
-    const bool ok = bounds_ok(p, fnew, lane);
-    accepted += ok;
-    if (live) {
-      // The edge containers after apply (+ revert): both orders of events are replayed in closed form.
-      if (kind == 0) {
-        // remove slot (swap_remove: the last element moves into its hole), append slot^1; a revert
-        // appends slot again and removes slot^1: either way `fin` ends up last
-        const u32 fin = ok ? slot ^ 1 : slot;
-        if (lane == 0) {
-          ITEMS(idx) = last; POS(last) = idx;
-          POS(fin ^ 1) = FCM_NONE;
-          ITEMS(E - 1) = fin; POS(fin) = E - 1;
-        }
-      } else {
-        const u32 add = slot ^ 1, pairA = slot >> 1;
+      // ---- Bounds::check, then keep or revert_transition (src/lib.rs:186-191, 81-95) ----
+      const bool ok = bounds_ok(p, fnew, lane);
+      accepted += ok;
+      if (live) {
+        update_containers(p, cb, kind, ok, slot, delme, idx, didx, dpair, last, qpos, E, ND, lane);
         if (ok) {
-          // append add (pairA turns double), swap_remove delme: add moves into delme's hole; dpair leaves
-          // the double set and pairA, just appended there, moves into its hole
+          // adjacency bits: gu->gv leaves, tb->ta comes (plain stores of the words read above: the
+          // rows are read through this SM's L1, which its own stores keep coherent)
           if (lane == 0) {
-            ITEMS(qpos) = add; POS(add) = qpos; POS(delme) = FCM_NONE;
-            DBL(didx) = pairA; DBLPOS(pairA) = didx; DBLPOS(dpair) = FCM_NONE;
+            const u32 mgo = 1u << (gv & 31), mcome = 1u << (ta & 31);
+            if (igo == icome) cb[igo] = (vgo & ~mgo) | mcome;
+            else { cb[igo] = vgo & ~mgo; cb[icome] = vcome | mcome; }
           }
-        } else {
-          // ... then the revert removes add again (the old last elements move into the holes) and
-          // appends delme / dpair at the ends
-          const u32 last0 = ITEMS(E - 1), lastd0 = DBL(ND - 1);
-          if (lane == 0) {
-            ITEMS(qpos) = last0; POS(last0) = qpos;
-            ITEMS(E - 1) = delme; POS(delme) = E - 1;
-            DBL(didx) = lastd0; DBLPOS(lastd0) = didx;
-            DBL(ND - 1) = dpair; DBLPOS(dpair) = ND - 1;
-          }
+          fc = fnew;
         }
+        __syncwarp();
       }
-      if (ok) {
-        // adjacency bits: gu->gv leaves, tb->ta comes (plain stores of the words read above: the
-        // rows are read through this SM's L1, which its own stores keep coherent)
-        if (lane == 0) {
-          const u32 mgo = 1u << (gv & 31), mcome = 1u << (ta & 31);
-          if (igo == icome) cb[igo] = (vgo & ~mgo) | mcome;
-          else { cb[igo] = vgo & ~mgo; cb[icome] = vcome | mcome; }
-        }
-        fc = fnew;
+      if (trace != nullptr && lane == 0) {
+        fcm_trace_rec tr;
+        tr.flags = (u32)kind | (ok ? FCM_TR_ACCEPT : 0u) | (live ? 0u : FCM_TR_EMPTY);
+        tr.a = ta; tr.b = tb; tr.dm0 = tdm0; tr.dm1 = tdm1; tr.K = (u32)K; tr.draws = 0; tr.pad = 0;
+        trace[step] = tr;
       }
-      __syncwarp();
     }
-    if (trace != nullptr && chain == trace_chain && lane == 0) {
-      fcm_trace_rec tr;
-      tr.flags = (u32)kind | (ok ? FCM_TR_ACCEPT : 0u) | (live ? 0u : FCM_TR_EMPTY);
-      tr.a = ta; tr.b = tb; tr.dm0 = tdm0; tr.dm1 = tdm1; tr.K = (u32)K; tr.draws = 0; tr.pad = 0;
-      trace[step] = tr;
+    // ---- end of the stretch: the chain's state goes back to HBM ----
+    __syncwarp();
+    st->flag_count[lane] = fc;
+    if (lane == 0) {
+      st->rng[0] = g.s0; st->rng[1] = g.s1; st->rng[2] = g.s2; st->rng[3] = g.s3;
+      st->fc_len = len;
+      st->sampled += step - step0; st->accepted += accepted; st->sumK += sumK; st->nonempty += nonempty;
+      if (err) st->err = err;
     }
+    __syncwarp();
+    if (err || !cold) break;
+    if (cold_step(p, chain, wb, lane, trace ? trace + step : nullptr, force_full)) break;
+    step++;
   }
 #undef ITEMS
 #undef POS
 #undef DBL
-#undef DBLPOS
-  __syncwarp();
-  st->flag_count[lane] = fc;
-  if (lane == 0) {
-    st->rng[0] = g.s0; st->rng[1] = g.s1; st->rng[2] = g.s2; st->rng[3] = g.s3;
-    st->fc_len = len;
-    st->sampled += step; st->accepted += accepted; st->sumK += sumK; st->nonempty += nonempty;
-    st->err = err;
-  }
 }
 
 // State::apply_transition / revert_transition with explicit edits on one chain (one warp).
