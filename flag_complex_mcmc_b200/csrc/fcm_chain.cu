@@ -259,7 +259,7 @@ __device__ int local_count_any(const u64* M, int K, int KW, int lane, u64* out, 
 // path's arrays (a proposal takes one path or the other).
 #define FAST_C 64                      // longest common-neighbour list the delta path takes
 #define NARROW_C 32                    // staged gather: one column per lane
-#define TILE_WORDS 1024
+#define TILE_WORDS 1536                // >= hot_tile_words(32) = 1152; 28 warps x (SM_TILE + 6 KB) fit one SM
 #define SM_A 0                         // u64[FAST_C + 4]  adjacency among the common neighbours
 #define SM_DEEP 544                    // u64[FCM_MAXD]    counts below the register levels, by flag_count index
 #define SM_ROWOFF 800                  // u32[64]          row offsets of the two lists
@@ -994,27 +994,30 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
       if (live) {
         const int cB = kind == 0 ? 0 : cD;
         const int wordsA = hot_tile_words(cA);
-        cold = force_full || cA > NARROW_C || cB > NARROW_C || wordsA + hot_tile_words(cB) > TILE_WORDS;
+        cold = force_full || cA > NARROW_C || cB > NARROW_C;
         int cnt[DELTA_SD];
 #pragma unroll
         for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
         int tri = 0, top = 1;
         if (!cold) {
           vgo = cb[igo]; vcome = cb[icome];             // early: rewritten on accept without a stall
-          // both gathers are in flight together
+          // both gathers are in flight together when the tile holds both, else one after the other
+          const bool both = wordsA + hot_tile_words(cB) <= TILE_WORDS;
+          u32* const tileD = both ? stile + wordsA : stile;
           const u32 xA = lane < cA ? __ldg(&p.nb_list[oA + lane]) : 0u;
           const u32 xD = lane < cB ? __ldg(&p.nb_list[oD + lane]) : 0u;
           hot_issue(cb, W32, xA, cA, tb, ta, scv, srowoff, stile, lane);
-          if (kind == 1) hot_issue(cb, W32, xD, cD, tdm0, tdm1, scv2, srowoff + 32, stile + wordsA, lane);
+          if (kind == 1 && both) hot_issue(cb, W32, xD, cD, tdm0, tdm1, scv2, srowoff + 32, tileD, lane);
           Tagged t;
 #pragma unroll 1
           for (int ph = 0; ph < 2 && !cold; ph++) {
             const int sign = ph ? -1 : 1;
             if (ph == 0 || kind == 1) {
-              if (ph == 0 && kind == 1) cp_async_wait<1>(); else cp_async_wait<0>();
+              if (ph == 1 && !both) hot_issue(cb, W32, xD, cD, tdm0, tdm1, scv2, srowoff + 32, tileD, lane);
+              if (ph == 0 && kind == 1 && both) cp_async_wait<1>(); else cp_async_wait<0>();
               __syncwarp();
               G32 ga = ph == 0 ? hot_finish(stile, cA, scv, tb, ta, sA32, lane)
-                               : hot_finish(stile + wordsA, cD, scv2, tdm0, tdm1, sA32, lane);
+                               : hot_finish(tileD, cD, scv2, tdm0, tdm1, sA32, lane);
               if (ph == 0 && kind == 1) hot_drop_edge(scv, cA, tb, ta, tdm0, tdm1, sA32, lane, ga);
               if (!hot_tag(ga, ph ? cD : cA, kind == 0, sA32, sAT, ssrc, lane, t)) { cold = true; break; }
             }
