@@ -62,7 +62,7 @@ __device__ __forceinline__ u64 gen_range(Rng& g, u64 range) {
 
 struct Chain {                        // pointers of one chain + live scalars
   u64* adj;
-  u32 *items, *pos, *dbl, *dblpos;
+  u32 *items, *pos, *dbl, *dblpos, *ori;
   u32 E, ND;
 };
 
@@ -108,6 +108,9 @@ __device__ __forceinline__ void c_set_bit(const EnsParams& p, Chain& c, u32 slot
     u64* w = &c.adj[(u64)e.x * p.W + (e.y >> 6)];
     u64 m = 1ULL << (e.y & 63);
     *w = add ? (*w | m) : (*w & ~m);
+    u32* o = &c.ori[slot >> 5];
+    const u32 om = 1u << (slot & 31);
+    *o = add ? (*o | om) : (*o & ~om);
   }
 }
 
@@ -259,7 +262,7 @@ __device__ int local_count_any(const u64* M, int K, int KW, int lane, u64* out, 
 // path's arrays (a proposal takes one path or the other).
 #define FAST_C 64                      // longest common-neighbour list the delta path takes
 #define NARROW_C 32                    // staged gather: one column per lane
-#define TILE_WORDS 1536                // >= hot_tile_words(32) = 1152; 28 warps x (SM_TILE + 6 KB) fit one SM
+#define TILE_WORDS 1504                // >= hot_tile_words(32) = 1152; 7 blocks of 4 warps x (SM_TILE + 5.9 KB) + 1 KB fit one SM
 #define SM_A 0                         // u64[FAST_C + 4]  adjacency among the common neighbours
 #define SM_DEEP 544                    // u64[FCM_MAXD]    counts below the register levels, by flag_count index
 #define SM_ROWOFF 800                  // u32[64]          row offsets of the two lists
@@ -281,12 +284,14 @@ struct WarpSmem {
   int* dflag;
   u32* tile;
 };
-__host__ __device__ inline size_t warp_smem_bytes(u32 Kcap, u32 KWcap) {
+// tile = false: the hot path reads the clique index, no staging tile is needed
+__host__ __device__ inline size_t warp_smem_bytes(u32 Kcap, u32 KWcap, bool tile) {
   size_t full = (size_t)Kcap * KWcap * 8 + 3 * FCM_MAXD * 8 + (size_t)Kcap * 4 + FCM_MAXEDIT * 2 * 4;
-  if (full < TILE_WORDS * 4) full = TILE_WORDS * 4;
+  if (tile && full < TILE_WORDS * 4) full = TILE_WORDS * 4;
   return SM_TILE + full;
 }
-size_t fcm_chain_smem_per_warp(u32 Kcap, u32 KWcap) { return (warp_smem_bytes(Kcap, KWcap) + 15) & ~(size_t)15; }
+size_t fcm_chain_smem_per_warp(u32 Kcap, u32 KWcap) { return (warp_smem_bytes(Kcap, KWcap, true) + 15) & ~(size_t)15; }
+static size_t chain_smem_per_warp_mode(u32 Kcap, u32 KWcap, bool tile) { return (warp_smem_bytes(Kcap, KWcap, tile) + 15) & ~(size_t)15; }
 
 __device__ __forceinline__ WarpSmem carve(unsigned char* base, u32 Kcap, u32 KWcap) {
   WarpSmem s;
@@ -508,72 +513,12 @@ __device__ __forceinline__ void red_adj_bit(const EnsParams& p, u32* a32, u32 fr
   if (add) atomicOr(w, m); else atomicAnd(w, ~m);
 }
 
-// ---- staged gather for lists of <= 32 common neighbours (one column per lane) -----------------------
-// All row words of the pair are requested at once with cp.async (no registers held, one memory
-// round trip for the whole gather) into the warp's tile: word (i, lane) = row C[i], the 32-bit word
-// holding column C[lane].  stage_issue only issues; stage_finish turns the tile into bit rows.
 __device__ __forceinline__ void cp_async4(u32 saddr, const void* g) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(saddr), "l"(g) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-struct Narrow { u32 m, lu, lv, xu, xv; };               // this lane's column mask and relation words
-// x = C[lane] (0 beyond c).  rowoff[0..32) and list[0..32) are this pair's.
-__device__ __forceinline__ void stage_issue(const EnsParams& p, const u32* a32, u32 x, int c, u32 u, u32 v,
-                                            u32* list, u32* rowoff, u32* tile, int lane, Narrow& nb) {
-  const u32 W32 = 2 * p.W;
-  list[lane] = x;
-  rowoff[lane] = x * W32;                               // rows past c: offset 0, copied but never read
-  __syncwarp();
-  const u32 w = x >> 5;
-  nb.m = lane < c ? 1u << (x & 31) : 0u;
-  const u32* rx = a32 + x * W32;
-  nb.lu = a32[u * W32 + w]; nb.lv = a32[v * W32 + w];
-  nb.xu = rx[u >> 5]; nb.xv = rx[v >> 5];
-  if (lane < c) {
-    u32 dst = (u32)__cvta_generic_to_shared(tile + lane);
-    const u32* src = a32 + w;
-    const u32 pitch = 4u * (u32)c;
-    const int cpad = (c + 3) & ~3;
-#pragma unroll 1
-    for (int i0 = 0; i0 < cpad; i0 += 4) {
-      const uint4 ro = *(const uint4*)&rowoff[i0];
-      cp_async4(dst, src + ro.x); dst += pitch;
-      cp_async4(dst, src + ro.y); dst += pitch;
-      cp_async4(dst, src + ro.z); dst += pitch;
-      cp_async4(dst, src + ro.w); dst += pitch;
-    }
-  }
-  cp_async_commit();
-}
-__device__ __forceinline__ void stage_finish(const u32* tile, int c, const Narrow& nb, u32 u, u32 v, u64* A, int lane,
-                                             Gathered& g) {
-  const u32* col = tile + min(lane, max(c - 1, 0));     // idle lanes re-read a valid word; their mask is 0
-  u32 row = 0;
-  const int c4 = c & ~3;
-  int i = 0;
-#pragma unroll 1
-  for (; i < c4; i += 4) {
-    const u32 t0 = col[i * c], t1 = col[(i + 1) * c], t2 = col[(i + 2) * c], t3 = col[(i + 3) * c];
-    const u32 b0 = __ballot_sync(FULL, t0 & nb.m), b1 = __ballot_sync(FULL, t1 & nb.m);
-    const u32 b2 = __ballot_sync(FULL, t2 & nb.m), b3 = __ballot_sync(FULL, t3 & nb.m);
-    const int d = lane - i;
-    if ((u32)d < 4u) row = d == 0 ? b0 : d == 1 ? b1 : d == 2 ? b2 : b3;
-  }
-  for (; i < c; i++) {
-    const u32 b = __ballot_sync(FULL, col[i * c] & nb.m);
-    if (lane == i) row = b;
-  }
-  A[lane] = row;
-  g.c = c;
-  g.outU = __ballot_sync(FULL, nb.lu & nb.m);
-  g.outV = __ballot_sync(FULL, nb.lv & nb.m);
-  g.inU = __ballot_sync(FULL, nb.m && ((nb.xu >> (u & 31)) & 1u));
-  g.inV = __ballot_sync(FULL, nb.m && ((nb.xv >> (v & 31)) & 1u));
-  __syncwarp();
-}
 
 // the double move's count of the coming edge u->v sees the graph without delme = d0->d1: take that bit
 // out of the gathered view (list/A/ga are the coming pair's)
@@ -652,6 +597,49 @@ __device__ __forceinline__ void hot_drop_edge(const u32* list, int c, u32 u, u32
   else if (ip >= 0) { if (iq == -2) g.inU &= ~(1u << ip); else g.inV &= ~(1u << ip); }
   else if (iq >= 0) { if (ip == -2) g.outU &= ~(1u << iq); else g.outV &= ~(1u << iq); }
 }
+// ---- hot path from the static clique index: the pair's triangles and 4-cliques are known slots, a
+//      proposal only looks up their orientation bits (two bits per adjacent pair, 32-bit words) ----
+struct OriReq { u32 sU, sV, wu, wv, e0, w0, e1, w1; };
+// issues every load of the pair (static entries, then the orientation words they name); u is the
+// pair's bigger vertex iff uBig
+__device__ __forceinline__ void idx_issue(const EnsParams& p, const u32* ori, u32 o, int c, u32 k4o, int m, bool uBig,
+                                          int lane, OriReq& r) {
+  r.sU = r.sV = r.wu = r.wv = r.e0 = r.w0 = r.e1 = r.w1 = 0;
+  if (lane < c) { const uint2 t = __ldg(&p.tri[o + lane]); r.sU = uBig ? t.x : t.y; r.sV = uBig ? t.y : t.x; }
+  if (lane < m) r.e0 = __ldg(&p.k4[k4o + lane]);
+  if (lane + 32 < m) r.e1 = __ldg(&p.k4[k4o + 32 + lane]);
+  if (lane < c) { r.wu = __ldcg(&ori[r.sU >> 5]); r.wv = __ldcg(&ori[r.sV >> 5]); }
+  if (lane < m) r.w0 = __ldcg(&ori[r.e0 >> 15]);
+  if (lane + 32 < m) r.w1 = __ldcg(&ori[r.e1 >> 15]);
+}
+// entry e = slot(w_i -> w_j) << 10 | j << 5 | i; w = the orientation word of that slot
+__device__ __forceinline__ void k4_scatter(u32 e, u32 w, u32* A32) {
+  const u32 s = e >> 10, i = e & 31, j = (e >> 5) & 31;
+  const u32 two = w >> (s & 30), d = s & 1;
+  if ((two >> d) & 1u) atomicOr(&A32[i], 1u << j);
+  if ((two >> (d ^ 1)) & 1u) atomicOr(&A32[j], 1u << i);
+}
+__device__ __forceinline__ G32 idx_finish(const EnsParams& p, const u32* ori, u32 k4o, int m, const OriReq& r, u32* A32,
+                                          int lane) {
+  A32[lane] = 0;
+  __syncwarp();
+  if (lane < m) k4_scatter(r.e0, r.w0, A32);
+  if (lane + 32 < m) k4_scatter(r.e1, r.w1, A32);
+  for (int t = 64 + lane; t < m; t += 32) {
+    const u32 e = __ldg(&p.k4[k4o + t]);
+    k4_scatter(e, __ldcg(&ori[e >> 15]), A32);
+  }
+  const u32 tu = r.wu >> (r.sU & 30), tv = r.wv >> (r.sV & 30);   // lanes past c hold 0: never vote
+  const u32 du = r.sU & 1, dv = r.sV & 1;
+  G32 g;
+  g.inU = __ballot_sync(FULL, (tu >> du) & 1u);
+  g.outU = __ballot_sync(FULL, (tu >> (du ^ 1)) & 1u);
+  g.inV = __ballot_sync(FULL, (tv >> dv) & 1u);
+  g.outV = __ballot_sync(FULL, (tv >> (dv ^ 1)) & 1u);
+  __syncwarp();
+  return g;
+}
+
 // Tagged graph.  A common neighbour w of u and v can stand before u (tag X: w->u, w->v), between them
 // (Y: u->w->v; Y2: v->w->u, the other direction of the same pair, used by a flip) or after v (Z).
 // A vertex gets one bit per tag it carries: its first tag on its own bit (< c), further tags on
@@ -761,6 +749,7 @@ __device__ __noinline__ u64 full_path(const EnsParams& p, u32* cb, unsigned char
   const WarpSmem s = carve(wb, p.Kcap, p.KWcap);
   Chain c;
   c.adj = (u64*)cb; c.items = cb + p.off_items; c.pos = cb + p.off_pos; c.dbl = cb + p.off_dbl; c.dblpos = cb + p.off_dblpos;
+  c.ori = cb + p.off_ori;
   c.E = 0; c.ND = 0;
   if (lane == 0) { s.edits[0] = slot0; s.edits[1] = add0; s.edits[2] = slot1; s.edits[3] = add1; }
   __syncwarp();
@@ -813,14 +802,23 @@ __device__ __forceinline__ void update_containers(const EnsParams& p, u32* cb, i
     }
   }
 }
-// adjacency bits of an accepted move: gu->gv leaves, cu->cv comes.  Plain stores: the rows are read
-// through this SM's L1 (cp.async.ca), which its own stores keep coherent.
-__device__ __forceinline__ void update_adjacency(u32* cb, u32 W32, u32 gu, u32 gv, u32 cu, u32 cv, int lane) {
+// adjacency bits of an accepted move (cold path): the edge of slot `sgo` = gu->gv leaves, `scome` = cu->cv
+// comes; the orientation bits follow.  red = false: plain stores (the row-gather hot path reads the rows
+// through this SM's L1, which its own stores keep coherent); red = true: L2 atomics, as the index hot
+// path updates the rows (every reader of the rows then uses ld.cg).
+__device__ __forceinline__ void update_adjacency(const EnsParams& p, u32* cb, u32 W32, u32 gu, u32 gv, u32 cu, u32 cv,
+                                                 u32 sgo, u32 scome, bool red, int lane) {
   if (lane == 0) {
     const u32 igo = gu * W32 + (gv >> 5), icome = cu * W32 + (cv >> 5);
     const u32 mgo = 1u << (gv & 31), mcome = 1u << (cv & 31);
-    if (igo == icome) cb[igo] = (cb[igo] & ~mgo) | mcome;
+    if (red) { atomicAnd(&cb[igo], ~mgo); atomicOr(&cb[icome], mcome); }
+    else if (igo == icome) cb[igo] = (cb[igo] & ~mgo) | mcome;
     else { cb[igo] &= ~mgo; cb[icome] |= mcome; }
+    u32* const ori = cb + p.off_ori;
+    const u32 wg = sgo >> 5, wc = scome >> 5;
+    const u32 og = __ldcg(&ori[wg]) & ~(1u << (sgo & 31));
+    if (wg == wc) ori[wg] = og | (1u << (scome & 31));
+    else { ori[wg] = og; ori[wc] = __ldcg(&ori[wc]) | (1u << (scome & 31)); }
   }
 }
 
@@ -828,7 +826,7 @@ __device__ __forceinline__ void update_adjacency(u32* cb, u32 W32, u32 gu, u32 g
 // two-slot lists (32 < c <= 64), more than 32 tagged copies, simplices beyond the register levels,
 // lists beyond FAST_C (full path) or a forced full path.  Reads and writes the chain's state in HBM.
 __device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned char* wb, int lane, fcm_trace_rec* tr_out,
-                                      int force_full) {
+                                      int force_full, bool red) {
   const u32* park = (const u32*)(wb + SM_PARK);
   u64* const sdeep = (u64*)(wb + SM_DEEP);
   int* const sflag = (int*)(wb + SM_FLAG);
@@ -870,7 +868,7 @@ __device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned ch
   if (err) { if (lane == 0) st->err = err; return err; }
   const bool ok = bounds_ok(p, fnew, lane);
   update_containers(p, cb, kind, ok, slot, delme, idx, didx, dpair, last, qpos, E, ND, lane);
-  if (ok) update_adjacency(cb, W32, kind == 0 ? ta : tdm0, kind == 0 ? tb : tdm1, tb, ta, lane);
+  if (ok) update_adjacency(p, cb, W32, kind == 0 ? ta : tdm0, kind == 0 ? tb : tdm1, tb, ta, kind == 0 ? slot : delme, slot ^ 1, red, lane);
   __syncwarp();
   if (ok) st->flag_count[lane] = fnew;
   if (lane == 0) {
@@ -887,6 +885,9 @@ __device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned ch
   return 0;
 }
 
+// IDX = true: the hot path reads the static clique index + the chain's orientation bits;
+// IDX = false: it gathers from the chain's adjacency rows (graphs too large for the index).
+template <bool IDX>
 __global__ void __launch_bounds__(128, 7)
 chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ trace, u32 trace_chain,
                   u32 smem_per_warp, int force_full) {
@@ -906,11 +907,12 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
   u32* const stile = (u32*)(wb + SM_TILE);
   ChainState* const st = &p.st[chain];
   if (st->err) return;
-  // the chain's block: adjacency rows (as 32-bit words) | items | pos | dbl | dblpos
+  // the chain's block: adjacency rows (as 32-bit words) | items | pos | dbl | dblpos | ori
   u32* const cb = (u32*)p.adj + (u64)chain * p.stride32;
 #define ITEMS(i) cb[p.off_items + (i)]
 #define POS(i) cb[p.off_pos + (i)]
 #define DBL(i) cb[p.off_dbl + (i)]
+#define ORI(i) cb[p.off_ori + (i)]
   const u32 E = st->E, ND = st->ND;                    // both moves keep |E| and the number of double pairs
   const u32 W32 = 2 * p.W;
   if (lane < 12) sflag[lane] = 0;
@@ -940,19 +942,26 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
       bool live = false;                                // a non-empty transition
       bool sampled_edge = false;
       u32 idx = 0, slot = 0, didx = 0, dpair = 0, delme = 0, last = 0, qpos = 0;
-      u32 oA = 0, oD = 0;
-      int cA = 0, cD = 0;
+      u32 oA = 0, oD = 0, kA = 0, kD = 0, oriA = 0, oriD = 0;
+      int cA = 0, cD = 0, mA = 0, mD = 0;
       uint2 abA = make_uint2(0, 0), abD = make_uint2(0, 0);
       if (kind == 0) {
         if (E) {
           idx = (u32)gen_range(g, E);
           slot = ITEMS(idx);
           last = ITEMS(E - 1);
-          const u32 rev = POS(slot ^ 1);
-          abA = __ldg(&p.pair_ab[slot >> 1]);
-          oA = __ldg(&p.nb_off[slot >> 1]);
-          cA = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - oA);
-          live = rev == FCM_NONE;                       // the reverse edge exists: empty transition
+          if constexpr (IDX) {
+            oriA = __ldcg(&ORI(slot >> 5));
+            const uint4 i0 = __ldg(&p.pinfo[2 * (slot >> 1)]), i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]);
+            abA = make_uint2(i0.x, i0.y); oA = i0.z; kA = i0.w; cA = (int)i1.x; mA = (int)i1.y;
+            live = !((oriA >> ((slot ^ 1) & 31)) & 1u);     // the reverse edge exists: empty transition
+          } else {
+            const u32 rev = POS(slot ^ 1);
+            abA = __ldg(&p.pair_ab[slot >> 1]);
+            oA = __ldg(&p.nb_off[slot >> 1]);
+            cA = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - oA);
+            live = rev == FCM_NONE;
+          }
           sampled_edge = true;
         }
       } else if (ND) {
@@ -961,15 +970,30 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
         idx = (u32)gen_range(g, E);                     // the next draw does not depend on the loaded pair
         dpair = DBL(didx);
         slot = ITEMS(idx);
-        abD = __ldg(&p.pair_ab[dpair]);
-        oD = __ldg(&p.nb_off[dpair]);
-        cD = (int)(__ldg(&p.nb_off[dpair + 1]) - oD);
+        if constexpr (IDX) {
+          oriD = __ldcg(&ORI(dpair >> 4));
+          const uint4 i0 = __ldg(&p.pinfo[2 * dpair]), i1 = __ldg(&p.pinfo[2 * dpair + 1]);
+          abD = make_uint2(i0.x, i0.y); oD = i0.z; kD = i0.w; cD = (int)i1.x; mD = (int)i1.y;
+        } else {
+          abD = __ldg(&p.pair_ab[dpair]);
+          oD = __ldg(&p.nb_off[dpair]);
+          cD = (int)(__ldg(&p.nb_off[dpair + 1]) - oD);
+        }
         for (;;) {
-          const u32 rev = POS(slot ^ 1);
-          abA = __ldg(&p.pair_ab[slot >> 1]);
-          oA = __ldg(&p.nb_off[slot >> 1]);
-          cA = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - oA);
-          if (rev == FCM_NONE) break;
+          bool single;
+          if constexpr (IDX) {
+            oriA = __ldcg(&ORI(slot >> 5));
+            const uint4 i0 = __ldg(&p.pinfo[2 * (slot >> 1)]), i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]);
+            abA = make_uint2(i0.x, i0.y); oA = i0.z; kA = i0.w; cA = (int)i1.x; mA = (int)i1.y;
+            single = !((oriA >> ((slot ^ 1) & 31)) & 1u);
+          } else {
+            const u32 rev = POS(slot ^ 1);
+            abA = __ldg(&p.pair_ab[slot >> 1]);
+            oA = __ldg(&p.nb_off[slot >> 1]);
+            cA = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - oA);
+            single = rev == FCM_NONE;
+          }
+          if (single) break;
           idx = (u32)gen_range(g, E);
           slot = ITEMS(idx);
         }
@@ -993,44 +1017,74 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
       u32 vgo = 0, vcome = 0;
       if (live) {
         const int cB = kind == 0 ? 0 : cD;
-        const int wordsA = hot_tile_words(cA);
         cold = force_full || cA > NARROW_C || cB > NARROW_C;
         int cnt[DELTA_SD];
 #pragma unroll
         for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
         int tri = 0, top = 1;
         if (!cold) {
-          vgo = cb[igo]; vcome = cb[icome];             // early: rewritten on accept without a stall
-          // both gathers are in flight together when the tile holds both, else one after the other
-          const bool both = wordsA + hot_tile_words(cB) <= TILE_WORDS;
-          u32* const tileD = both ? stile + wordsA : stile;
-          const u32 xA = lane < cA ? __ldg(&p.nb_list[oA + lane]) : 0u;
-          const u32 xD = lane < cB ? __ldg(&p.nb_list[oD + lane]) : 0u;
-          hot_issue(cb, W32, xA, cA, tb, ta, scv, srowoff, stile, lane);
-          if (kind == 1 && both) hot_issue(cb, W32, xD, cD, tdm0, tdm1, scv2, srowoff + 32, tileD, lane);
           Tagged t;
+          if constexpr (IDX) {
+            // every load of both pairs is in flight before the first one is used
+            u32* const ori = cb + p.off_ori;
+            OriReq rA, rD;
+            idx_issue(p, ori, oA, cA, kA, mA, tb == abA.x, lane, rA);
+            if (kind == 1) {
+              idx_issue(p, ori, oD, cD, kD, mD, tdm0 == abD.x, lane, rD);
+              // the vertex lists are only needed to take delme out of the coming pair's view and for K
+              scv[lane] = lane < cA ? __ldg(&p.nb_list[oA + lane]) : 0u;
+              scv2[lane] = lane < cD ? __ldg(&p.nb_list[oD + lane]) : 0u;
+            }
 #pragma unroll 1
-          for (int ph = 0; ph < 2 && !cold; ph++) {
-            const int sign = ph ? -1 : 1;
-            if (ph == 0 || kind == 1) {
-              if (ph == 1 && !both) hot_issue(cb, W32, xD, cD, tdm0, tdm1, scv2, srowoff + 32, tileD, lane);
-              if (ph == 0 && kind == 1 && both) cp_async_wait<1>(); else cp_async_wait<0>();
+            for (int ph = 0; ph < 2 && !cold; ph++) {
+              const int sign = ph ? -1 : 1;
+              if (ph == 0 || kind == 1) {
+                G32 ga = ph == 0 ? idx_finish(p, ori, kA, mA, rA, sA32, lane) : idx_finish(p, ori, kD, mD, rD, sA32, lane);
+                if (ph == 0 && kind == 1) hot_drop_edge(scv, cA, tb, ta, tdm0, tdm1, sA32, lane, ga);
+                if (!hot_tag(ga, ph ? cD : cA, kind == 0, sA32, sAT, ssrc, lane, t)) { cold = true; break; }
+              }
+              const u32 roots = (ph == 1 && kind == 0) ? t.go : t.come;
+              tri += sign * __popc(roots);
+              hot_count(roots, t.row, sAT, lane, sign, cnt, &sflag[FL_OVF]);
+              if (ph == 0) {
+                const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : roots ? 2 : 1;
+                top = __reduce_max_sync(FULL, mytop);
+              }
               __syncwarp();
-              G32 ga = ph == 0 ? hot_finish(stile, cA, scv, tb, ta, sA32, lane)
-                               : hot_finish(tileD, cD, scv2, tdm0, tdm1, sA32, lane);
-              if (ph == 0 && kind == 1) hot_drop_edge(scv, cA, tb, ta, tdm0, tdm1, sA32, lane, ga);
-              if (!hot_tag(ga, ph ? cD : cA, kind == 0, sA32, sAT, ssrc, lane, t)) { cold = true; break; }
             }
-            const u32 roots = (ph == 1 && kind == 0) ? t.go : t.come;
-            tri += sign * __popc(roots);
-            hot_count(roots, t.row, sAT, lane, sign, cnt, &sflag[FL_OVF]);
-            if (ph == 0) {
-              const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : roots ? 2 : 1;
-              top = __reduce_max_sync(FULL, mytop);
+          } else {
+            const int wordsA = hot_tile_words(cA);
+            vgo = cb[igo]; vcome = cb[icome];             // early: rewritten on accept without a stall
+            // both gathers are in flight together when the tile holds both, else one after the other
+            const bool both = wordsA + hot_tile_words(cB) <= TILE_WORDS;
+            u32* const tileD = both ? stile + wordsA : stile;
+            const u32 xA = lane < cA ? __ldg(&p.nb_list[oA + lane]) : 0u;
+            const u32 xD = lane < cB ? __ldg(&p.nb_list[oD + lane]) : 0u;
+            hot_issue(cb, W32, xA, cA, tb, ta, scv, srowoff, stile, lane);
+            if (kind == 1 && both) hot_issue(cb, W32, xD, cD, tdm0, tdm1, scv2, srowoff + 32, tileD, lane);
+#pragma unroll 1
+            for (int ph = 0; ph < 2 && !cold; ph++) {
+              const int sign = ph ? -1 : 1;
+              if (ph == 0 || kind == 1) {
+                if (ph == 1 && !both) hot_issue(cb, W32, xD, cD, tdm0, tdm1, scv2, srowoff + 32, tileD, lane);
+                if (ph == 0 && kind == 1 && both) cp_async_wait<1>(); else cp_async_wait<0>();
+                __syncwarp();
+                G32 ga = ph == 0 ? hot_finish(stile, cA, scv, tb, ta, sA32, lane)
+                                 : hot_finish(tileD, cD, scv2, tdm0, tdm1, sA32, lane);
+                if (ph == 0 && kind == 1) hot_drop_edge(scv, cA, tb, ta, tdm0, tdm1, sA32, lane, ga);
+                if (!hot_tag(ga, ph ? cD : cA, kind == 0, sA32, sAT, ssrc, lane, t)) { cold = true; break; }
+              }
+              const u32 roots = (ph == 1 && kind == 0) ? t.go : t.come;
+              tri += sign * __popc(roots);
+              hot_count(roots, t.row, sAT, lane, sign, cnt, &sflag[FL_OVF]);
+              if (ph == 0) {
+                const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : roots ? 2 : 1;
+                top = __reduce_max_sync(FULL, mytop);
+              }
+              __syncwarp();
             }
-            __syncwarp();
+            cp_async_wait<0>();
           }
-          cp_async_wait<0>();
           if (sflag[FL_OVF]) { cold = true; __syncwarp(); if (lane == 0) sflag[FL_OVF] = 0; }
         }
         if (cold) {
@@ -1064,12 +1118,31 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
       if (live) {
         update_containers(p, cb, kind, ok, slot, delme, idx, didx, dpair, last, qpos, E, ND, lane);
         if (ok) {
-          // adjacency bits: gu->gv leaves, tb->ta comes (plain stores of the words read above: the
-          // rows are read through this SM's L1, which its own stores keep coherent)
+          // adjacency bits: gu->gv leaves, tb->ta comes
           if (lane == 0) {
             const u32 mgo = 1u << (gv & 31), mcome = 1u << (ta & 31);
-            if (igo == icome) cb[igo] = (vgo & ~mgo) | mcome;
-            else { cb[igo] = vgo & ~mgo; cb[icome] = vcome | mcome; }
+            if constexpr (IDX) {
+              // rows: fire-and-forget L2 atomics (only the cold path reads them, with ld.cg); orientation
+              // bits: plain stores of the words read while sampling
+              atomicAnd(&cb[igo], ~mgo); atomicOr(&cb[icome], mcome);
+              if (kind == 0) ORI(slot >> 5) = oriA ^ (3u << (slot & 30));
+              else {
+                const u32 wa = slot >> 5, wd = delme >> 5;
+                const u32 ma = 1u << ((slot ^ 1) & 31), md = 1u << (delme & 31);
+                if (wa == wd) ORI(wa) = (oriA | ma) & ~md;
+                else { ORI(wa) = oriA | ma; ORI(wd) = oriD & ~md; }
+              }
+            } else {
+              // plain stores of the words read above: the rows are read through this SM's L1, which its
+              // own stores keep coherent
+              if (igo == icome) cb[igo] = (vgo & ~mgo) | mcome;
+              else { cb[igo] = vgo & ~mgo; cb[icome] = vcome | mcome; }
+              u32* const ori = cb + p.off_ori;
+              const u32 sg = kind == 0 ? slot : delme, sc = slot ^ 1;
+              const u32 og = ori[sg >> 5] & ~(1u << (sg & 31));
+              if ((sg >> 5) == (sc >> 5)) ori[sg >> 5] = og | (1u << (sc & 31));
+              else { ori[sg >> 5] = og; ori[sc >> 5] |= 1u << (sc & 31); }
+            }
           }
           fc = fnew;
         }
@@ -1093,12 +1166,13 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
     }
     __syncwarp();
     if (err || !cold) break;
-    if (cold_step(p, chain, wb, lane, trace ? trace + step : nullptr, force_full)) break;
+    if (cold_step(p, chain, wb, lane, trace ? trace + step : nullptr, force_full, IDX)) break;
     step++;
   }
 #undef ITEMS
 #undef POS
 #undef DBL
+#undef ORI
 }
 
 // State::apply_transition / revert_transition with explicit edits on one chain (one warp).
@@ -1116,6 +1190,7 @@ __global__ void chain_apply_kernel(const EnsParams p, u32 chain, const u32* __re
   c.pos = p.pos + (u64)chain * p.stride32;
   c.dbl = p.dbl + (u64)chain * p.stride32;
   c.dblpos = p.dblpos + (u64)chain * p.stride32;
+  c.ori = p.ori + (u64)chain * p.stride32;
   c.E = st->E; c.ND = st->ND;
   u64 fc = st->flag_count[lane];
   int len = st->fc_len;
@@ -1191,20 +1266,31 @@ int fcm_chain_launch_replicate(fcm_ensemble* e) {
   return FCM_OK;
 }
 
-int fcm_chain_launch_step(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
-  const int wpb = e->warps_per_block;
-  size_t smem = e->smem_per_warp * wpb;
-  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  u32 blocks = (e->p.nchains + wpb - 1) / wpb;
+template <bool IDX>
+static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
+  const EnsParams& p = e->p;
+  const size_t per_warp = chain_smem_per_warp_mode(p.Kcap, p.KWcap, !IDX);
+  int wpb = 4;
+  while (wpb > 1 && per_warp * wpb > e->ctx->smem_optin) wpb >>= 1;
+  if (per_warp * wpb > e->ctx->smem_optin) { fcm_set_error("neighbourhood tile does not fit shared memory"); return FCM_ELIMIT; }
+  const size_t smem = per_warp * wpb;
+  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  const u32 blocks = (p.nchains + wpb - 1) / wpb;
   const u64 chunk = 1ULL << 24;                         // the kernel's per-launch counters are 32-bit
   for (u64 done = 0; done < nsteps; done += chunk) {
     const u32 now = (u32)std::min<u64>(chunk, nsteps - done);
-    chain_step_kernel<<<blocks, wpb * 32, smem, e->ctx->stream>>>(e->p, now, trace_dev ? trace_dev + done : nullptr,
-                                                                trace_chain, (u32)e->smem_per_warp, e->force_full);
+    chain_step_kernel<IDX><<<blocks, wpb * 32, smem, e->ctx->stream>>>(p, now, trace_dev ? trace_dev + done : nullptr,
+                                                                     trace_chain, (u32)per_warp, e->force_full);
     e->ctx->launches++;
   }
   FCM_CUDA(cudaGetLastError());
   return FCM_OK;
+}
+
+int fcm_chain_launch_step(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
+  if (e->have_index && !e->force_rows) return launch_step_mode<true>(e, nsteps, trace_dev, trace_chain);
+  return launch_step_mode<false>(e, nsteps, trace_dev, trace_chain);
 }
 
 int fcm_chain_launch_apply(fcm_ensemble* e, u32 chain, int nedits, int mode) {

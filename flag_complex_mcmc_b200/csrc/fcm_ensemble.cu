@@ -170,6 +170,78 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     for (auto& t : th) t.join();
   }
   p.maxc = maxc;
+
+  // ---- static clique index (hot path of chain_step_kernel): for every pair the slots of the edges
+  //      between its common neighbours and its endpoints (triangles) and of the edges among its
+  //      common neighbours (4-cliques).  The undirected graph never changes under the moves
+  //      (src/lib.rs:292-325), so a proposal only has to look up the ORIENTATION of these slots. ----
+  std::vector<uint4> pinfo;
+  std::vector<uint2> tri;
+  std::vector<u32> k4;
+  {
+    const u64 nslots_ = 2 * p.npairs;
+    u64 work = 0;
+    for (u64 q = 0; q < p.npairs; q++) { u64 c = nb_off[q + 1] - nb_off[q]; if (c <= 32) work += c * c; }
+    const char* off_env = getenv("FCM_NO_CLIQUE_INDEX");
+    bool build = p.npairs > 0 && nslots_ < (1ULL << 22) && work < (1ULL << 32) && !(off_env && off_env[0] == '1');
+    if (build) {
+      // pair id of (v, und[v][k]), parallel to the sorted neighbour lists
+      std::vector<std::vector<u32>> undpid(n);
+      for (u32 v = 0; v < n; v++) undpid[v].resize(und[v].size());
+      for (u64 q = 0; q < p.npairs; q++) {
+        const uint2 ab = pair_ab[q];
+        undpid[ab.x][std::lower_bound(und[ab.x].begin(), und[ab.x].end(), ab.y) - und[ab.x].begin()] = (u32)q;
+        undpid[ab.y][std::lower_bound(und[ab.y].begin(), und[ab.y].end(), ab.x) - und[ab.y].begin()] = (u32)q;
+      }
+      auto slot_of = [&](u32 from, u32 to) -> u32 {      // FCM_NONE when not adjacent
+        const std::vector<u32>& L = und[from];
+        auto it = std::lower_bound(L.begin(), L.end(), to);
+        if (it == L.end() || *it != to) return FCM_NONE;
+        return 2 * undpid[from][it - L.begin()] + (from > to ? 0u : 1u);
+      };
+      tri.resize(nb_list.size());
+      std::vector<u64> k4_off(p.npairs + 1, 0);
+      std::vector<std::vector<u32>> k4_part(nthreads);
+      std::vector<std::vector<u32>> k4_cnt(nthreads);
+      // contiguous ranges of pairs per thread so that the per-thread entry lists concatenate in pair order
+      auto range = [&](int t) { return std::make_pair(p.npairs * t / nthreads, p.npairs * (t + 1) / nthreads); };
+      std::vector<std::thread> th;
+      for (int t = 0; t < nthreads; t++) th.emplace_back([&, t]() {
+        auto r = range(t);
+        for (u64 q = r.first; q < r.second; q++) {
+          const uint2 ab = pair_ab[q];
+          const u64 o = nb_off[q];
+          const u32 c = (u32)(nb_off[q + 1] - o);
+          for (u32 i = 0; i < c; i++) tri[o + i] = make_uint2(slot_of(nb_list[o + i], ab.x), slot_of(nb_list[o + i], ab.y));
+          u32 m = 0;
+          if (c <= 32)
+            for (u32 i = 0; i < c; i++)
+              for (u32 j = i + 1; j < c; j++) {
+                const u32 sl = slot_of(nb_list[o + i], nb_list[o + j]);
+                if (sl != FCM_NONE) { k4_part[t].push_back((sl << 10) | (j << 5) | i); m++; }
+              }
+          k4_cnt[t].push_back(m);
+        }
+      });
+      for (auto& t : th) t.join();
+      u64 tot = 0;
+      for (int t = 0; t < nthreads; t++) {
+        auto r = range(t);
+        for (u64 q = r.first; q < r.second; q++) { k4_off[q] = tot; tot += k4_cnt[t][q - r.first]; }
+      }
+      k4_off[p.npairs] = tot;
+      if (tot < 0xffffffffULL) {
+        k4.reserve(tot + 1);
+        for (int t = 0; t < nthreads; t++) k4.insert(k4.end(), k4_part[t].begin(), k4_part[t].end());
+        pinfo.resize(2 * p.npairs);
+        for (u64 q = 0; q < p.npairs; q++) {
+          pinfo[2 * q] = make_uint4(pair_ab[q].x, pair_ab[q].y, (u32)nb_off[q], (u32)k4_off[q]);
+          pinfo[2 * q + 1] = make_uint4((u32)(nb_off[q + 1] - nb_off[q]), (u32)(k4_off[q + 1] - k4_off[q]), 0, 0);
+        }
+        e->have_index = 1;
+      } else tri.clear();
+    }
+  }
   u32 kneed = 2 * maxc + 4;                            // double-edge move: two pairs + four endpoints
   p.Kcap = std::min<u32>(std::max<u32>(kneed, 8), 512);
   u32 kw = (p.Kcap + 63) / 64;
@@ -182,7 +254,7 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   // ---- device memory ----
   const u64 nslots = 2 * p.npairs;
   const u64 adjw = (u64)n * p.W;
-  e->bytes_per_chain = adjw * 8 + nslots * 8 + p.npairs * 8 + sizeof(ChainState);   // before padding
+  e->bytes_per_chain = adjw * 8 + nslots * 8 + p.npairs * 8 + (nslots + 7) / 8 + sizeof(ChainState);   // before padding
   uint2* d_pair; u32* d_off; u32* d_list;
   if (nb_off[p.npairs] > 0xffffffffULL) { fcm_set_error("common-neighbour lists hold %llu entries (> 2^32)", (unsigned long long)nb_off[p.npairs]); return fail(FCM_ELIMIT); }
   std::vector<u32> nb_off32(nb_off.begin(), nb_off.end());
@@ -191,7 +263,8 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   if ((rc = dev_alloc(e, &d_list, nb_list.size()))) return fail(rc);
   {
     // one block per chain: [adj | items | pos | dbl | dblpos], block stride padded to 128 bytes
-    const u64 w_adj = adjw * 2, w_total = w_adj + 2 * nslots + 2 * p.npairs;
+    const u64 w_ori = (nslots + 31) / 32 + 1;
+    const u64 w_adj = adjw * 2, w_total = w_adj + 2 * nslots + 2 * p.npairs + w_ori;
     if (w_total > 0xfffffff0ULL) { fcm_set_error("graph too large: a chain's state exceeds 2^32 words"); return fail(FCM_ELIMIT); }
     p.stride32 = (w_total + 31) & ~31ULL;
     p.off_items = (u32)w_adj; p.off_pos = (u32)(w_adj + nslots);
@@ -199,7 +272,26 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     u32* blk = nullptr;
     if ((rc = dev_alloc(e, &blk, p.stride32 * nchains))) return fail(rc);
     p.adj = (u64*)blk; p.items = blk + p.off_items; p.pos = blk + p.off_pos;
-    p.dbl = blk + p.off_dbl; p.dblpos = blk + p.off_dblpos;
+    p.off_ori = (u32)(w_adj + 2 * nslots + 2 * p.npairs);
+    p.dbl = blk + p.off_dbl; p.dblpos = blk + p.off_dblpos; p.ori = blk + p.off_ori;
+    std::vector<u32> ori(w_ori, 0);
+    for (u64 sl = 0; sl < nslots; sl++) if (pos[sl] != FCM_NONE) ori[sl >> 5] |= 1u << (sl & 31);
+    cudaError_t ce = cudaMemcpyAsync(p.ori, ori.data(), w_ori * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(ctx->stream);   // `ori` is a local
+    if (ce != cudaSuccess) { fcm_set_error("upload of the orientation bits failed: %s", cudaGetErrorString(ce)); return fail(FCM_ECUDA); }
+  }
+  if (e->have_index) {
+    uint4* d_pinfo; uint2* d_tri; u32* d_k4;
+    if ((rc = dev_alloc(e, &d_pinfo, pinfo.size()))) return fail(rc);
+    if ((rc = dev_alloc(e, &d_tri, tri.size()))) return fail(rc);
+    if ((rc = dev_alloc(e, &d_k4, k4.size()))) return fail(rc);
+    cudaError_t ce = cudaMemcpyAsync(d_pinfo, pinfo.data(), pinfo.size() * sizeof(uint4), cudaMemcpyHostToDevice, ctx->stream);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(d_tri, tri.data(), tri.size() * sizeof(uint2), cudaMemcpyHostToDevice, ctx->stream);
+    if (ce == cudaSuccess && !k4.empty()) ce = cudaMemcpyAsync(d_k4, k4.data(), k4.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(ctx->stream);
+    if (ce != cudaSuccess) { fcm_set_error("upload of the clique index failed: %s", cudaGetErrorString(ce)); return fail(FCM_ECUDA); }
+    p.pinfo = d_pinfo; p.tri = d_tri; p.k4 = d_k4;
+    e->index_bytes = pinfo.size() * sizeof(uint4) + tri.size() * sizeof(uint2) + k4.size() * 4;
   }
   if ((rc = dev_alloc(e, &p.st, (size_t)nchains))) return fail(rc);
   if ((rc = dev_alloc(e, &e->edit_dev, (size_t)FCM_MAXEDIT * 2))) return fail(rc);
@@ -242,8 +334,9 @@ extern "C" int fcm_ensemble_set_bounds(fcm_ensemble* e, const uint64_t* mn, int 
 
 extern "C" int fcm_ensemble_set_kernel(fcm_ensemble* e, int kind) {
   REQUIRE(e, "ensemble is null");
-  REQUIRE(kind == 0 || kind == 1, "kernel kind must be 0 (auto: delta path) or 1 (full pre/post counts)");
-  e->force_full = kind;
+  REQUIRE(kind >= 0 && kind <= 2, "kernel kind must be 0 (auto), 1 (full pre/post counts) or 2 (delta path from the adjacency rows)");
+  e->force_full = kind == 1;
+  e->force_rows = kind == 2;
   return FCM_OK;
 }
 

@@ -79,15 +79,24 @@ struct EnsParams {
   const uint2* pair_ab;             // pair id -> (big, small)
   const u32* nb_off;                // npairs + 1 (total list length < 2^32 is checked at create)
   const u32* nb_list;               // common undirected neighbours, ascending
-  // per chain: one block of stride32 32-bit words = [adj | items | pos | dbl | dblpos]; the pointers
+  // static clique index (null when not built: graph too large for it, see fcm_ensemble.cu).  For the
+  // pair (big,small) with common neighbours w_0..w_{c-1}:
+  //   pinfo[2*pair]   = (big, small, nb_off, k4_off)      pinfo[2*pair+1] = (c, m, 0, 0)
+  //   tri[nb_off + i] = (slot of w_i -> big, slot of w_i -> small)
+  //   k4[k4_off + e]  = slot of w_i -> w_j << 10 | j << 5 | i   for the m adjacent i < j (lists of <= 32 only)
+  const uint4* pinfo;
+  const uint2* tri;
+  const u32* k4;
+  // per chain: one block of stride32 32-bit words = [adj | items | pos | dbl | dblpos | ori]; the pointers
   // below are chain 0's, chain k's are stride32 words further (one base register per chain)
   u64 stride32;
-  u32 off_items, off_pos, off_dbl, off_dblpos;   // word offsets inside a block (adj is at 0)
+  u32 off_items, off_pos, off_dbl, off_dblpos, off_ori;   // word offsets inside a block (adj is at 0)
   u64* adj;                         // n * W        packed 64-bit out-neighbour rows
   u32* items;                       // 2*npairs     directed-edge slots in container order
   u32* pos;                         // 2*npairs     slot -> index in items | NONE
   u32* dbl;                         // npairs       pair ids in container order
   u32* dblpos;                      // npairs
+  u32* ori;                         // ceil(2*npairs/32)  orientation bits: bit `slot` = that directed edge exists
   ChainState* st;                   // nchains
   // settings
   u64 bmin[FCM_MAXB], bmax[FCM_MAXB];
@@ -106,6 +115,9 @@ struct fcm_ensemble {
   size_t smem_per_warp = 0;
   int warps_per_block = 4;
   int force_full = 0;                     // 1: every proposal through the full pre/post count path
+  int force_rows = 0;                     // 1: hot path gathers from the adjacency rows even when the clique index exists
+  int have_index = 0;                     // the static clique index was built
+  u64 index_bytes = 0;
   fcm_trace_rec* trace_dev = nullptr;
   u64 trace_cap = 0;
   u32* edit_dev = nullptr;                // FCM_MAXEDIT * 2 (slot, add)

@@ -304,7 +304,9 @@ class MCMCSampler:
         self.sample_distance = int(sample_distance)
 
     def set_kernel(self, kind):
-        """0 = delta path (default), 1 = full pre/post neighbourhood counts; identical results."""
+        """0 = delta path, from the static clique index + orientation bits when it was built (default),
+        1 = full pre/post neighbourhood counts, 2 = delta path gathered from the adjacency rows;
+        identical results."""
         check(lib().fcm_ensemble_set_kernel(self.h, int(kind)))
 
     # -- stepping --

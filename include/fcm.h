@@ -123,9 +123,12 @@ int fcm_ensemble_set_bounds(fcm_ensemble* e, const uint64_t* bounds_min, int nmi
                             const uint64_t* bounds_max, int nmax);
 
 /* how a proposal's count change is computed: 0 = auto (delta path: only the simplices through the
- * changed edges are enumerated; falls back per proposal when a common-neighbour list exceeds 64),
+ * changed edges are enumerated; the hot loop looks the orientation of the pair's triangles and
+ * 4-cliques up in a static clique index when the graph is small enough for it, else gathers them
+ * from the adjacency rows; falls back per proposal when a common-neighbour list exceeds 64),
  * 1 = always the full pre/post counts of the neighbourhood graph as the reference does them
- * (src/lib.rs:63,71).  flag_count, accept/reject and the trace are identical. */
+ * (src/lib.rs:63,71), 2 = delta path gathered from the adjacency rows even when the index exists.
+ * flag_count, accept/reject and the trace are identical. */
 int fcm_ensemble_set_kernel(fcm_ensemble* e, int kind);
 
 /* one record per proposal (optional trace; identical layout in oracle/fcm_oracle.cpp) */

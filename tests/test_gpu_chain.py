@@ -29,7 +29,7 @@ def compare_chain(s, chain, o):
     assert np.array_equal(r["edges"], w["edges"])        # container order, not just the set
 
 
-@pytest.mark.parametrize("kernel", [0, 1])
+@pytest.mark.parametrize("kernel", [0, 1, 2])
 @pytest.mark.parametrize("name,seed,steps", [("counterexample_seo_greedy_5_start", 0, 20000),
                                              ("counterexample_any_order", 3, 3000),
                                              ("bug_calc_relax_de", 1, 8000),
@@ -54,7 +54,7 @@ def test_trace_parity_single_chain(name, seed, steps, kernel, ctx, graphs):
     s.close()
 
 
-@pytest.mark.parametrize("kernel", [0, 1])
+@pytest.mark.parametrize("kernel", [0, 1, 2])
 def test_many_chains_match_per_seed_oracle(kernel, ctx):
     n = 120
     e = rand_graph(n, 0.12, 21, pdouble=0.3)
@@ -156,7 +156,7 @@ def test_apply_revert_api(ctx, graphs):
     s.close()
 
 
-@pytest.mark.parametrize("kernel", [0, 1])
+@pytest.mark.parametrize("kernel", [0, 1, 2])
 def test_rejections_happen_and_revert_restores(kernel, ctx, graphs):
     # tight hand-set bounds: most flips are rejected; state must stay consistent
     n, e = graphs["c2_chunglu_279"]
@@ -214,7 +214,7 @@ def test_delta_path_deep_and_double_heavy(n, p, pd, steps, minlen, ctx):
     o = orc.Sampler(n, e, 7, 0.9, nthreads=8)
     want = o.steps(steps)
     assert len(o.read()["flag_count"]) >= minlen         # >= 7: beyond the register levels (index > 5)
-    for kernel in (0, 1):
+    for kernel in (0, 1, 2):
         s = fcm.initialize_new_sampler(ctx, n, e, [7], target_relaxation=0.9, simple=True)
         s.set_kernel(kernel)
         assert_trace_equal(s.step_trace(steps, 0), want)
@@ -234,9 +234,26 @@ def test_delta_path_flag_count_length_growth(ctx):
     for seed in range(6):
         o = orc.Sampler(m, e, seed, 5.0)
         want = o.steps(400)
-        for kernel in (0, 1):
+        for kernel in (0, 1, 2):
             s = fcm.initialize_new_sampler(ctx, m, e, [seed], target_relaxation=5.0, simple=True)
             s.set_kernel(kernel)
             assert_trace_equal(s.step_trace(400, 0), want)
             compare_chain(s, 0, o)                         # flag_count incl. its length (trailing zeros)
             s.close()
+
+
+@pytest.mark.parametrize("name", ["counterexample_seo_greedy_5_start", "c2_chunglu_279"])
+def test_switching_kernels_mid_run_keeps_rows_and_orientation_bits_in_step(name, ctx, graphs):
+    # the index hot path (0) works from the orientation bits, the row-gather hot path (2) and the full
+    # path (1) from the adjacency rows: both views are updated by every accepted move, so a chain may
+    # change kernels at any proposal and must still follow the oracle.
+    n, e = graphs[name]
+    o = orc.Sampler(n, e, 11, 0.05)
+    s = fcm.initialize_new_sampler(ctx, n, e, [3, 11], target_relaxation=0.05, simple=True)
+    for kernel, steps in ((0, 700), (2, 500), (0, 300), (1, 200), (2, 300), (0, 500)):
+        s.set_kernel(kernel)
+        assert_trace_equal(s.step_trace(steps, 1), o.steps(steps))
+    compare_chain(s, 1, o)
+    r = s.read(1)
+    assert ds.trim(r["flag_count"]) == fcm.flagser_count(n, r["edges"], ctx)
+    s.close()
