@@ -21,7 +21,7 @@ SYMBOLS = [
     "fcm_graph_count_async", "fcm_graph_set_kernel", "fcm_graph_info",
     "fcm_ensemble_create", "fcm_ensemble_destroy", "fcm_ensemble_set_bounds", "fcm_ensemble_set_kernel", "fcm_ensemble_step",
     "fcm_ensemble_step_trace", "fcm_ensemble_read", "fcm_ensemble_read_all", "fcm_ensemble_status",
-    "fcm_ensemble_info", "fcm_apply", "fcm_revert", "fcm_bounds_check",
+    "fcm_ensemble_info", "fcm_ensemble_set_stats", "fcm_ensemble_index_info", "fcm_apply", "fcm_revert", "fcm_bounds_check",
 ]
 
 
@@ -77,6 +77,8 @@ def lib():
     L.fcm_ensemble_destroy.argtypes = [vp]
     L.fcm_ensemble_set_bounds.argtypes = [vp, vp, i32, vp, i32]
     L.fcm_ensemble_set_kernel.argtypes = [vp, i32]
+    L.fcm_ensemble_set_stats.argtypes = [vp, i32]
+    L.fcm_ensemble_index_info.argtypes = [vp, P(i32), P(u64)]
     L.fcm_ensemble_step.argtypes = [vp, u64]
     L.fcm_ensemble_step_trace.argtypes = [vp, u64, u32, vp]
     L.fcm_ensemble_read.argtypes = [vp, u32, vp, P(i32), P(u64), P(u64), vp, P(u64), P(u64), vp]

@@ -271,11 +271,13 @@ __device__ int local_count_any(const u64* M, int K, int KW, int lane, u64* out, 
 #define SM_FLAG 1568                   // int[12]          see FL_*
 #define SM_AT 1616                     // u32[32]          hot path: rows of the tagged graph
 #define SM_SRC 1744                    // u32[32]          hot path: source vertex of each extra tagged copy
-#define SM_PARK 1872                   // u32[16]          a sampled proposal handed to cold_step, see PK_*
-#define SM_TILE 1936
-enum { FL_DEEP = 0, FL_TOP = 1, FL_ERR = 2, FL_RC = 3, FL_K = 4, FL_LEN = 5, FL_OVF = 6 };
+#define SM_PARK 1872                   // u32[32]          the sampled proposal (update stage, cold_step), see PK_*
+#define SM_RNG 2000                    // u64[4]           xoshiro state between the sampling stages
+#define SM_FC 2032                     // u64[32]          flag_count, one entry per lane
+#define SM_TILE 2288
+enum { FL_DEEP = 0, FL_TOP = 1, FL_ERR = 2, FL_RC = 3, FL_K = 4, FL_LEN = 5, FL_OVF = 6, FL_E = 8, FL_ND = 9, FL_ACC = 10, FL_FCLEN = 11 };
 enum { PK_KIND = 0, PK_SLOT, PK_DELME, PK_IDX, PK_DIDX, PK_DPAIR, PK_LAST, PK_QPOS, PK_TA, PK_TB, PK_TDM0, PK_TDM1,
-       PK_CA, PK_CD, PK_OA, PK_OD };
+       PK_CA, PK_CD, PK_OA, PK_OD, PK_ORIA, PK_ORID };
 struct WarpSmem {
   u64 *M, *fc, *pre, *post;
   u32 *verts, *edits;
@@ -826,7 +828,7 @@ __device__ __forceinline__ void update_adjacency(const EnsParams& p, u32* cb, u3
 // two-slot lists (32 < c <= 64), more than 32 tagged copies, simplices beyond the register levels,
 // lists beyond FAST_C (full path) or a forced full path.  Reads and writes the chain's state in HBM.
 __device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned char* wb, int lane, fcm_trace_rec* tr_out,
-                                      int force_full, bool red) {
+                                      int force_full, bool red, bool instr) {
   const u32* park = (const u32*)(wb + SM_PARK);
   u64* const sdeep = (u64*)(wb + SM_DEEP);
   int* const sflag = (int*)(wb + SM_FLAG);
@@ -873,7 +875,8 @@ __device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned ch
   if (ok) st->flag_count[lane] = fnew;
   if (lane == 0) {
     st->fc_len = len;
-    st->sampled += 1; st->accepted += ok; st->sumK += (u64)K; st->nonempty += 1;
+    st->sampled += 1; st->accepted += ok;
+    if (instr) { st->sumK += (u64)K; st->nonempty += 1; }
     if (tr_out) {
       fcm_trace_rec tr;
       tr.flags = (u32)kind | (ok ? FCM_TR_ACCEPT : 0u);
@@ -887,7 +890,8 @@ __device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned ch
 
 // IDX = true: the hot path reads the static clique index + the chain's orientation bits;
 // IDX = false: it gathers from the chain's adjacency rows (graphs too large for the index).
-template <bool IDX>
+// INSTR = true: per-proposal trace and the neighbourhood-size statistic (sumK / nonempty) are produced.
+template <bool IDX, bool INSTR>
 __global__ void __launch_bounds__(128, 7)
 chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ trace, u32 trace_chain,
                   u32 smem_per_warp, int force_full) {
@@ -913,24 +917,30 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
 #define POS(i) cb[p.off_pos + (i)]
 #define DBL(i) cb[p.off_dbl + (i)]
 #define ORI(i) cb[p.off_ori + (i)]
-  const u32 E = st->E, ND = st->ND;                    // both moves keep |E| and the number of double pairs
   const u32 W32 = 2 * p.W;
-  if (lane < 12) sflag[lane] = 0;
+  if (lane < 12) sflag[lane] = lane == FL_E ? (int)st->E : lane == FL_ND ? (int)st->ND : 0;   // both moves keep |E| and #double pairs
   ((u64*)(wb + SM_DEEP))[lane] = 0;
   __syncwarp();
-  if (trace != nullptr && chain != trace_chain) trace = nullptr;
+  if (!INSTR || chain != trace_chain) trace = nullptr;
 
+  u64* const srng = (u64*)(wb + SM_RNG);
+  u64* const sfc = (u64*)(wb + SM_FC);
   u32 step = 0;
   while (step < nsteps) {
-    // ---- hot stretch: chain state in registers until a proposal needs the general code ----
-    Rng g{st->rng[0], st->rng[1], st->rng[2], st->rng[3]};
-    u64 fc = st->flag_count[lane];                     // lane d owns flag_count[d]
-    int len = st->fc_len;
-    u32 accepted = 0, sumK = 0, nonempty = 0;          // per stretch (nsteps <= 2^24: the host splits longer runs)
+    // ---- hot stretch: the chain's scalars live in shared memory (registers are the scarce resource:
+    //      28 resident warps per SM leave 72 per thread) until a proposal needs the general code ----
+    if (lane < 4) srng[lane] = st->rng[lane];
+    sfc[lane] = st->flag_count[lane];                  // lane d owns flag_count[d]
+    if (lane == 0) { sflag[FL_ACC] = 0; sflag[FL_FCLEN] = st->fc_len; }
+    __syncwarp();
+    u32 sumK = 0, nonempty = 0;                        // per stretch (nsteps <= 2^24: the host splits longer runs)
     const u32 step0 = step;
     int err = 0;
     bool cold = false;
     for (; step < nsteps; step++) {
+      const u32 E = (u32)sflag[FL_E], ND = (u32)sflag[FL_ND];
+      Rng g;
+      { const ulonglong2 a = *(const ulonglong2*)&srng[0], b = *(const ulonglong2*)&srng[2]; g.s0 = a.x; g.s1 = a.y; g.s2 = b.x; g.s3 = b.y; }
       // ---- Transition::random_move: WeightedIndex<f64>::sample (src/lib.rs:210) ----
       const u64 r = g.next();
       const double v = __longlong_as_double((long long)((r >> 12) | 0x3ff0000000000000ULL)) - 1.0;
@@ -1007,14 +1017,21 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
       u32 ta = 0, tb = 0, tdm0 = 0, tdm1 = 0;
       if (sampled_edge) { ta = (slot & 1) ? abA.y : abA.x; tb = (slot & 1) ? abA.x : abA.y; }
       if (kind == 1 && live) { tdm0 = (delme & 1) ? abD.y : abD.x; tdm1 = (delme & 1) ? abD.x : abD.y; }
+      if (lane == 0) { *(ulonglong2*)&srng[0] = make_ulonglong2(g.s0, g.s1); *(ulonglong2*)&srng[2] = make_ulonglong2(g.s2, g.s3); }
+      // the proposal is parked in shared memory: the update stage (lane 0) and cold_step read it back, so
+      // that its scalars do not occupy registers while the simplices are counted
+      if (live && lane == 0) {
+        *(uint4*)&spark[PK_KIND] = make_uint4((u32)kind, slot, delme, idx);
+        *(uint4*)&spark[PK_DIDX] = make_uint4(didx, dpair, last, qpos);
+        *(uint4*)&spark[PK_TA] = make_uint4(ta, tb, tdm0, tdm1);
+        *(uint4*)&spark[PK_CA] = make_uint4((u32)cA, (u32)cD, oA, oD);
+        *(uint2*)&spark[PK_ORIA] = make_uint2(oriA, oriD);
+      }
 
       // ---- State::apply_transition  src/lib.rs:61-79: flag_count += post - pre ----
       int K = 0;
-      u64 fnew = fc;
-      // the edge that comes is tb->ta for both moves; the edge that goes is ta->tb (flip) or delme
-      const u32 gu = kind == 0 ? ta : tdm0, gv = kind == 0 ? tb : tdm1;
-      const u32 igo = gu * W32 + (gv >> 5), icome = tb * W32 + (ta >> 5);
-      u32 vgo = 0, vcome = 0;
+      u64 fnew;
+      u32 vgo = 0, vcome = 0;                           // row-gather path: the two row words an accept rewrites
       if (live) {
         const int cB = kind == 0 ? 0 : cD;
         cold = force_full || cA > NARROW_C || cB > NARROW_C;
@@ -1033,7 +1050,7 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
               idx_issue(p, ori, oD, cD, kD, mD, tdm0 == abD.x, lane, rD);
               // the vertex lists are only needed to take delme out of the coming pair's view and for K
               scv[lane] = lane < cA ? __ldg(&p.nb_list[oA + lane]) : 0u;
-              scv2[lane] = lane < cD ? __ldg(&p.nb_list[oD + lane]) : 0u;
+              if constexpr (INSTR) scv2[lane] = lane < cD ? __ldg(&p.nb_list[oD + lane]) : 0u;
             }
 #pragma unroll 1
             for (int ph = 0; ph < 2 && !cold; ph++) {
@@ -1054,7 +1071,9 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
             }
           } else {
             const int wordsA = hot_tile_words(cA);
-            vgo = cb[igo]; vcome = cb[icome];             // early: rewritten on accept without a stall
+            // the edge that comes is tb->ta for both moves; the edge that goes is ta->tb (flip) or delme
+            vgo = cb[(kind == 0 ? ta : tdm0) * W32 + ((kind == 0 ? tb : tdm1) >> 5)];
+            vcome = cb[tb * W32 + (ta >> 5)];             // early: rewritten on accept without a stall
             // both gathers are in flight together when the tile holds both, else one after the other
             const bool both = wordsA + hot_tile_words(cB) <= TILE_WORDS;
             u32* const tileD = both ? stile + wordsA : stile;
@@ -1088,17 +1107,11 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
           if (sflag[FL_OVF]) { cold = true; __syncwarp(); if (lane == 0) sflag[FL_OVF] = 0; }
         }
         if (cold) {
-          // hand the sampled proposal to the general code (nothing of the chain was modified yet)
-          if (lane == 0) {
-            spark[PK_KIND] = (u32)kind; spark[PK_SLOT] = slot; spark[PK_DELME] = delme; spark[PK_IDX] = idx;
-            spark[PK_DIDX] = didx; spark[PK_DPAIR] = dpair; spark[PK_LAST] = last; spark[PK_QPOS] = qpos;
-            spark[PK_TA] = ta; spark[PK_TB] = tb; spark[PK_TDM0] = tdm0; spark[PK_TDM1] = tdm1;
-            spark[PK_CA] = (u32)cA; spark[PK_CD] = (u32)cD; spark[PK_OA] = oA; spark[PK_OD] = oD;
-          }
+          // the parked proposal goes to the general code (nothing of the chain was modified yet)
           __syncwarp();
           break;
         }
-        K = kind == 0 ? cA + 2 : union_size(scv, cA, scv2, cD, ta, tb, tdm0, tdm1, lane);
+        if constexpr (INSTR) K = kind == 0 ? cA + 2 : union_size(scv, cA, scv2, cD, ta, tb, tdm0, tdm1, lane);
         long long delta = 0;
 #pragma unroll
         for (int k = 0; k < DELTA_SD; k++) {
@@ -1106,31 +1119,36 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
           if (lane == k + 3) delta = tot;
         }
         if (lane == 2) delta = tri;
-        fnew = fc + (u64)delta;
+        fnew = sfc[lane] + (u64)delta;
         if (__any_sync(FULL, (long long)fnew < 0)) { err = FCM_EASSERT; break; }
-        len = max(len, top + 1);
-        sumK += K;
-        nonempty++;
-      }
+        if (lane == 0) sflag[FL_FCLEN] = max(sflag[FL_FCLEN], top + 1);
+        if constexpr (INSTR) { sumK += K; nonempty++; }
+      } else fnew = sfc[lane];
       // ---- Bounds::check, then keep or revert_transition (src/lib.rs:186-191, 81-95) ----
       const bool ok = bounds_ok(p, fnew, lane);
-      accepted += ok;
+      if (lane == 0) sflag[FL_ACC] += ok;
       if (live) {
-        update_containers(p, cb, kind, ok, slot, delme, idx, didx, dpair, last, qpos, E, ND, lane);
-        if (ok) {
-          // adjacency bits: gu->gv leaves, tb->ta comes
-          if (lane == 0) {
-            const u32 mgo = 1u << (gv & 31), mcome = 1u << (ta & 31);
+        if (lane == 0) {                                // the parked proposal, read back
+          const uint4 q0 = *(const uint4*)&spark[PK_KIND], q1 = *(const uint4*)&spark[PK_DIDX];
+          const u32 uslot = q0.y, udelme = q0.z;
+          update_containers(p, cb, kind, ok, uslot, udelme, q0.w, q1.x, q1.y, q1.z, q1.w, E, ND, 0);
+          if (ok) {
+            // adjacency bits: gu->gv leaves, tb->ta comes
+            const uint4 q2 = *(const uint4*)&spark[PK_TA];
+            const u32 gu = kind == 0 ? q2.x : q2.z, gv = kind == 0 ? q2.y : q2.w;
+            const u32 igo = gu * W32 + (gv >> 5), icome = q2.y * W32 + (q2.x >> 5);
+            const u32 mgo = 1u << (gv & 31), mcome = 1u << (q2.x & 31);
             if constexpr (IDX) {
               // rows: fire-and-forget L2 atomics (only the cold path reads them, with ld.cg); orientation
               // bits: plain stores of the words read while sampling
+              const uint2 q4 = *(const uint2*)&spark[PK_ORIA];
               atomicAnd(&cb[igo], ~mgo); atomicOr(&cb[icome], mcome);
-              if (kind == 0) ORI(slot >> 5) = oriA ^ (3u << (slot & 30));
+              if (kind == 0) ORI(uslot >> 5) = q4.x ^ (3u << (uslot & 30));
               else {
-                const u32 wa = slot >> 5, wd = delme >> 5;
-                const u32 ma = 1u << ((slot ^ 1) & 31), md = 1u << (delme & 31);
-                if (wa == wd) ORI(wa) = (oriA | ma) & ~md;
-                else { ORI(wa) = oriA | ma; ORI(wd) = oriD & ~md; }
+                const u32 wa = uslot >> 5, wd = udelme >> 5;
+                const u32 ma = 1u << ((uslot ^ 1) & 31), md = 1u << (udelme & 31);
+                if (wa == wd) ORI(wa) = (q4.x | ma) & ~md;
+                else { ORI(wa) = q4.x | ma; ORI(wd) = q4.y & ~md; }
               }
             } else {
               // plain stores of the words read above: the rows are read through this SM's L1, which its
@@ -1138,35 +1156,38 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
               if (igo == icome) cb[igo] = (vgo & ~mgo) | mcome;
               else { cb[igo] = vgo & ~mgo; cb[icome] = vcome | mcome; }
               u32* const ori = cb + p.off_ori;
-              const u32 sg = kind == 0 ? slot : delme, sc = slot ^ 1;
+              const u32 sg = kind == 0 ? uslot : udelme, sc = uslot ^ 1;
               const u32 og = ori[sg >> 5] & ~(1u << (sg & 31));
               if ((sg >> 5) == (sc >> 5)) ori[sg >> 5] = og | (1u << (sc & 31));
               else { ori[sg >> 5] = og; ori[sc >> 5] |= 1u << (sc & 31); }
             }
           }
-          fc = fnew;
         }
+        if (ok) sfc[lane] = fnew;
         __syncwarp();
       }
-      if (trace != nullptr && lane == 0) {
-        fcm_trace_rec tr;
-        tr.flags = (u32)kind | (ok ? FCM_TR_ACCEPT : 0u) | (live ? 0u : FCM_TR_EMPTY);
-        tr.a = ta; tr.b = tb; tr.dm0 = tdm0; tr.dm1 = tdm1; tr.K = (u32)K; tr.draws = 0; tr.pad = 0;
-        trace[step] = tr;
+      if constexpr (INSTR) {
+        if (trace != nullptr && lane == 0) {
+          fcm_trace_rec tr;
+          tr.flags = (u32)kind | (ok ? FCM_TR_ACCEPT : 0u) | (live ? 0u : FCM_TR_EMPTY);
+          tr.a = ta; tr.b = tb; tr.dm0 = tdm0; tr.dm1 = tdm1; tr.K = (u32)K; tr.draws = 0; tr.pad = 0;
+          trace[step] = tr;
+        }
       }
     }
     // ---- end of the stretch: the chain's state goes back to HBM ----
     __syncwarp();
-    st->flag_count[lane] = fc;
+    st->flag_count[lane] = sfc[lane];
+    if (lane < 4) st->rng[lane] = srng[lane];
     if (lane == 0) {
-      st->rng[0] = g.s0; st->rng[1] = g.s1; st->rng[2] = g.s2; st->rng[3] = g.s3;
-      st->fc_len = len;
-      st->sampled += step - step0; st->accepted += accepted; st->sumK += sumK; st->nonempty += nonempty;
+      st->fc_len = sflag[FL_FCLEN];
+      st->sampled += step - step0; st->accepted += (u32)sflag[FL_ACC];
+      if constexpr (INSTR) { st->sumK += sumK; st->nonempty += nonempty; }
       if (err) st->err = err;
     }
     __syncwarp();
     if (err || !cold) break;
-    if (cold_step(p, chain, wb, lane, trace ? trace + step : nullptr, force_full, IDX)) break;
+    if (cold_step(p, chain, wb, lane, trace ? trace + step : nullptr, force_full, IDX, INSTR)) break;
     step++;
   }
 #undef ITEMS
@@ -1266,7 +1287,7 @@ int fcm_chain_launch_replicate(fcm_ensemble* e) {
   return FCM_OK;
 }
 
-template <bool IDX>
+template <bool IDX, bool INSTR>
 static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
   const EnsParams& p = e->p;
   const size_t per_warp = chain_smem_per_warp_mode(p.Kcap, p.KWcap, !IDX);
@@ -1274,13 +1295,13 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
   while (wpb > 1 && per_warp * wpb > e->ctx->smem_optin) wpb >>= 1;
   if (per_warp * wpb > e->ctx->smem_optin) { fcm_set_error("neighbourhood tile does not fit shared memory"); return FCM_ELIMIT; }
   const size_t smem = per_warp * wpb;
-  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   const u32 blocks = (p.nchains + wpb - 1) / wpb;
   const u64 chunk = 1ULL << 24;                         // the kernel's per-launch counters are 32-bit
   for (u64 done = 0; done < nsteps; done += chunk) {
     const u32 now = (u32)std::min<u64>(chunk, nsteps - done);
-    chain_step_kernel<IDX><<<blocks, wpb * 32, smem, e->ctx->stream>>>(p, now, trace_dev ? trace_dev + done : nullptr,
+    chain_step_kernel<IDX, INSTR><<<blocks, wpb * 32, smem, e->ctx->stream>>>(p, now, trace_dev ? trace_dev + done : nullptr,
                                                                      trace_chain, (u32)per_warp, e->force_full);
     e->ctx->launches++;
   }
@@ -1289,8 +1310,11 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
 }
 
 int fcm_chain_launch_step(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
-  if (e->have_index && !e->force_rows) return launch_step_mode<true>(e, nsteps, trace_dev, trace_chain);
-  return launch_step_mode<false>(e, nsteps, trace_dev, trace_chain);
+  const bool idx = e->have_index && !e->force_rows, instr = trace_dev != nullptr || e->stats;
+  if (idx) return instr ? launch_step_mode<true, true>(e, nsteps, trace_dev, trace_chain)
+                        : launch_step_mode<true, false>(e, nsteps, trace_dev, trace_chain);
+  return instr ? launch_step_mode<false, true>(e, nsteps, trace_dev, trace_chain)
+               : launch_step_mode<false, false>(e, nsteps, trace_dev, trace_chain);
 }
 
 int fcm_chain_launch_apply(fcm_ensemble* e, u32 chain, int nedits, int mode) {

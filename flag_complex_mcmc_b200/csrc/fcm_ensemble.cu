@@ -340,6 +340,19 @@ extern "C" int fcm_ensemble_set_kernel(fcm_ensemble* e, int kind) {
   return FCM_OK;
 }
 
+extern "C" int fcm_ensemble_set_stats(fcm_ensemble* e, int on) {
+  REQUIRE(e, "ensemble is null");
+  e->stats = on != 0;
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_index_info(const fcm_ensemble* e, int* have_index, uint64_t* index_bytes) {
+  REQUIRE(e, "ensemble is null");
+  if (have_index) *have_index = e->have_index;
+  if (index_bytes) *index_bytes = e->index_bytes;
+  return FCM_OK;
+}
+
 extern "C" int fcm_ensemble_info(const fcm_ensemble* e, uint32_t* n, uint64_t* npairs, uint32_t* nchains,
                                  uint32_t* maxc, uint64_t* bytes_per_chain) {
   REQUIRE(e, "ensemble is null");

@@ -117,6 +117,7 @@ struct fcm_ensemble {
   int force_full = 0;                     // 1: every proposal through the full pre/post count path
   int force_rows = 0;                     // 1: hot path gathers from the adjacency rows even when the clique index exists
   int have_index = 0;                     // the static clique index was built
+  int stats = 1;                          // 1: the kernels keep the neighbourhood-size statistic (sumK / nonempty)
   u64 index_bytes = 0;
   fcm_trace_rec* trace_dev = nullptr;
   u64 trace_cap = 0;

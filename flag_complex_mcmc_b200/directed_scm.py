@@ -359,6 +359,15 @@ class MCMCSampler:
         return {"n": n.value, "npairs": npairs.value, "nchains": nch.value, "max_common_nbhd": maxc.value,
                 "bytes_per_chain": bpc.value}
 
+    def set_stats(self, on):
+        """Switch the neighbourhood-size statistic (sumK / nonempty of read_all) on (default) or off."""
+        check(lib().fcm_ensemble_set_stats(self.h, 1 if on else 0))
+
+    def index_info(self):
+        have, nbytes = C.c_int32(), C.c_uint64()
+        check(lib().fcm_ensemble_index_info(self.h, C.byref(have), C.byref(nbytes)))
+        return {"have_index": bool(have.value), "index_bytes": nbytes.value}
+
     def set_bounds(self, bounds):
         mn = np.asarray(bounds.flag_count_min, dtype=np.uint64)
         mx = np.asarray(bounds.flag_count_max, dtype=np.uint64)

@@ -131,6 +131,15 @@ int fcm_ensemble_set_bounds(fcm_ensemble* e, const uint64_t* bounds_min, int nmi
  * flag_count, accept/reject and the trace are identical. */
 int fcm_ensemble_set_kernel(fcm_ensemble* e, int kind);
 
+/* Instrumentation switch.  on (default): every non-empty proposal adds its neighbourhood size
+ * |State::edgeset_neighborhood| (src/lib.rs:99-111) to the statistic fcm_ensemble_read_all returns
+ * in stats[2].  off: the statistic stands still (a double-edge move then skips the size of the union
+ * of its two neighbourhoods, which nothing else needs); flag_count, sampled, accepted, the RNG and
+ * the edge containers are unaffected.  Traced steps always carry K. */
+int fcm_ensemble_set_stats(fcm_ensemble* e, int on);
+/* whether the static clique index was built for this graph and its size in HBM (shared by all chains) */
+int fcm_ensemble_index_info(const fcm_ensemble* e, int* have_index, uint64_t* index_bytes);
+
 /* one record per proposal (optional trace; identical layout in oracle/fcm_oracle.cpp) */
 typedef struct fcm_trace_rec {
   uint32_t flags;              /* bits 0-1 move kind, bit 4 accepted, bit 5 empty transition */

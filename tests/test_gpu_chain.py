@@ -257,3 +257,23 @@ def test_switching_kernels_mid_run_keeps_rows_and_orientation_bits_in_step(name,
     r = s.read(1)
     assert ds.trim(r["flag_count"]) == fcm.flagser_count(n, r["edges"], ctx)
     s.close()
+
+
+def test_statistic_switch_does_not_change_the_chain(ctx, graphs):
+    # fcm_ensemble_set_stats(off) only freezes sumK / nonempty: trajectory, counts, containers, RNG equal
+    n, e = graphs["c2_chunglu_279"]
+    o = orc.Sampler(n, e, 5, 0.01)
+    o.steps(6000, trace=False)
+    s = fcm.initialize_new_sampler(ctx, n, e, [4, 5], target_relaxation=0.01, simple=True)
+    s.step(1000)
+    a = s.read_all()
+    s.set_stats(False)
+    s.step(4000)
+    b = s.read_all()
+    assert (a["sumK"], a["nonempty"]) == (b["sumK"], b["nonempty"]) and a["nonempty"] > 0
+    s.set_stats(True)
+    s.step(1000)
+    c = s.read_all()
+    assert c["nonempty"] > b["nonempty"]
+    compare_chain(s, 1, o)
+    s.close()
