@@ -218,6 +218,7 @@ def main():
 
     import torch
     import flag_complex_mcmc_b200 as fcm
+    from flag_complex_mcmc_b200 import sharding
     from tools import synth
 
     world = env_int("WORLD_SIZE", 1)
@@ -257,7 +258,7 @@ def main():
 
     # ---- chains --------------------------------------------------------------------------------
     n, e = synth.config("c3_er_2000")
-    seeds = np.arange(rank * args.chains, (rank + 1) * args.chains, dtype=np.uint64)
+    seeds = sharding.chain_seeds(0, args.chains * ngpu, rank, ngpu)   # chain k -> GPU k mod N
     s = fcm.initialize_new_sampler(ctx, n, e, seeds, target_relaxation=0.01, simple=True)
     P = args.proposals
     # warm-up steps run instrumented: they give the mean neighbourhood size K and the non-empty fraction
