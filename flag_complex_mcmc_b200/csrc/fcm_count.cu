@@ -19,9 +19,7 @@
 
 #include <algorithm>
 
-#define LOCAL_THREADS 128
 #define DENSE_WARPS 4
-#define MAXL_LOCAL (FCM_MAXD - 2)   // level l holds candidates for vertex index l+2
 #define MAXL_DENSE (FCM_MAXD - 1)   // level l holds candidates for vertex index l+1
 
 // ---------------------------------------------------------------------------------------------------
@@ -112,28 +110,93 @@ int fcm_graph_build_device(fcm_graph* g, const uint2* edges_dev, u64 ne_in, int 
 // ---------------------------------------------------------------------------------------------------
 // block-local relabelled count
 // ---------------------------------------------------------------------------------------------------
-template <int WK> struct LocalCfg { static constexpr int LS = WK | 1; };   // odd row stride: no bank conflicts
+// One CTA per source vertex v0 (persistent CTAs, sources handed out by a ticket in degree-descending
+// order).  out(v0) is relabelled 0..k-1 and its k x k induced adjacency L is gathered once into shared
+// memory (row stride LS = WK|1 64-bit words: odd, so rows fall on different banks).  The simplices
+// under v0 are then enumerated through a per-warp STACK OF PENDING SIMPLICES in shared memory: an
+// entry is the tuple (v1..vd) of local ids, 10 bits each, d <= 6.
+//   fill   when fewer than 32 entries are pending the warp takes the next row i (= v1) and pushes one
+//          entry (i, j) per member j of L[i] (the triangles v0,v1,v2); lane l extracts 2*WK bits;
+//   step   the warp pops the top 32 entries, one per lane: P = L[v1] & .. & L[vd] is rebuilt from the
+//          rows (d*WK shared-memory loads, no per-thread stack), popc(P) simplices of d+2 vertices are
+//          counted, and every member of P is pushed back as a child entry (warp scan for the offsets).
+// Every lane thus runs the same straight-line AND/popc code on a different simplex whatever the shape
+// of the tree (a per-thread DFS leaves most lanes idle: a triangle of the cortical graph has 1.26
+// children on average, spread over WK words).  Tuples deeper than 6 ids, or a full stack, fall back to
+// a generic per-thread DFS (deep_count), which is rare.
+template <int WK> struct LocalCfg {
+  static constexpr int LS = WK | 1;
+  static constexpr int THREADS = WK >= 16 ? 128 : 256;
+  static constexpr int MINBLOCKS = WK >= 16 ? 1 : 3;
+  static constexpr int MAXIDS = 6;                                 // ids per stack entry (10 bits each + depth)
+  static constexpr int BPL = 2 * WK;                               // bits of a row each lane extracts (32 lanes x BPL = 64*WK)
+};
+__host__ __device__ constexpr u32 stack_cap(u32 kcap) { return kcap + 128; }   // entries per warp (>= kcap + 32; a full stack falls back to deep_count)
+
+// P = candidates for the vertex of index `lvl` (non-empty, already counted).  Generic levels: explicit
+// stack in local memory, counts through shared atomics (rare: dimension > REG_LEVELS + 2).
+template <int WK>
+__device__ __noinline__ void deep_count(const u64 (&P0)[WK], int lvl, const u64* __restrict__ L,
+                                        unsigned long long* s_cnt, u32* ctrl) {
+  constexpr int LS = LocalCfg<WK>::LS;
+  u64 P[FCM_MAXD][WK];
+  int cw[FCM_MAXD];
+  u64 cb[FCM_MAXD];
+#pragma unroll
+  for (int x = 0; x < WK; x++) P[0][x] = P0[x];
+  int l = 0, w = 0;
+  u64 bits = P[0][0];
+  for (;;) {
+    while (bits == 0) { if (++w == WK) break; bits = P[l][w]; }
+    if (w == WK) {
+      if (l == 0) break;
+      --l; w = cw[l]; bits = cb[l];
+      continue;
+    }
+    const int j = w * 64 + (__ffsll((long long)bits) - 1);
+    bits &= bits - 1;
+    const u64* Lj = L + (size_t)j * LS;
+    u32 cpc = 0;
+    const int d = lvl + l + 1;                          // flag_count index the children of this node close
+    if (d < FCM_MAXD) {
+#pragma unroll
+      for (int x = 0; x < WK; x++) { u64 q = P[l][x] & Lj[x]; P[l + 1][x] = q; cpc += __popcll(q); }
+      if (cpc) {
+        atomicAdd(&s_cnt[d], (unsigned long long)cpc);
+        cw[l] = w; cb[l] = bits; ++l; w = 0; bits = P[l][0];
+      }
+    } else {
+#pragma unroll
+      for (int x = 0; x < WK; x++) cpc += __popcll(P[l][x] & Lj[x]);
+      if (cpc) atomicExch(&ctrl[CT_ERR], 2u);           // a simplex of dimension >= FCM_MAXD
+    }
+  }
+}
 
 template <int WK>
-__global__ void __launch_bounds__(LOCAL_THREADS)
+__global__ void __launch_bounds__(LocalCfg<WK>::THREADS, LocalCfg<WK>::MINBLOCKS)
 count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
                    const u32* __restrict__ csr, const u32* __restrict__ order, u32 W, u32 nv_total,
                    u32 part, u32 nparts, u32 kcap, u32* __restrict__ ctrl,
                    u32* __restrict__ overflow, u64* __restrict__ counts) {
-  constexpr int LS = LocalCfg<WK>::LS;
+  using Cfg = LocalCfg<WK>;
+  constexpr int LS = Cfg::LS, NT = Cfg::THREADS, NW = NT / 32, BPL = Cfg::BPL, MAXIDS = Cfg::MAXIDS;
+  constexpr int RL = MAXIDS - 1;                        // cnt[r]: flag_count index 3 + r (tuples of 2 + r ids)
   extern __shared__ __align__(16) unsigned char smem_raw[];
   u64* L = (u64*)smem_raw;                              // kcap * LS
   u32* verts = (u32*)(L + (size_t)kcap * LS);           // kcap
+  u64* stacks = (u64*)(verts + kcap + (kcap & 1));      // NW * stack_cap(kcap)
   __shared__ u32 s_task, s_next;
   __shared__ unsigned long long s_cnt[FCM_MAXD];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  constexpr int NW = LOCAL_THREADS / 32;
-  u64 cnt[FCM_MAXD];
+  const u32 scap = stack_cap(kcap);
+  u64* const stk = stacks + (size_t)warp * scap;
+  u64 c0 = 0, c01 = 0, c2 = 0;                          // c0, c01: thread 0 only (sources, edges)
+  u64 cnt[RL];
 #pragma unroll
-  for (int d = 0; d < FCM_MAXD; d++) cnt[d] = 0;
+  for (int r = 0; r < RL; r++) cnt[r] = 0;
   if (tid < FCM_MAXD) s_cnt[tid] = 0;
-  bool dim_overflow = false;
 
   // number of source vertices of this shard: indices part, part+nparts, ... < nv_total
   const u32 ntasks = nv_total > part ? (nv_total - part + nparts - 1) / nparts : 0;
@@ -147,76 +210,142 @@ count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
     const u32 v0 = order[part + t * nparts];
     const u64 o0 = csr_off[v0];
     const u32 k = (u32)(csr_off[v0 + 1] - o0);
-    if (tid == 0) { cnt[0] += 1; cnt[1] += k; }
     if (k > kcap) {                                     // tile too small: hand to the dense-row kernel
-      if (tid == 0) { cnt[0] -= 1; cnt[1] -= k; overflow[atomicAdd(&ctrl[CT_NOVER], 1u)] = v0; }
+      if (tid == 0) overflow[atomicAdd(&ctrl[CT_NOVER], 1u)] = v0;
       continue;
     }
+    if (tid == 0) { c0 += 1; c01 += k; }
     if (k < 2) continue;                                // no 2-simplex possible
-    for (u32 i = tid; i < k; i += LOCAL_THREADS) verts[i] = csr[o0 + i];
+    for (u32 i = tid; i < k; i += NT) verts[i] = csr[o0 + i];
     __syncthreads();
-    // gather the k x k induced adjacency: warp per row, lane per column, ballot -> 32 columns/instr
-    u32* L32 = (u32*)L;
-    const u32 nch = (k + 31) >> 5;
-    for (u32 i = warp; i < k; i += NW) {
-      const u64* row = adj + (u64)verts[i] * W;
-      u32* dst = L32 + (size_t)i * (2 * LS);
-      for (u32 c = 0; c < 2 * WK; c++) {
-        u32 b = 0;
-        if (c < nch) {
-          u32 j = c * 32 + lane;
-          bool bit = false;
-          if (j < k) { u32 gv = verts[j]; bit = (__ldg(&row[gv >> 6]) >> (gv & 63)) & 1ULL; }
-          b = __ballot_sync(0xffffffffu, bit);
+    // ---- gather the k x k induced adjacency.  Tasks = (32 rows) x (32 columns); a lane owns a column,
+    //      the loads of 8 rows are in flight together, lane r keeps the ballot of row r ----
+    {
+      u32* L32 = (u32*)L;
+      const u32 nch = (k + 31) >> 5;
+      for (u32 task = warp; task < nch * nch; task += NW) {
+        const u32 rb = task / nch, c = task - rb * nch;
+        const u32 j = c * 32 + lane;
+        const u32 gv = j < k ? verts[j] : 0u;
+        const u64* col = adj + (gv >> 6);
+        const u32 gs = gv & 63;
+        const u32 r0 = rb * 32, nr = min(32u, k - r0);
+        u32 mine = 0;
+#pragma unroll 1
+        for (u32 r = 0; r < nr; r += 8) {
+          u64 wv[8];
+#pragma unroll
+          for (int q = 0; q < 8; q++) wv[q] = r + q < nr ? __ldg(&col[(u64)verts[r0 + r + q] * W]) : 0ULL;
+#pragma unroll
+          for (int q = 0; q < 8; q++) {
+            const u32 b = __ballot_sync(0xffffffffu, j < k && ((wv[q] >> gs) & 1ULL));
+            if (lane == (int)(r + q)) mine = b;
+          }
         }
-        if (lane == 0) dst[c] = b;
+        if ((u32)lane < nr) L32[(size_t)(r0 + lane) * (2 * LS) + c] = mine;
       }
+      // words past the last column chunk
+      if (nch < 2 * WK)
+        for (u32 i = tid; i < k * (2 * WK - nch); i += NT) {
+          const u32 row = i / (2 * WK - nch), c = nch + i % (2 * WK - nch);
+          L32[(size_t)row * (2 * LS) + c] = 0;
+        }
     }
     __syncthreads();
-    // one DFS per thread, roots = local rows (v1), fetched dynamically
-    for (;;) {
-      u32 i = atomicAdd(&s_next, 1u);
-      if (i >= k) break;
-      u64 P[MAXL_LOCAL][WK];
-      int cw[MAXL_LOCAL];
-      u64 cb[MAXL_LOCAL];
-      u32 pc = 0;
-#pragma unroll
-      for (int x = 0; x < WK; x++) { u64 q = L[(size_t)i * LS + x]; P[0][x] = q; pc += __popcll(q); }
-      cnt[2] += pc;
-      if (!pc) continue;
-      int l = 0, w = 0;
-      u64 bits = P[0][0];
+    // ---- enumerate ----
+    {
+      const u32* L32 = (const u32*)L;
+      u32 top = 0;                                      // pending entries: stk[0..top)
+      bool rows_left = true;
       for (;;) {
-        while (bits == 0) { if (++w == WK) break; bits = P[l][w]; }
-        if (w == WK) {
-          if (l == 0) break;
-          --l; w = cw[l]; bits = cb[l];
+        if (top < 32 && rows_left) {
+          u32 i = 0;
+          if (lane == 0) i = atomicAdd(&s_next, 1u);
+          i = __shfl_sync(0xffffffffu, i, 0);
+          if (i >= k) { rows_left = false; continue; }
+          // this lane's BPL bits of row i
+          u32 bits;
+          if constexpr (BPL >= 32) bits = L32[(size_t)i * (2 * LS) + lane];
+          else bits = (L32[(size_t)i * (2 * LS) + ((lane * BPL) >> 5)] >> ((lane * BPL) & 31)) & ((1u << BPL) - 1u);
+          const u32 pc = __popc(bits);
+          c2 += pc;
+          u32 incl = pc;
+#pragma unroll
+          for (int d = 1; d < 32; d <<= 1) { const u32 tt = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += tt; }
+          u32 o = top + incl - pc;
+          while (bits) {
+            const u32 j = lane * BPL + (__ffs((int)bits) - 1);
+            bits &= bits - 1;
+            stk[o++] = (2ULL << 60) | ((u64)j << 10) | i;
+          }
+          top += __shfl_sync(0xffffffffu, incl, 31);
+          __syncwarp();
           continue;
         }
-        const int j = w * 64 + (__ffsll((long long)bits) - 1);
-        bits &= bits - 1;
-        const u64* Lj = L + (size_t)j * LS;
-        u32 cpc = 0;
-        if (l + 1 < MAXL_LOCAL) {
+        if (top == 0) break;
+        const u32 take = min(32u, top);
+        const bool have = (u32)lane < take;
+        u64 e = 0;
+        u64 P[WK];
+        u32 pc = 0, d = 0;
+        if (have) {
+          e = stk[top - take + lane];
+          d = (u32)(e >> 60);
+          const u64* R0 = L + (size_t)(e & 1023u) * LS;
 #pragma unroll
-          for (int x = 0; x < WK; x++) { u64 q = P[l][x] & Lj[x]; P[l + 1][x] = q; cpc += __popcll(q); }
-          cnt[l + 3] += cpc;
-          if (cpc) { cw[l] = w; cb[l] = bits; ++l; w = 0; bits = P[l][0]; }
-        } else {
+          for (int y = 0; y < WK; y++) P[y] = R0[y];
+#pragma unroll 1
+          for (u32 t = 1; t < d; t++) {
+            const u64* Rt = L + (size_t)((e >> (10 * t)) & 1023u) * LS;
 #pragma unroll
-          for (int x = 0; x < WK; x++) cpc += __popcll(P[l][x] & Lj[x]);
-          if (cpc) dim_overflow = true;                 // a simplex of dimension >= FCM_MAXD
+            for (int y = 0; y < WK; y++) P[y] &= Rt[y];
+          }
+#pragma unroll
+          for (int y = 0; y < WK; y++) pc += __popcll(P[y]);
+#pragma unroll
+          for (int r = 0; r < RL; r++) cnt[r] += (d == (u32)(2 + r)) ? pc : 0u;
         }
+        top -= take;
+        // children: one entry per member of P
+        const bool deep = pc && d >= (u32)MAXIDS;
+        const u32 want = deep ? 0u : pc;
+        u32 incl = want;
+#pragma unroll
+        for (int s2 = 1; s2 < 32; s2 <<= 1) { const u32 tt = __shfl_up_sync(0xffffffffu, incl, s2); if (lane >= s2) incl += tt; }
+        const u32 total = __shfl_sync(0xffffffffu, incl, 31);
+        __syncwarp();                                   // every lane has read its entry
+        if (top + total > scap) {                       // stack full: this batch's subtrees by per-thread DFS
+          if (pc) deep_count<WK>(P, (int)d + 1, L, s_cnt, ctrl);
+        } else {
+          if (deep) deep_count<WK>(P, (int)d + 1, L, s_cnt, ctrl);
+          else if (pc) {
+            u32 o = top + incl - want;
+            const u64 base = (e & 0x0fffffffffffffffULL) | ((u64)(d + 1) << 60);
+            const u32 sh = 10 * d;
+#pragma unroll
+            for (int y = 0; y < WK; y++) {
+              u64 b = P[y];
+              while (b) {
+                const u32 j = y * 64 + (__ffsll((long long)b) - 1);
+                b &= b - 1;
+                stk[o++] = base | ((u64)j << sh);
+              }
+            }
+          }
+          top += total;
+        }
+        __syncwarp();
       }
     }
   }
   // flush: thread -> block (shared atomics) -> global
   __syncthreads();
+  if (c0) atomicAdd(&s_cnt[0], (unsigned long long)c0);
+  if (c01) atomicAdd(&s_cnt[1], (unsigned long long)c01);
+  if (c2) atomicAdd(&s_cnt[2], (unsigned long long)c2);
 #pragma unroll
-  for (int d = 0; d < FCM_MAXD; d++)
-    if (cnt[d]) atomicAdd(&s_cnt[d], (unsigned long long)cnt[d]);
-  if (dim_overflow) atomicExch(&ctrl[CT_ERR], 2u);
+  for (int r = 0; r < RL; r++)
+    if (cnt[r]) atomicAdd(&s_cnt[3 + r], (unsigned long long)cnt[r]);
   __syncthreads();
   if (tid < FCM_MAXD && s_cnt[tid]) atomicAdd((unsigned long long*)&counts[tid], s_cnt[tid]);
 }
@@ -319,7 +448,8 @@ template <int WK>
 static int launch_local(fcm_graph* g, u32 part, u32 nparts, u32 kcap) {
   fcm_ctx* c = g->ctx;
   constexpr int LS = LocalCfg<WK>::LS;
-  size_t smem = (size_t)kcap * LS * 8 + (size_t)kcap * 4;
+  constexpr int LOCAL_THREADS = LocalCfg<WK>::THREADS;
+  size_t smem = (size_t)kcap * LS * 8 + (size_t)(kcap + (kcap & 1)) * 4 + (size_t)(LOCAL_THREADS / 32) * stack_cap(kcap) * 8;
   auto kern = count_local_kernel<WK>;
   FCM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
@@ -364,11 +494,13 @@ int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts) {
   u32 kmax = g->maxout;
   int rc;
   u32 kcap;
-  if (kmax <= 64) { kcap = 64; rc = launch_local<1>(g, part, nparts, kcap); }
-  else if (kmax <= 128) { kcap = 128; rc = launch_local<2>(g, part, nparts, kcap); }
-  else if (kmax <= 256) { kcap = 256; rc = launch_local<4>(g, part, nparts, kcap); }
-  else if (kmax <= 512) { kcap = 512; rc = launch_local<8>(g, part, nparts, kcap); }
-  else { kcap = 1024; rc = launch_local<16>(g, part, nparts, kcap); }
+  // (rows: the actual largest out-degree rounded up to 32, so that more CTAs fit one SM)
+  kcap = std::min<u32>(1024u, std::max<u32>(32u, (kmax + 31u) & ~31u));
+  if (kmax <= 64) rc = launch_local<1>(g, part, nparts, kcap);
+  else if (kmax <= 128) rc = launch_local<2>(g, part, nparts, kcap);
+  else if (kmax <= 256) rc = launch_local<4>(g, part, nparts, kcap);
+  else if (kmax <= 512) rc = launch_local<8>(g, part, nparts, kcap);
+  else rc = launch_local<16>(g, part, nparts, kcap);
   if (rc) return rc;
   if (kmax > kcap) {
     // sources that did not fit the tile were appended to g->overflow; their number is only known
