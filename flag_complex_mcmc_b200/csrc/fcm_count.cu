@@ -272,13 +272,15 @@ count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
           u32 incl = pc;
 #pragma unroll
           for (int d = 1; d < 32; d <<= 1) { const u32 tt = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += tt; }
+          const u32 c1 = __shfl_sync(0xffffffffu, incl, 31);
+          if (c1 < 2) continue;                         // a lone triangle has no 3-simplex above it
           u32 o = top + incl - pc;
           while (bits) {
             const u32 j = lane * BPL + (__ffs((int)bits) - 1);
             bits &= bits - 1;
             stk[o++] = (2ULL << 60) | ((u64)j << 10) | i;
           }
-          top += __shfl_sync(0xffffffffu, incl, 31);
+          top += c1;
           __syncwarp();
           continue;
         }
@@ -306,7 +308,9 @@ count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
           for (int r = 0; r < RL; r++) cnt[r] += (d == (u32)(2 + r)) ? pc : 0u;
         }
         top -= take;
-        // children: one entry per member of P
+        // children: one entry per member of P.  A lone candidate has no child simplex of its own (the
+        // graph has no self loops: P & L[j] = 0 for P = {j}), so it is not pushed.
+        if (pc < 2) pc = 0;
         const bool deep = pc && d >= (u32)MAXIDS;
         const u32 want = deep ? 0u : pc;
         u32 incl = want;
