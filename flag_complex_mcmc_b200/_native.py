@@ -22,6 +22,7 @@ SYMBOLS = [
     "fcm_ensemble_create", "fcm_ensemble_destroy", "fcm_ensemble_set_bounds", "fcm_ensemble_set_kernel", "fcm_ensemble_step",
     "fcm_ensemble_step_trace", "fcm_ensemble_read", "fcm_ensemble_read_all", "fcm_ensemble_status",
     "fcm_ensemble_info", "fcm_ensemble_set_stats", "fcm_ensemble_index_info", "fcm_apply", "fcm_revert", "fcm_bounds_check",
+    "fcm_ensemble_edgebits_info", "fcm_ensemble_edgebits_slots", "fcm_ensemble_edgebits",
 ]
 
 
@@ -88,6 +89,9 @@ def lib():
     L.fcm_apply.argtypes = [vp, u32, vp, i32, vp, P(i32), vp, P(i32)]
     L.fcm_revert.argtypes = [vp, u32, vp, i32, vp, i32, vp, i32]
     L.fcm_bounds_check.argtypes = [vp, u32, P(i32)]
+    L.fcm_ensemble_edgebits_info.argtypes = [vp, P(u64), P(u64)]
+    L.fcm_ensemble_edgebits_slots.argtypes = [vp, vp]
+    L.fcm_ensemble_edgebits.argtypes = [vp, u32, u32, vp]
     for name in SYMBOLS:
         f = getattr(L, name)
         if f.restype is C.c_int and name not in ("fcm_abi_version", "fcm_device_count"):

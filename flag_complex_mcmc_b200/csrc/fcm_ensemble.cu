@@ -75,6 +75,7 @@ extern "C" int fcm_ensemble_destroy(fcm_ensemble* e) {
   if (e->ctx) { cudaSetDevice(e->ctx->device); cudaStreamSynchronize(e->ctx->stream); }
   for (void* q : e->dev_allocs) cudaFree(q);
   if (e->trace_dev) cudaFree(e->trace_dev);
+  if (e->eb_out_dev) cudaFree(e->eb_out_dev);
   delete e;
   return FCM_OK;
 }
@@ -469,6 +470,93 @@ extern "C" int fcm_ensemble_read_all(fcm_ensemble* e, uint64_t* fcs, int* lens, 
   }
   if (stats) { stats[0] = sk; stats[1] = ne; }
   if (err) { fcm_set_error("chain %u: %s", errchain, status_text(err)); return err; }
+  return FCM_OK;
+}
+
+// ---- io::BitOutput (src/io.rs:128-212): one packed bit per directed slot of the underlying
+//      undirected graph, slots sorted by (max, min, a < b) = pairs in (big, small) order, big -> small
+//      first.  A chain's orientation bits already hold exactly these bits in PAIR-ID order, so a sample
+//      is a static permutation of 2-bit fields: one thread per output word (16 pairs), packed on the
+//      device, and only ceil(2*npairs/8) bytes per chain cross PCIe instead of the edge list. ----
+__global__ void edgebits_pack_kernel(const EnsParams p, const u32* __restrict__ rank2pair, u32 chain_first,
+                                     u32 nchains, u32 words, u32* __restrict__ out) {
+  const u64 total = (u64)nchains * words;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (u64)gridDim.x * blockDim.x) {
+    const u32 ch = (u32)(i / words), w = (u32)(i - (u64)ch * words);
+    const u32* ori = p.ori + (u64)(chain_first + ch) * p.stride32;
+    u32 v = 0;
+#pragma unroll 4
+    for (u32 t = 0; t < 16; t++) {
+      const u64 r = (u64)w * 16 + t;
+      if (r < p.npairs) {
+        const u32 pair = __ldg(&rank2pair[r]);
+        v |= ((__ldcg(&ori[pair >> 4]) >> (2 * (pair & 15))) & 3u) << (2 * t);
+      }
+    }
+    out[i] = v;
+  }
+}
+
+static int edgebits_prepare(fcm_ensemble* e) {
+  if (e->eb_rank2pair_dev || e->p.npairs == 0) return FCM_OK;
+  const u64 np = e->p.npairs;
+  e->eb_rank2pair.resize(np);
+  for (u64 q = 0; q < np; q++) e->eb_rank2pair[q] = (u32)q;
+  const std::vector<uint2>& ab = e->pair_ab_host;
+  std::sort(e->eb_rank2pair.begin(), e->eb_rank2pair.end(), [&](u32 x, u32 y) {
+    return ab[x].x != ab[y].x ? ab[x].x < ab[y].x : ab[x].y < ab[y].y;
+  });
+  int rc = dev_alloc(e, &e->eb_rank2pair_dev, np);
+  if (rc) return rc;
+  FCM_CUDA(cudaMemcpyAsync(e->eb_rank2pair_dev, e->eb_rank2pair.data(), np * 4, cudaMemcpyHostToDevice, e->ctx->stream));
+  FCM_CUDA(cudaStreamSynchronize(e->ctx->stream));
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_edgebits_info(const fcm_ensemble* e, uint64_t* nslots, uint64_t* nbytes) {
+  REQUIRE(e, "ensemble is null");
+  if (nslots) *nslots = 2 * e->p.npairs;
+  if (nbytes) *nbytes = (2 * e->p.npairs + 7) / 8;
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_edgebits_slots(fcm_ensemble* e, uint32_t* slots_out) {
+  REQUIRE(e && slots_out, "ensemble/slots_out is null");
+  FCM_CUDA(cudaSetDevice(e->ctx->device));
+  int rc = edgebits_prepare(e);
+  if (rc) return rc;
+  for (u64 r = 0; r < e->p.npairs; r++) {
+    const uint2 ab = e->pair_ab_host[e->eb_rank2pair[r]];
+    slots_out[4 * r] = ab.x; slots_out[4 * r + 1] = ab.y;       // a > b: key (.., false) sorts first
+    slots_out[4 * r + 2] = ab.y; slots_out[4 * r + 3] = ab.x;
+  }
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_edgebits(fcm_ensemble* e, uint32_t chain_first, uint32_t nchains, uint8_t* out) {
+  REQUIRE(e && out, "ensemble/out is null");
+  REQUIRE(nchains >= 1 && (u64)chain_first + nchains <= e->p.nchains, "chain range out of bounds");
+  FCM_CUDA(cudaSetDevice(e->ctx->device));
+  const u64 nbytes = (2 * e->p.npairs + 7) / 8;
+  if (nbytes == 0) return FCM_OK;
+  int rc = edgebits_prepare(e);
+  if (rc) return rc;
+  const u32 words = (u32)((nbytes + 3) / 4);
+  if (nchains > e->eb_out_cap) {
+    if (e->eb_out_dev) FCM_CUDA(cudaFree(e->eb_out_dev));
+    e->eb_out_dev = nullptr; e->eb_out_cap = 0;
+    FCM_CUDA(cudaMalloc(&e->eb_out_dev, (size_t)nchains * words * 4));
+    e->eb_out_cap = nchains;
+  }
+  cudaStream_t s = e->ctx->stream;
+  const u64 total = (u64)nchains * words;
+  const int blocks = (int)std::min<u64>((total + 255) / 256, (u64)e->ctx->sm_count * 8);
+  edgebits_pack_kernel<<<blocks, 256, 0, s>>>(e->p, e->eb_rank2pair_dev, chain_first, nchains, words, e->eb_out_dev);
+  e->ctx->launches++;
+  FCM_CUDA(cudaGetLastError());
+  // rows of `words` 32-bit words on the device, rows of nbytes bytes for the caller (little endian: LSB-first bytes)
+  FCM_CUDA(cudaMemcpy2DAsync(out, nbytes, e->eb_out_dev, (size_t)words * 4, nbytes, nchains, cudaMemcpyDeviceToHost, s));
+  FCM_CUDA(cudaStreamSynchronize(s));
   return FCM_OK;
 }
 

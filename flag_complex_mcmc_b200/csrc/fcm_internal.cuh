@@ -123,6 +123,11 @@ struct fcm_ensemble {
   u64 trace_cap = 0;
   u32* edit_dev = nullptr;                // FCM_MAXEDIT * 2 (slot, add)
   u64* io_dev = nullptr;                  // pre/post exchange: 2*FCM_MAXD + 4
+  // BitOutput (src/io.rs:128-212), built on first use
+  std::vector<u32> eb_rank2pair;          // rank in (big, small) order -> pair id (host copy)
+  u32* eb_rank2pair_dev = nullptr;
+  u32* eb_out_dev = nullptr;              // packed samples, eb_out_cap chains x eb_words words
+  u32 eb_out_cap = 0;
 };
 
 // fcm_chain.cu

@@ -107,6 +107,15 @@ def read_flag_file(fname):
 
 
 # ---- device plumbing -------------------------------------------------------------------------------
+def save_flag_file(fname, n, edges):
+    """io::save_flag_file (src/io.rs:37-49): "dim 0:", n ones, "dim 1:", the edges sorted, weight 1."""
+    e = np.asarray(edges, dtype=np.uint32).reshape(-1, 2)
+    e = e[np.lexsort((e[:, 1], e[:, 0]))]
+    with open(fname, "w") as f:
+        f.write("dim 0:\n" + " ".join(["1"] * int(n)) + "\ndim 1:\n")
+        f.write("".join("%d %d 1\n" % (a, b) for a, b in e))
+
+
 class Context:
     """One CUDA device + stream (fcm_ctx)."""
 
@@ -396,6 +405,26 @@ class MCMCSampler:
         check(lib().fcm_bounds_check(self.h, int(chain), C.byref(ok)))
         return bool(ok.value)
 
+    # -- io::BitOutput (src/io.rs:128-212): samples packed on the device --
+    def edgebits_info(self):
+        ns, nb = C.c_uint64(), C.c_uint64()
+        check(lib().fcm_ensemble_edgebits_info(self.h, C.byref(ns), C.byref(nb)))
+        return {"nslots": ns.value, "nbytes": nb.value}
+
+    def edgebits_slots(self):
+        """BitOutput.edges: (nslots, 2) directed slots in file order (src/io.rs:152-159)."""
+        out = np.zeros((self.edgebits_info()["nslots"], 2), dtype=np.uint32)
+        check(lib().fcm_ensemble_edgebits_slots(self.h, ptr(out)))
+        return out
+
+    def edgebits(self, chain_first=0, nchains=None):
+        """One BitOutput::save row per chain: (nchains, nbytes) uint8 (src/io.rs:180-194)."""
+        nchains = self.nchains - chain_first if nchains is None else nchains
+        out = np.zeros((nchains, self.edgebits_info()["nbytes"]), dtype=np.uint8)
+        if out.size:
+            check(lib().fcm_ensemble_edgebits(self.h, int(chain_first), int(nchains), ptr(out)))
+        return out
+
     def close(self):
         if self.h:
             lib().fcm_ensemble_destroy(self.h)
@@ -426,3 +455,39 @@ def initialize_new_sampler(ctx, n, edges, seeds, target_relaxation=0.01, simple=
     s.initial_flag_count = flag_count
     s.ncliques = ncliques
     return s
+
+
+class BitOutput:
+    """io::BitOutput (src/io.rs:128-212) for one chain of a device ensemble: `dir/graph.flag` +
+    `dir/<k>.edgebits` files of `chunk_size` samples each; every save() is one device-side pack and
+    a D2H copy of ceil(nslots/8) bytes."""
+
+    def __init__(self, sampler, directory, chain=0, n=None, edges=None):
+        import os
+        os.makedirs(directory, exist_ok=True)
+        self.sampler, self.dir, self.chain = sampler, directory, chain
+        self.edges = sampler.edgebits_slots()
+        if edges is not None:
+            save_flag_file(os.path.join(directory, "graph.flag"), n, edges)
+        # src/io.rs:161: max(2e9 / (len/8), 1); the reference divides by zero below 8 slots
+        self.chunk_size = max(2_000_000_000 // max(len(self.edges) // 8, 1), 1)
+        self.index_in_file = 0
+        self.index_in_dir = 0
+        self.current_file = None
+
+    def save(self):
+        import os
+        if self.index_in_file == 0:
+            assert self.current_file is None
+            self.current_file = open(os.path.join(self.dir, "%d.edgebits" % self.index_in_dir), "wb")
+        self.current_file.write(self.sampler.edgebits(self.chain, 1)[0].tobytes())
+        self.index_in_file += 1
+        if self.index_in_file == self.chunk_size:
+            self.current_file.close()
+            self.current_file = None
+            self.index_in_file = 0
+            self.index_in_dir += 1
+
+    def flush(self):
+        if self.current_file is not None:
+            self.current_file.flush()

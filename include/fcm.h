@@ -184,6 +184,19 @@ int fcm_revert(fcm_ensemble* e, uint32_t chain, const uint32_t* edits3, int nedi
 /* Bounds::check (src/lib.rs:157-160) of one chain's current state: *ok = 0/1 */
 int fcm_bounds_check(fcm_ensemble* e, uint32_t chain, int* ok);
 
+/* ------------------------------------------------------------------------------------------------
+ * 5. io::BitOutput (src/io.rs:128-212): the `.edgebits` sample format, packed on the device.
+ *    Slots = both directions of every adjacent pair, sorted by (max(a,b), min(a,b), a < b)
+ *    (src/io.rs:152-159); a sample = one bit per slot (set iff the chain's graph has that directed
+ *    edge), LSB-first in bytes, ceil(nslots/8) bytes (src/io.rs:180-194).
+ * ---------------------------------------------------------------------------------------------- */
+int fcm_ensemble_edgebits_info(const fcm_ensemble* e, uint64_t* nslots, uint64_t* nbytes);
+/* BitOutput.edges: slots_out[2*nslots] = (a, b) of every slot in file order */
+int fcm_ensemble_edgebits_slots(fcm_ensemble* e, uint32_t* slots_out);
+/* BitOutput::save for chains [chain_first, chain_first + nchains): synchronises, packs on the device
+ * and writes nchains rows of nbytes bytes to out (host). */
+int fcm_ensemble_edgebits(fcm_ensemble* e, uint32_t chain_first, uint32_t nchains, uint8_t* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -30,6 +30,9 @@
 // Build: see oracle/Makefile (g++ -O3 -march=native -shared).  C ABI at the bottom (orc_*).
 
 #include <algorithm>
+#include <unordered_set>
+#include <tuple>
+#include <array>
 #include <atomic>
 #include <cmath>
 #include <cstdint>
@@ -743,6 +746,37 @@ u64 orc_nbhd_stats(void* h, u64* sum_len, u32* max_len) {
   Sampler* s = (Sampler*)h; u64 sum = 0; u32 mx = 0;
   for (auto& kv : s->state.edge_neighborhood) { sum += kv.second.size(); mx = std::max<u32>(mx, kv.second.size()); }
   *sum_len = sum; *max_len = mx; return s->state.edge_neighborhood.size();
+}
+
+// io::BitOutput (src/io.rs:128-212).  new(): the slot list = edges of the initial graph plus their
+// reverses, sorted by the key (max(a,b), min(a,b), a < b), deduplicated (:152-159).  save(): one bit
+// per slot, set iff the current graph has that directed edge, packed LSB-first into bytes, a last
+// partial byte is written as it stands (:180-194).
+// orc_edgebits_slots: slots_out[2*nslots] (pass null to get the count only) -> nslots
+u64 orc_edgebits_slots(u64 ne0, const u32* edges0, u32* slots_out) {
+  std::vector<std::array<u32, 2>> ed;
+  ed.reserve(2 * ne0);
+  for (u64 i = 0; i < ne0; i++) ed.push_back({edges0[2 * i], edges0[2 * i + 1]});
+  for (u64 i = 0; i < ne0; i++) ed.push_back({edges0[2 * i + 1], edges0[2 * i]});
+  auto key = [](const std::array<u32, 2>& e) { return std::make_tuple(std::max(e[0], e[1]), std::min(e[0], e[1]), e[0] < e[1]); };
+  std::sort(ed.begin(), ed.end(), [&](const std::array<u32, 2>& x, const std::array<u32, 2>& y) { return key(x) < key(y); });
+  ed.erase(std::unique(ed.begin(), ed.end()), ed.end());
+  if (slots_out) for (size_t i = 0; i < ed.size(); i++) { slots_out[2 * i] = ed[i][0]; slots_out[2 * i + 1] = ed[i][1]; }
+  return ed.size();
+}
+// orc_edgebits_save: one sample; out holds ceil(nslots/8) bytes
+void orc_edgebits_save(u64 nslots, const u32* slots, u64 ne, const u32* edges, unsigned char* out) {
+  std::unordered_set<u64> have;
+  have.reserve(ne * 2);
+  for (u64 i = 0; i < ne; i++) have.insert(((u64)edges[2 * i] << 32) | edges[2 * i + 1]);
+  unsigned char bit = 1, byte = 0;
+  u64 o = 0;
+  for (u64 i = 0; i < nslots; i++) {
+    if (have.count(((u64)slots[2 * i] << 32) | slots[2 * i + 1])) byte |= bit;
+    bit = (unsigned char)((bit << 1) | (bit >> 7));     // u8::rotate_left(1)
+    if (bit == 1) { out[o++] = byte; byte = 0; }
+  }
+  if (bit != 1) out[o++] = byte;
 }
 
 }  // extern "C"

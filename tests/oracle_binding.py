@@ -66,6 +66,10 @@ def lib():
     L.orc_bounds_check.argtypes = [vp]
     L.orc_nbhd_stats.argtypes = [vp, P(u64), P(u32)]
     L.orc_nbhd_stats.restype = u64
+    L.orc_edgebits_slots.argtypes = [u64, vp, vp]
+    L.orc_edgebits_slots.restype = u64
+    L.orc_edgebits_save.argtypes = [u64, vp, u64, vp, vp]
+    L.orc_edgebits_save.restype = None
     _lib = L
     return L
 
@@ -111,6 +115,23 @@ def ncliques(n, edges, nthreads=1):
     ln = C.c_int()
     lib().orc_ncliques(int(n), e.shape[0], _p(e), int(nthreads), _p(out), C.byref(ln))
     return [int(x) for x in out[:ln.value]]
+
+
+def edgebits_slots(edges0):
+    """BitOutput::new's slot list (src/io.rs:152-159) -> (nslots, 2) uint32"""
+    e = _e(edges0)
+    ns = lib().orc_edgebits_slots(e.shape[0], _p(e), None)
+    out = np.zeros((ns, 2), dtype=np.uint32)
+    lib().orc_edgebits_slots(e.shape[0], _p(e), _p(out))
+    return out
+
+
+def edgebits_save(slots, edges):
+    """BitOutput::save (src/io.rs:180-194) of the graph with directed edges `edges` -> uint8[ceil(nslots/8)]"""
+    sl, e = _e(slots), _e(edges)
+    out = np.zeros((sl.shape[0] + 7) // 8, dtype=np.uint8)
+    lib().orc_edgebits_save(sl.shape[0], _p(sl), e.shape[0], _p(e), _p(out))
+    return out
 
 
 def read_flag_file(path):

@@ -277,3 +277,32 @@ def test_statistic_switch_does_not_change_the_chain(ctx, graphs):
     assert c["nonempty"] > b["nonempty"]
     compare_chain(s, 1, o)
     s.close()
+
+
+@pytest.mark.parametrize("name,kernel", [("c2_chunglu_279", 0), ("counterexample_any_order", 2), ("bug_calc_relax_de", 1)])
+def test_edgebits_match_bitoutput_of_the_chain_graph(name, kernel, ctx, graphs, tmp_path):
+    # io::BitOutput (src/io.rs:128-212): device-packed sample == oracle's save() of the chain's edge list
+    n, e = graphs[name]
+    seeds = [0, 1, 2, 3, 4]
+    s = fcm.initialize_new_sampler(ctx, n, e, seeds, target_relaxation=0.01, simple=True)
+    s.set_kernel(kernel)
+    slots = s.edgebits_slots()
+    assert np.array_equal(slots, orc.edgebits_slots(e))
+    info = s.edgebits_info()
+    assert info["nslots"] == slots.shape[0] and info["nbytes"] == (slots.shape[0] + 7) // 8
+    bo = fcm.BitOutput(s, str(tmp_path / "out"), chain=3, n=n, edges=e)
+    want_file = b""
+    for rnd in range(3):
+        bits = s.edgebits()
+        assert bits.shape == (len(seeds), info["nbytes"])
+        for k in range(len(seeds)):
+            assert np.array_equal(bits[k], orc.edgebits_save(slots, s.read(k)["edges"])), (rnd, k)
+        assert np.array_equal(s.edgebits(2, 2), bits[2:4])
+        bo.save()
+        want_file += bits[3].tobytes()
+        s.step(1500)
+    bo.flush()
+    assert open(str(tmp_path / "out" / "0.edgebits"), "rb").read() == want_file
+    n2, e2 = ds.read_flag_file(str(tmp_path / "out" / "graph.flag"))
+    assert n2 == n and sorted(map(tuple, e2.tolist())) == sorted(map(tuple, e.tolist()))
+    s.close()

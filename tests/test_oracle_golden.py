@@ -163,3 +163,51 @@ def test_read_flag_file_mirror(tmp_path):
     n, e = ds.read_flag_file(str(p))
     n2, e2 = orc.read_flag_file(str(p))
     assert n == n2 == 4 and np.array_equal(e, e2) and e.tolist() == [[0, 1], [2, 3], [3, 0]]
+
+
+def _bitoutput_literal(edges0, edges):
+    """src/io.rs:152-159 + :180-194 as literal Python (small inputs only)."""
+    ed = [tuple(x) for x in np.asarray(edges0).tolist()]
+    ed += [(b, a) for a, b in ed]
+    ed.sort(key=lambda ab: (max(ab), min(ab), ab[0] < ab[1]))
+    slots = [ed[i] for i in range(len(ed)) if i == 0 or ed[i] != ed[i - 1]]
+    have = set(tuple(x) for x in np.asarray(edges).tolist())
+    out, bit, byte = [], 1, 0
+    for s in slots:
+        if s in have:
+            byte |= bit
+        bit = ((bit << 1) | (bit >> 7)) & 0xFF
+        if bit == 1:
+            out.append(byte)
+            byte = 0
+    if bit != 1:
+        out.append(byte)
+    return np.array(slots, dtype=np.uint32).reshape(-1, 2), np.array(out, dtype=np.uint8)
+
+
+def test_edgebits_oracle_matches_literal_bitoutput(graphs):
+    # toy: 0->1, 1->0, 2->0, 1->2 : pairs (1,0),(2,0),(2,1); slots (1,0),(0,1),(2,0),(0,2),(2,1),(1,2)
+    e0 = np.array([[0, 1], [1, 0], [2, 0], [1, 2]], dtype=np.uint32)
+    sl = orc.edgebits_slots(e0)
+    assert sl.tolist() == [[1, 0], [0, 1], [2, 0], [0, 2], [2, 1], [1, 2]]
+    assert orc.edgebits_save(sl, e0).tolist() == [0b100111]
+    for name in ("counterexample_any_order", "c2_chunglu_279"):
+        n, e = graphs[name]
+        flipped = e.copy()
+        flipped[::3] = flipped[::3, ::-1]                  # some other orientation of the same pairs
+        for cur in (e, flipped):
+            sl_want, bits_want = _bitoutput_literal(e, cur)
+            sl = orc.edgebits_slots(e)
+            assert np.array_equal(sl, sl_want), name
+            assert np.array_equal(orc.edgebits_save(sl, cur), bits_want), name
+
+
+def test_save_flag_file_round_trip(tmp_path, graphs):
+    n, e = graphs["c2_chunglu_279"]
+    f = str(tmp_path / "g.flag")
+    ds.save_flag_file(f, n, e)
+    n2, e2 = ds.read_flag_file(f)
+    n3, e3 = orc.read_flag_file(f)
+    assert n2 == n3 == n
+    assert np.array_equal(e2, e3)
+    assert sorted(map(tuple, e2.tolist())) == sorted(map(tuple, e.tolist()))

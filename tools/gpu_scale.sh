@@ -1,0 +1,6 @@
+# bench at N GPUs of one box (torchrun, one rank per GPU); $1 = N
+set -x
+N=${1:-2}
+python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 5 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?"
+tail -3 gpurun_out/bench_n$N.err
+cat gpurun_out/bench_n$N.json
