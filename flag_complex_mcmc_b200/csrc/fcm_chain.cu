@@ -278,22 +278,24 @@ __device__ int local_count_any(const u64* M, int K, int KW, int lane, u64* out, 
 enum { FL_DEEP = 0, FL_TOP = 1, FL_ERR = 2, FL_RC = 3, FL_K = 4, FL_LEN = 5, FL_OVF = 6, FL_E = 8, FL_ND = 9, FL_ACC = 10, FL_FCLEN = 11 };
 enum { PK_KIND = 0, PK_SLOT, PK_DELME, PK_IDX, PK_DIDX, PK_DPAIR, PK_LAST, PK_QPOS, PK_TA, PK_TB, PK_TDM0, PK_TDM1,
        PK_CA, PK_CD, PK_OA, PK_OD, PK_ORIA, PK_ORID };
+#define CQ_MAXPAIRS 256                 // entries of new_edges / old_edges in clique_swap (src/lib.rs:256-270)
+#define CQ_BYTES (3 * FCM_MAXCQ * 4 + 2 * CQ_MAXPAIRS * 8 + 64)
 struct WarpSmem {
   u64 *M, *fc, *pre, *post;
-  u32 *verts, *edits;
+  u32 *verts, *edits, *cq;
   u64 *A, *deep;
   u32 *cv, *cv2, *rowoff;
   int* dflag;
   u32* tile;
 };
 // tile = false: the hot path reads the clique index, no staging tile is needed
-__host__ __device__ inline size_t warp_smem_bytes(u32 Kcap, u32 KWcap, bool tile) {
-  size_t full = (size_t)Kcap * KWcap * 8 + 3 * FCM_MAXD * 8 + (size_t)Kcap * 4 + FCM_MAXEDIT * 2 * 4;
+__host__ __device__ inline size_t warp_smem_bytes(u32 Kcap, u32 KWcap, bool tile, bool cq) {
+  size_t full = (size_t)Kcap * KWcap * 8 + 3 * FCM_MAXD * 8 + (size_t)(Kcap + (Kcap & 1)) * 4 + FCM_MAXEDIT * 2 * 4 + (cq ? CQ_BYTES : 0);
   if (tile && full < TILE_WORDS * 4) full = TILE_WORDS * 4;
   return SM_TILE + full;
 }
-size_t fcm_chain_smem_per_warp(u32 Kcap, u32 KWcap) { return (warp_smem_bytes(Kcap, KWcap, true) + 15) & ~(size_t)15; }
-static size_t chain_smem_per_warp_mode(u32 Kcap, u32 KWcap, bool tile) { return (warp_smem_bytes(Kcap, KWcap, tile) + 15) & ~(size_t)15; }
+size_t fcm_chain_smem_per_warp(u32 Kcap, u32 KWcap, bool cliques) { return (warp_smem_bytes(Kcap, KWcap, true, cliques) + 15) & ~(size_t)15; }
+static size_t chain_smem_per_warp_mode(u32 Kcap, u32 KWcap, bool tile, bool cq) { return (warp_smem_bytes(Kcap, KWcap, tile, cq) + 15) & ~(size_t)15; }
 
 __device__ __forceinline__ WarpSmem carve(unsigned char* base, u32 Kcap, u32 KWcap) {
   WarpSmem s;
@@ -309,7 +311,8 @@ __device__ __forceinline__ WarpSmem carve(unsigned char* base, u32 Kcap, u32 KWc
   s.pre = s.fc + FCM_MAXD;
   s.post = s.pre + FCM_MAXD;
   s.verts = (u32*)(s.post + FCM_MAXD);
-  s.edits = s.verts + Kcap;
+  s.edits = s.verts + Kcap + (Kcap & 1);
+  s.cq = s.edits + 2 * FCM_MAXEDIT;                     // clique-move scratch (only sized when the ensemble has clique moves)
   return s;
 }
 
@@ -824,6 +827,236 @@ __device__ __forceinline__ void update_adjacency(const EnsParams& p, u32* cb, u3
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// clique moves: Transition::clique_permute / clique_swap (src/lib.rs:214-290).  Cold path: lane 0
+// builds the transition in shared memory (the draws, util::random_perm, vec_intersect / vec_setminus,
+// the sort / dedup / contains logic of clique_swap), the warp gathers the has_edge bits it needs and
+// then runs the reference's literal apply_transition: full pre/post counts of the union neighbourhood.
+// ---------------------------------------------------------------------------------------------------
+// rand 0.8 UniformInt<u32>::sample_single(0, range) as used by seq::gen_index (choose / shuffle):
+// next_u32 = upper half of next_u64 (rand_xoshiro 0.6), 32 x 32 widening multiply, rejection zone
+__device__ __forceinline__ u32 gen_range_u32(Rng& g, u32 range) {
+  const u32 zone = (range << __clz((int)range)) - 1u;
+  for (;;) {
+    const u32 v = (u32)(g.next() >> 32);
+    const u64 m = (u64)v * range;
+    if ((u32)m <= zone) return (u32)(m >> 32);
+  }
+}
+// util::random_perm(l, h) (src/util.rs:28-32): out[0..h-l) = shuffle of l..h
+__device__ void random_perm_dev(Rng& g, u32 l, u32 h, u32* out) {
+  const u32 len = h - l;
+  for (u32 i = 0; i < len; i++) out[i] = l + i;
+  for (u32 i = len; i-- > 1;) {
+    const u32 j = gen_range_u32(g, i + 1);
+    const u32 t = out[i]; out[i] = out[j]; out[j] = t;
+  }
+}
+// pair id of the adjacent pair {a, b} (binary search in the sorted keys) or FCM_NONE
+__device__ u32 find_pair(const EnsParams& p, u32 a, u32 b) {
+  const u64 key = ((u64)max(a, b) << 32) | min(a, b);
+  u64 lo = 0, hi = p.npairs;
+  while (lo < hi) { const u64 mid = (lo + hi) >> 1; if (__ldg(&p.pkeys[mid]) < key) lo = mid + 1; else hi = mid; }
+  if (lo < p.npairs && __ldg(&p.pkeys[lo]) == key) return __ldg(&p.pkey_pair[lo]);
+  return FCM_NONE;
+}
+__device__ void sort_dedup_u64(u64* a, int& n) {       // lane 0, short lists: insertion sort + unique
+  for (int i = 1; i < n; i++) { const u64 x = a[i]; int j = i; while (j > 0 && a[j - 1] > x) { a[j] = a[j - 1]; j--; } a[j] = x; }
+  int m = 0;
+  for (int i = 0; i < n; i++) if (i == 0 || a[i] != a[m - 1]) a[m++] = a[i];
+  n = m;
+}
+
+// kind 2 = clique_permute, 3 = clique_swap.  The chain's RNG state (after the move-kind draw) and all
+// other state are in HBM (the hot stretch has been closed).  Returns 0 or an FCM_E* code.
+__device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned char* wb, int lane, int kind,
+                                        fcm_trace_rec* tr_out, bool red, bool instr) {
+  const WarpSmem s = carve(wb, p.Kcap, p.KWcap);
+  int* const sflag = (int*)(wb + SM_FLAG);
+  ChainState* const st = &p.st[chain];
+  u32* const cb = (u32*)p.adj + (u64)chain * p.stride32;
+  const u32 W32 = 2 * p.W;
+  u32* const dv = s.cq;                                 // d = c ++ a ++ b            (src/lib.rs:240)
+  u32* const perm = s.cq + FCM_MAXCQ;                   // perm_d (swap) / perm (permute)
+  u32* const H = s.cq + 2 * FCM_MAXCQ;                  // H[i] bit j = has_edge(d[i], d[j])
+  u32* const hdr = s.cq + 3 * FCM_MAXCQ;                // [0] n_d [1] n_c [2] n_a [3] status [4] i1 [5] i2 [6] ord [7] nedit
+  u64* const newe = (u64*)(hdr + 16);
+  u64* const olde = newe + CQ_MAXPAIRS;
+  // ---- the draws and the vertex lists (lane 0) ----
+  if (lane == 0) {
+    Rng g; g.s0 = st->rng[0]; g.s1 = st->rng[1]; g.s2 = st->rng[2]; g.s3 = st->rng[3];
+    int status = 0;
+    const u64 r = g.next();                             // clique_order_distribution.sample(rng)
+    const double v = __longlong_as_double((long long)((r >> 12) | 0x3ff0000000000000ULL)) - 1.0;
+    const double chosen = __dadd_rn(__dmul_rn(v, p.cq_scale), 0.0);
+    int ord = 0;
+    while (ord < p.cq_norders - 1 && p.cq_cum[ord] <= chosen) ord++;
+    const u32 ncl = p.cq_count[ord], k = (u32)ord + 1;
+    u32 n_d = 0, n_c = 0, n_a = 0, i1 = 0, i2 = 0;
+    if (ncl == 0) status = FCM_EINVAL;                  // reference: choose() -> None -> unwrap panics
+    else if (kind == 2) {
+      i1 = gen_range_u32(g, ncl);
+      if (k > FCM_MAXCQ) status = FCM_ELIMIT;
+      else {
+        const u32* cl = p.cq_verts + p.cq_base[ord] + (u64)i1 * k;
+        for (u32 i = 0; i < k; i++) dv[i] = __ldg(&cl[i]);
+        n_d = k; n_c = k;
+        random_perm_dev(g, 0, k, perm);
+      }
+    } else {
+      i1 = gen_range_u32(g, ncl);
+      i2 = gen_range_u32(g, ncl);
+      const u32* m1 = p.cq_verts + p.cq_base[ord] + (u64)i1 * k;
+      const u32* m2 = p.cq_verts + p.cq_base[ord] + (u64)i2 * k;
+      if (k > FCM_MAXCQ) status = FCM_ELIMIT;
+      else {
+        // c = vec_intersect(m1, m2) in m1's order; d = c ++ (m1 - c) ++ (m2 - c)
+        u32 inm2 = 0, inm1 = 0;                         // bit i: m1[i] is in m2 / m2[i] is in m1
+        for (u32 i = 0; i < k; i++)
+          for (u32 j = 0; j < k; j++)
+            if (__ldg(&m1[i]) == __ldg(&m2[j])) { inm2 |= 1u << i; inm1 |= 1u << j; }
+        n_c = (u32)__popc(inm2); n_a = k - n_c;
+        if (2 * k - n_c > FCM_MAXCQ) status = FCM_ELIMIT;
+        else {
+          for (u32 i = 0; i < k; i++) if ((inm2 >> i) & 1u) dv[n_d++] = __ldg(&m1[i]);
+          for (u32 i = 0; i < k; i++) if (!((inm2 >> i) & 1u)) dv[n_d++] = __ldg(&m1[i]);
+          for (u32 i = 0; i < k; i++) if (!((inm1 >> i) & 1u)) dv[n_d++] = __ldg(&m2[i]);
+          // perm_d = perm_c ++ perm_b ++ perm_a, drawn in the order c, a, b (src/lib.rs:247-251)
+          u32* const tmp = (u32*)olde;                  // free until the transition is built
+          random_perm_dev(g, 0, n_c, perm);
+          random_perm_dev(g, n_c, n_c + n_a, tmp);      // perm_a
+          random_perm_dev(g, n_c + n_a, n_d, perm + n_c);   // perm_b sits right behind perm_c
+          for (u32 i = 0; i < n_a; i++) perm[n_c + (n_d - n_c - n_a) + i] = tmp[i];
+        }
+      }
+    }
+    st->rng[0] = g.s0; st->rng[1] = g.s1; st->rng[2] = g.s2; st->rng[3] = g.s3;
+    hdr[0] = n_d; hdr[1] = n_c; hdr[2] = n_a; hdr[3] = (u32)status; hdr[4] = i1; hdr[5] = i2; hdr[6] = (u32)ord; hdr[7] = 0;
+  }
+  __syncwarp();
+  if (hdr[3]) { const int e = (int)hdr[3]; if (lane == 0) st->err = e; return e; }
+  const int n_d = (int)hdr[0], n_c = (int)hdr[1], n_a = (int)hdr[2];
+  // ---- has_edge among d: lane j probes column d[j] of row d[i] ----
+  {
+    const u32 col = lane < n_d ? dv[lane] : 0u;
+    for (int i = 0; i < n_d; i++) {
+      const u32 w = lane < n_d ? __ldcg(&cb[dv[i] * W32 + (col >> 5)]) : 0u;
+      const u32 b = __ballot_sync(FULL, lane < n_d && ((w >> (col & 31)) & 1u));
+      if (lane == 0) H[i] = b;
+    }
+  }
+  __syncwarp();
+  // ---- the transition: change_edges as (from, to, add) in s.edits, then as (slot, add) ----
+  if (lane == 0) {
+    int ne = 0, status = 0;
+    u32* const ed = s.edits;                            // 2 words per edit: (from << 16 | to) indices into d, add
+    auto push = [&](u32 from, u32 to, u32 add) {
+      if (ne >= FCM_MAXEDIT) { status = FCM_ELIMIT; return; }
+      ed[2 * ne] = (from << 16) | to; ed[2 * ne + 1] = add; ne++;
+    };
+    if (kind == 2) {
+      for (int i = 0; i < n_d; i++)
+        for (int j = 0; j < n_d; j++) {
+          const u32 pre = (H[perm[i]] >> perm[j]) & 1u, post = (H[i] >> j) & 1u;
+          if (pre != post) push(perm[i], perm[j], post);
+        }
+    } else {
+      // new_edges / old_edges as keys (from vertex << 32 | to vertex): [Node;2] order = numeric order
+      int nn = 0, no = 0;
+      auto visit = [&](int i, int j) {
+        if (!((H[i] >> j) & 1u)) return;
+        if (nn >= CQ_MAXPAIRS) { status = FCM_ELIMIT; return; }
+        newe[nn++] = ((u64)dv[perm[i]] << 32) | dv[perm[j]];
+        olde[no++] = ((u64)dv[i] << 32) | dv[j];
+      };
+      for (int i = 0; i < n_c + n_a; i++) for (int j = 0; j < n_c + n_a; j++) visit(i, j);
+      for (int ii = 0; ii < n_d - n_a; ii++) {
+        const int i = ii < n_c ? ii : ii + n_a;
+        for (int jj = 0; jj < n_d - n_a; jj++) visit(i, jj < n_c ? jj : jj + n_a);
+      }
+      sort_dedup_u64(newe, nn);
+      sort_dedup_u64(olde, no);
+      auto local = [&](u32 vtx) { for (int i = 0; i < n_d; i++) if (dv[i] == vtx) return (u32)i; return 0u; };
+      for (int x = 0; x < nn && !status; x++) {
+        int at = -1;
+        for (int y = 0; y < no; y++) if (olde[y] == newe[x]) { at = y; break; }
+        if (at >= 0) { for (int y = at; y + 1 < no; y++) olde[y] = olde[y + 1]; no--; }
+        else push(local((u32)(newe[x] >> 32)), local((u32)newe[x]), 1u);
+      }
+      for (int y = 0; y < no && !status; y++) push(local((u32)(olde[y] >> 32)), local((u32)olde[y]), 0u);
+    }
+    hdr[3] = (u32)status; hdr[7] = (u32)ne;
+  }
+  __syncwarp();
+  if (hdr[3]) { const int e = (int)hdr[3]; if (lane == 0) st->err = e; return e; }
+  const int nedit = (int)hdr[7];
+  for (int t = lane; t < nedit; t += 32) {              // (from, to) -> slot
+    const u32 ft = s.edits[2 * t], from = dv[ft >> 16], to = dv[ft & 0xffffu];
+    const u32 pair = find_pair(p, from, to);
+    s.edits[2 * t] = pair == FCM_NONE ? FCM_NONE : 2 * pair + (from > to ? 0u : 1u);
+  }
+  __syncwarp();
+  for (int t = 0; t < nedit; t++) if (s.edits[2 * t] == FCM_NONE) { if (lane == 0) st->err = FCM_ENOTADJ; return FCM_ENOTADJ; }
+  // ---- State::apply_transition (src/lib.rs:61-79) ----
+  Chain c;
+  c.adj = (u64*)cb; c.items = cb + p.off_items; c.pos = cb + p.off_pos; c.dbl = cb + p.off_dbl; c.dblpos = cb + p.off_dblpos;
+  c.ori = cb + p.off_ori;
+  c.E = st->E; c.ND = st->ND;
+  const u64 fc = st->flag_count[lane];
+  int len = st->fc_len, K = 0, prelen = 0, postlen = 0, rc = 0;
+  u64 fnew = fc;
+  if (nedit) {
+    rc = transition_counts(p, c, s, nedit, lane, K, prelen, postlen);
+    if (!rc) {
+      const u64 pr = lane < min(prelen, len) ? s.pre[lane] : 0;
+      if (__any_sync(FULL, fc < pr)) rc = FCM_EASSERT;
+      else fnew = fc - pr + (lane < postlen ? s.post[lane] : 0);
+      len = max(len, max(postlen, prelen));
+    }
+  }
+  if (rc) { if (lane == 0) st->err = rc; return rc; }
+  const bool ok = bounds_ok(p, fnew, lane);
+  // containers: the edits in order; a rejected transition is applied and reverted like the reference
+  // does (src/lib.rs:186-191), which leaves the containers in a different ORDER than before
+  for (int pass = 0; pass < (ok ? 1 : 2); pass++)
+    for (int t = 0; t < nedit; t++) {
+      const u32 slot = s.edits[2 * t];
+      const bool add = (s.edits[2 * t + 1] != 0) != (pass == 1);
+      if (add) c_add_edge(c, slot, lane); else c_remove_edge(c, slot, lane);
+    }
+  if (ok && lane == 0)
+    for (int t = 0; t < nedit; t++) {                   // adjacency rows + orientation bits
+      const u32 slot = s.edits[2 * t];
+      const bool add = s.edits[2 * t + 1] != 0;
+      const uint2 ft = slot_edge(p, slot);
+      u32* const w = &cb[ft.x * W32 + (ft.y >> 5)];
+      const u32 m = 1u << (ft.y & 31);
+      if (red) { if (add) atomicOr(w, m); else atomicAnd(w, ~m); }
+      else *w = add ? (*w | m) : (*w & ~m);
+      u32* const o = &c.ori[slot >> 5];
+      const u32 om = 1u << (slot & 31);
+      const u32 ov = __ldcg(o);
+      *o = add ? (ov | om) : (ov & ~om);
+    }
+  __syncwarp();
+  if (ok) st->flag_count[lane] = fnew;
+  if (lane == 0) {
+    st->E = c.E; st->ND = c.ND;
+    st->fc_len = len;
+    st->sampled += 1; st->accepted += ok;
+    if (instr && nedit) { st->sumK += (u64)K; st->nonempty += 1; }
+    if (tr_out) {
+      fcm_trace_rec tr;
+      tr.flags = (u32)kind | (ok ? FCM_TR_ACCEPT : 0u) | (nedit ? 0u : FCM_TR_EMPTY);
+      tr.a = hdr[4]; tr.b = kind == 3 ? hdr[5] : 0u; tr.dm0 = hdr[6]; tr.dm1 = (u32)nedit; tr.K = (u32)K; tr.draws = 0; tr.pad = 0;
+      *tr_out = tr;
+    }
+    sflag[FL_E] = (int)c.E; sflag[FL_ND] = (int)c.ND;   // the hot stretch keeps both in shared memory
+  }
+  __syncwarp();
+  return 0;
+}
+
 // One sampled proposal (parked in shared memory by the hot loop) finished by the general code:
 // two-slot lists (32 < c <= 64), more than 32 tagged copies, simplices beyond the register levels,
 // lists beyond FAST_C (full path) or a forced full path.  Reads and writes the chain's state in HBM.
@@ -833,6 +1066,7 @@ __device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned ch
   u64* const sdeep = (u64*)(wb + SM_DEEP);
   int* const sflag = (int*)(wb + SM_FLAG);
   const int kind = (int)park[PK_KIND];
+  if (kind >= 2) return clique_step(p, chain, wb, lane, kind, tr_out, red, instr);
   const u32 slot = park[PK_SLOT], delme = park[PK_DELME], idx = park[PK_IDX], didx = park[PK_DIDX], dpair = park[PK_DPAIR];
   const u32 last = park[PK_LAST], qpos = park[PK_QPOS], ta = park[PK_TA], tb = park[PK_TB], tdm0 = park[PK_TDM0], tdm1 = park[PK_TDM1];
   const int cA = (int)park[PK_CA], cD = (int)park[PK_CD];
@@ -946,7 +1180,17 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
       const double v = __longlong_as_double((long long)((r >> 12) | 0x3ff0000000000000ULL)) - 1.0;
       const double chosen = __dadd_rn(__dmul_rn(v, p.scale), 0.0);
       const int kind = (p.cum[0] <= chosen) + (p.cum[1] <= chosen) + (p.cum[2] <= chosen);
-      if (kind > 1) { err = FCM_EUNSUPPORTED; break; }
+      if (kind > 1) {
+        // clique move: the general code takes it from here (the kind draw is consumed)
+        if (p.cq_norders == 0) { err = FCM_EUNSUPPORTED; break; }
+        if (lane == 0) {
+          *(ulonglong2*)&srng[0] = make_ulonglong2(g.s0, g.s1); *(ulonglong2*)&srng[2] = make_ulonglong2(g.s2, g.s3);
+          spark[PK_KIND] = (u32)kind;
+        }
+        cold = true;
+        __syncwarp();
+        break;
+      }
       // ---- single_edge_flip (src/lib.rs:292-299) / double_edge_move (:304-325): the draws.  Loads are
       //      written in the order they become issuable so that independent ones overlap. ----
       bool live = false;                                // a non-empty transition
@@ -1290,9 +1534,18 @@ int fcm_chain_launch_replicate(fcm_ensemble* e) {
 template <bool IDX, bool INSTR>
 static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
   const EnsParams& p = e->p;
-  const size_t per_warp = chain_smem_per_warp_mode(p.Kcap, p.KWcap, !IDX);
+  const size_t per_warp = chain_smem_per_warp_mode(p.Kcap, p.KWcap, !IDX, e->cliques != 0);
+  // warps per block: the choice that keeps most warps resident on one SM (big neighbourhood tiles of
+  // ensembles with clique moves fit better in smaller blocks)
   int wpb = 4;
-  while (wpb > 1 && per_warp * wpb > e->ctx->smem_optin) wpb >>= 1;
+  {
+    size_t best = 0;
+    for (int w = 4; w >= 1; w >>= 1) {
+      if (per_warp * w > e->ctx->smem_optin) continue;
+      const size_t resident = std::min<size_t>(7, (size_t)(227 * 1024) / (per_warp * w + 1024)) * w;
+      if (resident > best) { best = resident; wpb = w; }
+    }
+  }
   if (per_warp * wpb > e->ctx->smem_optin) { fcm_set_error("neighbourhood tile does not fit shared memory"); return FCM_ELIMIT; }
   const size_t smem = per_warp * wpb;
   FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -70,6 +70,81 @@ static int copy_bounds(EnsParams& p, const u64* mn, int nmin, const u64* mx, int
   return FCM_OK;
 }
 
+// rand 0.8 WeightedIndex<f64>::new for any number of weights (clique_order_distribution,
+// src/bin/sample.rs:87-88): cum[i] = w[0] + .. + w[i], i < n - 1
+static int weighted_index_init_n(const std::vector<double>& w, double* cum, double* scale) {
+  if (w.empty()) { fcm_set_error("no clique orders"); return FCM_EINVAL; }
+  double total = w[0];
+  for (size_t i = 1; i < w.size(); i++) { cum[i - 1] = total; total += w[i]; }
+  if (!(total > 0.0)) { fcm_set_error("the graph has no maximal cliques to draw from"); return FCM_EINVAL; }
+  const double max_rand = 1.0 - 2.220446049250313e-16;
+  double sc = total;
+  for (;;) {
+    volatile double prod = sc * max_rand;
+    if (prod + 0.0 < total) break;
+    u64 b; memcpy(&b, &sc, 8); b -= 1; memcpy(&sc, &b, 8);
+  }
+  *scale = sc;
+  return FCM_OK;
+}
+
+// Graph::compute_maximal_cliques (external crate, called src/lib.rs:41): maximal cliques of the
+// underlying undirected graph.  Enumeration: for every vertex v the cliques whose SMALLEST vertex is
+// v, by pivoted expansion over sorted candidate lists with bit-row adjacency tests (one host thread
+// per stripe of v).  Order handed to the chains: each clique ascending, cliques lexicographic - the
+// documented assumption of oracle/fcm_oracle.cpp (the crate is not on disk: parity unpinned).
+struct CliqueEnum {
+  const std::vector<std::vector<u32>>& und;
+  const std::vector<u64>& bits;          // n x W undirected bit rows
+  u32 W;
+  std::vector<std::vector<u32>> out;
+  bool adj(u32 a, u32 b) const { return (bits[(size_t)a * W + (b >> 6)] >> (b & 63)) & 1ULL; }
+  void expand(std::vector<u32>& R, std::vector<u32>& P, std::vector<u32>& X) {
+    if (P.empty()) { if (X.empty()) { out.push_back(R); std::sort(out.back().begin(), out.back().end()); } return; }
+    u32 pivot = P[0]; size_t best = 0; bool first = true;
+    for (int which = 0; which < 2; which++)
+      for (u32 u : (which ? X : P)) {
+        size_t c = 0;
+        for (u32 w : P) c += adj(u, w);
+        if (first || c > best) { best = c; pivot = u; first = false; }
+      }
+    std::vector<u32> cand;
+    for (u32 w : P) if (!adj(pivot, w)) cand.push_back(w);
+    for (u32 v : cand) {
+      std::vector<u32> P2, X2;
+      for (u32 w : P) if (adj(v, w)) P2.push_back(w);
+      for (u32 w : X) if (adj(v, w)) X2.push_back(w);
+      R.push_back(v);
+      expand(R, P2, X2);
+      R.pop_back();
+      P.erase(std::find(P.begin(), P.end(), v));
+      X.push_back(v);
+    }
+  }
+};
+static std::vector<std::vector<u32>> maximal_cliques(u32 n, const std::vector<std::vector<u32>>& und, int nthreads) {
+  const u32 W = (n + 63) / 64;
+  std::vector<u64> bits((size_t)n * W, 0);
+  for (u32 v = 0; v < n; v++) for (u32 w : und[v]) bits[(size_t)v * W + (w >> 6)] |= 1ULL << (w & 63);
+  std::vector<std::vector<std::vector<u32>>> part(nthreads);
+  std::vector<std::thread> th;
+  for (int t = 0; t < nthreads; t++)
+    th.emplace_back([&, t]() {
+      CliqueEnum ce{und, bits, W, {}};
+      for (u32 v = t; v < n; v += nthreads) {
+        std::vector<u32> R{v}, P, X;
+        for (u32 w : und[v]) (w > v ? P : X).push_back(w);
+        ce.expand(R, P, X);
+      }
+      part[t] = std::move(ce.out);
+    });
+  for (auto& t : th) t.join();
+  std::vector<std::vector<u32>> all;
+  for (auto& pt : part) for (auto& c : pt) all.push_back(std::move(c));
+  std::sort(all.begin(), all.end());
+  return all;
+}
+
 extern "C" int fcm_ensemble_destroy(fcm_ensemble* e) {
   if (!e) return FCM_OK;
   if (e->ctx) { cudaSetDevice(e->ctx->device); cudaStreamSynchronize(e->ctx->stream); }
@@ -91,10 +166,7 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   REQUIRE(nchains >= 1 && seeds, "need at least one chain and its seed");
   REQUIRE(flag_count0 && len0 >= 0 && len0 <= FCM_MAXD, "flag_count0 missing or longer than FCM_MAXD");
   REQUIRE(move_weights, "move_weights is null");
-  if (move_weights[2] != 0.0 || move_weights[3] != 0.0) {
-    fcm_set_error("clique_permute / clique_swap moves are not implemented (weights must be 0)");
-    return FCM_EUNSUPPORTED;
-  }
+  const bool want_cliques = move_weights[2] != 0.0 || move_weights[3] != 0.0;
   FCM_CUDA(cudaSetDevice(ctx->device));
   fcm_ensemble* e = new fcm_ensemble();
   e->ctx = ctx;
@@ -244,10 +316,59 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     }
   }
   u32 kneed = 2 * maxc + 4;                            // double-edge move: two pairs + four endpoints
+  // ---- clique moves: maximal cliques by order, the order distribution, the sorted pair keys ----
+  std::vector<u32> cq_verts;
+  std::vector<u64> pkeys(p.npairs);
+  std::vector<u32> pkey_pair(p.npairs);
+  {
+    std::vector<u32> rk(p.npairs);
+    for (u64 q = 0; q < p.npairs; q++) rk[q] = (u32)q;
+    std::sort(rk.begin(), rk.end(), [&](u32 x, u32 y) { return pkey(pair_ab[x].x, pair_ab[x].y) < pkey(pair_ab[y].x, pair_ab[y].y); });
+    for (u64 r = 0; r < p.npairs; r++) { pkeys[r] = pkey(pair_ab[rk[r]].x, pair_ab[rk[r]].y); pkey_pair[r] = rk[r]; }
+  }
+  if (want_cliques) {
+    std::vector<std::vector<u32>> cl = maximal_cliques(n, und, nthreads);
+    size_t maxo = 0;
+    for (auto& c : cl) maxo = std::max(maxo, c.size());
+    if (maxo > FCM_MAXD) { fcm_set_error("a maximal clique of order %zu (> %d)", maxo, FCM_MAXD); return fail(FCM_EDIM); }
+    std::vector<u64> cnt(maxo, 0);
+    for (auto& c : cl) cnt[c.size() - 1]++;
+    u64 base = 0;
+    for (size_t o = 0; o < maxo; o++) {
+      if (cnt[o] > 0xffffffffULL || base > 0xffffffffULL) { fcm_set_error("too many maximal cliques"); return fail(FCM_ELIMIT); }
+      p.cq_count[o] = (u32)cnt[o]; p.cq_base[o] = (u32)base; base += cnt[o] * (o + 1);
+    }
+    cq_verts.resize(std::max<u64>(base, 1));
+    std::vector<u64> fill(maxo, 0);
+    u32 kunion = 0;
+    std::vector<u32> mark(n, 0);
+    u32 stamp = 0;
+    for (auto& c : cl) {                               // lexicographic order is kept inside every order
+      const size_t o = c.size() - 1;
+      std::copy(c.begin(), c.end(), cq_verts.begin() + p.cq_base[o] + fill[o] * (o + 1));
+      fill[o]++;
+      // |edgeset_neighborhood| of a permutation of this clique: its vertices + the common neighbours of its pairs
+      stamp++;
+      u32 usz = 0;
+      for (u32 v : c) if (mark[v] != stamp) { mark[v] = stamp; usz++; }
+      for (size_t i = 0; i < c.size(); i++)
+        for (size_t j = i + 1; j < c.size(); j++) {
+          const u32 q = e->pairmap[pkey(c[j], c[i])];
+          for (u64 t = nb_off[q]; t < nb_off[q + 1]; t++) if (mark[nb_list[t]] != stamp) { mark[nb_list[t]] = stamp; usz++; }
+        }
+      kunion = std::max(kunion, usz);
+    }
+    std::vector<double> w(maxo);
+    for (size_t o = 0; o < maxo; o++) w[o] = std::pow((double)cnt[o], 0.2);   // src/bin/sample.rs:87
+    if ((rc = weighted_index_init_n(w, p.cq_cum, &p.cq_scale))) return fail(rc);
+    p.cq_norders = (int)maxo;
+    e->cliques = 1;
+    kneed = std::max<u32>(kneed, std::min<u32>(n, 2 * kunion));   // clique_swap: two cliques
+  }
   p.Kcap = std::min<u32>(std::max<u32>(kneed, 8), 512);
   u32 kw = (p.Kcap + 63) / 64;
   p.KWcap = kw <= 1 ? 1 : kw <= 2 ? 2 : kw <= 4 ? 4 : 8;
-  e->smem_per_warp = fcm_chain_smem_per_warp(p.Kcap, p.KWcap);
+  e->smem_per_warp = fcm_chain_smem_per_warp(p.Kcap, p.KWcap, e->cliques != 0);
   e->warps_per_block = 4;
   while (e->warps_per_block > 1 && e->smem_per_warp * e->warps_per_block > ctx->smem_optin) e->warps_per_block >>= 1;
   if (e->smem_per_warp > ctx->smem_optin) { fcm_set_error("neighbourhood tile does not fit shared memory"); return fail(FCM_ELIMIT); }
@@ -293,6 +414,19 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     if (ce != cudaSuccess) { fcm_set_error("upload of the clique index failed: %s", cudaGetErrorString(ce)); return fail(FCM_ECUDA); }
     p.pinfo = d_pinfo; p.tri = d_tri; p.k4 = d_k4;
     e->index_bytes = pinfo.size() * sizeof(uint4) + tri.size() * sizeof(uint2) + k4.size() * 4;
+  }
+  {
+    u64* d_keys; u32* d_kp; u32* d_cq;
+    if ((rc = dev_alloc(e, &d_keys, pkeys.size()))) return fail(rc);
+    if ((rc = dev_alloc(e, &d_kp, pkey_pair.size()))) return fail(rc);
+    if ((rc = dev_alloc(e, &d_cq, cq_verts.size()))) return fail(rc);
+    cudaError_t ce = cudaSuccess;
+    if (!pkeys.empty()) ce = cudaMemcpyAsync(d_keys, pkeys.data(), pkeys.size() * 8, cudaMemcpyHostToDevice, ctx->stream);
+    if (ce == cudaSuccess && !pkey_pair.empty()) ce = cudaMemcpyAsync(d_kp, pkey_pair.data(), pkey_pair.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (ce == cudaSuccess && !cq_verts.empty()) ce = cudaMemcpyAsync(d_cq, cq_verts.data(), cq_verts.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(ctx->stream);
+    if (ce != cudaSuccess) { fcm_set_error("upload of the clique tables failed: %s", cudaGetErrorString(ce)); return fail(FCM_ECUDA); }
+    p.pkeys = d_keys; p.pkey_pair = d_kp; p.cq_verts = d_cq;
   }
   if ((rc = dev_alloc(e, &p.st, (size_t)nchains))) return fail(rc);
   if ((rc = dev_alloc(e, &e->edit_dev, (size_t)FCM_MAXEDIT * 2))) return fail(rc);

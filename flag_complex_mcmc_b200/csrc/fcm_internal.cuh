@@ -60,7 +60,8 @@ int fcm_graph_build_device(fcm_graph* g, const uint2* edges_dev, u64 ne_in, int 
 
 // ---- ensemble of chains ----------------------------------------------------------------------------
 #define FCM_MAXB (FCM_MAXD + 1)     // bounds vectors may be one longer (src/lib.rs:152 push(10))
-#define FCM_MAXEDIT 64
+#define FCM_MAXEDIT 128                 // change_edges of one transition (clique_swap of two 8-cliques: 112)
+#define FCM_MAXCQ 32                    // vertices of d = c ++ a ++ b in clique_swap (src/lib.rs:240): cliques of order <= 16
 
 struct ChainState {                 // one per chain, in HBM
   u64 rng[4];
@@ -102,6 +103,14 @@ struct EnsParams {
   u64 bmin[FCM_MAXB], bmax[FCM_MAXB];
   int nmin, nmax;
   double cum[3], scale;             // WeightedIndex<f64>
+  // clique moves (src/lib.rs:214-290); cq_norders = 0 when the ensemble was created without them
+  int cq_norders;                   // cliques_by_order.len()
+  double cq_cum[FCM_MAXD], cq_scale; // clique_order_distribution (src/bin/sample.rs:87-88)
+  u32 cq_count[FCM_MAXD + 1];       // maximal cliques of order o + 1
+  u32 cq_base[FCM_MAXD + 1];        // first vertex of the first clique of order o + 1 in cq_verts
+  const u32* cq_verts;              // cliques of one order back to back, vertices ascending
+  const u64* pkeys;                 // (big << 32 | small) of every adjacent pair, ascending
+  const u32* pkey_pair;             // ... and its pair id
 };
 
 struct fcm_ensemble {
@@ -117,6 +126,7 @@ struct fcm_ensemble {
   int force_full = 0;                     // 1: every proposal through the full pre/post count path
   int force_rows = 0;                     // 1: hot path gathers from the adjacency rows even when the clique index exists
   int have_index = 0;                     // the static clique index was built
+  int cliques = 0;                        // clique moves enabled (bigger per-warp shared memory)
   int stats = 1;                          // 1: the kernels keep the neighbourhood-size statistic (sumK / nonempty)
   u64 index_bytes = 0;
   fcm_trace_rec* trace_dev = nullptr;
@@ -131,7 +141,7 @@ struct fcm_ensemble {
 };
 
 // fcm_chain.cu
-size_t fcm_chain_smem_per_warp(u32 Kcap, u32 KWcap);
+size_t fcm_chain_smem_per_warp(u32 Kcap, u32 KWcap, bool cliques);
 int fcm_chain_launch_step(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain);
 int fcm_chain_launch_apply(fcm_ensemble* e, u32 chain, int nedits, int revert);
 int fcm_chain_launch_replicate(fcm_ensemble* e);

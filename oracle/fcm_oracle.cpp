@@ -96,6 +96,30 @@ static inline u64 gen_range_u64(Xoshiro256SS& rng, u64 range) {
   }
 }
 
+// rand 0.8 UniformInt<u32>::sample_single(0, range): next_u32 = upper half of next_u64
+// (rand_xoshiro 0.6 Xoshiro256StarStar::next_u32), 32x32 widening multiply, rejection zone.
+static inline u32 gen_range_u32(Xoshiro256SS& rng, u32 range) {
+  u32 zone = (range << __builtin_clz(range)) - 1;
+  for (;;) {
+    u32 v = (u32)(rng.next_u64() >> 32);
+    u64 m = (u64)v * range;
+    if ((u32)m <= zone) return (u32)(m >> 32);
+  }
+}
+// rand 0.8 seq::gen_index: the u32 sampler when the bound fits u32 (SliceRandom::choose / shuffle)
+static inline size_t gen_index(Xoshiro256SS& rng, size_t ubound) {
+  if (ubound <= 0xffffffffULL) return gen_range_u32(rng, (u32)ubound);
+  return gen_range_u64(rng, ubound);
+}
+// util::random_perm (src/util.rs:28-32): (l..h) then SliceRandom::shuffle =
+// for i in (1..len).rev() { swap(i, gen_index(rng, i + 1)) }
+static inline std::vector<size_t> random_perm(size_t l, size_t h, Xoshiro256SS& rng) {
+  std::vector<size_t> perm;
+  for (size_t x = l; x < h; x++) perm.push_back(x);
+  for (size_t i = perm.size(); i-- > 1;) std::swap(perm[i], perm[gen_index(rng, i + 1)]);
+  return perm;
+}
+
 // rand 0.8 Bernoulli: p_int = (p * 2^64) as u64 ; sample = next_u64 < p_int  (p < 1)
 static inline bool gen_bool(Xoshiro256SS& rng, double p) {
   if (p >= 1.0) return true;                      // ALWAYS_TRUE consumes no draw
@@ -344,10 +368,47 @@ static bool calc_relax_de(const std::vector<u64>& sc, std::vector<u64>& relax_de
 // ---------------------------------------------------------------------------------------------
 // State / Transition / Bounds / MCMCSampler  (src/lib.rs)
 // ---------------------------------------------------------------------------------------------
+// Graph::compute_maximal_cliques of the external flag-complex crate (called src/lib.rs:41): maximal
+// cliques of the underlying undirected graph.  ASSUMED output order (the crate is not on disk, parity
+// unpinned): every clique's vertices ascending, the cliques in lexicographic order.  Bron-Kerbosch
+// with a pivot; the order is imposed by the final sort, not by the enumeration.
+static void bron_kerbosch(const std::vector<std::vector<Node>>& adj, std::vector<Node>& R, std::vector<Node> P,
+                          std::vector<Node> X, std::vector<std::vector<Node>>& out) {
+  if (P.empty()) { if (X.empty()) { std::vector<Node> c = R; std::sort(c.begin(), c.end()); out.push_back(c); } return; }
+  Node pivot = P[0]; size_t best = 0; bool first = true;
+  auto common = [&](const std::vector<Node>& S, Node u) { size_t c = 0; for (Node v : S) c += std::binary_search(adj[u].begin(), adj[u].end(), v); return c; };
+  for (const std::vector<Node>* S : {&P, &X})
+    for (Node u : *S) { size_t c = common(P, u); if (first || c > best) { best = c; pivot = u; first = false; } }
+  std::vector<Node> cand;
+  for (Node v : P) if (!std::binary_search(adj[pivot].begin(), adj[pivot].end(), v)) cand.push_back(v);
+  for (Node v : cand) {
+    std::vector<Node> P2, X2;
+    for (Node w : P) if (std::binary_search(adj[v].begin(), adj[v].end(), w)) P2.push_back(w);
+    for (Node w : X) if (std::binary_search(adj[v].begin(), adj[v].end(), w)) X2.push_back(w);
+    R.push_back(v);
+    bron_kerbosch(adj, R, P2, X2, out);
+    R.pop_back();
+    P.erase(std::find(P.begin(), P.end(), v));
+    X.push_back(v);
+  }
+}
+static std::vector<std::vector<Node>> compute_maximal_cliques(const Graph& g) {
+  std::vector<std::vector<Node>> adj(g.nnodes());
+  for (const Edge& e : g.edges.items) { adj[e.a].push_back(e.b); adj[e.b].push_back(e.a); }
+  for (auto& v : adj) { std::sort(v.begin(), v.end()); v.erase(std::unique(v.begin(), v.end()), v.end()); }
+  std::vector<Node> R, P, X;
+  for (Node v = 0; v < g.nnodes(); v++) P.push_back(v);
+  std::vector<std::vector<Node>> out;
+  bron_kerbosch(adj, R, P, X, out);
+  std::sort(out.begin(), out.end());
+  return out;
+}
+
 struct Change { Edge e; bool add; };
 struct Transition { std::vector<Change> change_edges; };
 
 struct State {
+  std::vector<std::vector<std::vector<Node>>> cliques_by_order;   // [order-1] -> cliques (src/lib.rs:41-49)
   std::unordered_map<u64, std::vector<Node>> edge_neighborhood;   // key [big,small]
   Graph graph;
   std::vector<u64> flag_count;
@@ -362,8 +423,13 @@ struct State {
     for (const Edge& e : und) m.emplace(ekey(e.a, e.b), intersect_sorted(adj[e.a], adj[e.b]));
     return m;
   }
-  static State create(Graph g, int nthreads) {                    // State::new, src/lib.rs:38-58
-    State s;                                                      // (maximal cliques: clique moves only)
+  static State create(Graph g, int nthreads, bool with_cliques = false) {                    // State::new, src/lib.rs:38-58
+    State s;
+    if (with_cliques)                                             // src/lib.rs:41-49
+      for (auto& c : compute_maximal_cliques(g)) {
+        if (c.size() > s.cliques_by_order.size()) s.cliques_by_order.resize(c.size());
+        s.cliques_by_order[c.size() - 1].push_back(c);
+      }
     s.flag_count = flagser_count(g, nthreads);
     s.edge_neighborhood = compute_edge_neighborhoods(g);
     s.graph = std::move(g);
@@ -456,7 +522,7 @@ struct Sampler {
   Xoshiro256SS rng;
   State state;
   Bounds bounds;
-  WeightedIndexF64 move_distribution;
+  WeightedIndexF64 move_distribution, clique_order_distribution;
   u64 sample_distance = 0, sampled = 0, accepted = 0;
   u64 draws = 0;
 
@@ -485,6 +551,83 @@ struct Sampler {
     }
     return Transition{};
   }
+  // util::vec_intersect / vec_setminus (src/util.rs:34-50): order of the first argument is kept
+  static std::vector<Node> vec_intersect(const std::vector<Node>& xs, const std::vector<Node>& ys) {
+    std::vector<Node> r;
+    for (Node x : xs) if (std::find(ys.begin(), ys.end(), x) != ys.end()) r.push_back(x);
+    return r;
+  }
+  static std::vector<Node> vec_setminus(const std::vector<Node>& xs, const std::vector<Node>& ys) {
+    std::vector<Node> r;
+    for (Node x : xs) if (std::find(ys.begin(), ys.end(), x) == ys.end()) r.push_back(x);
+    return r;
+  }
+  // Transition::clique_permute  src/lib.rs:214-233
+  Transition clique_permute(TraceRec* tr) {
+    const size_t ord = clique_order_distribution.sample(rng);
+    const auto& cliques = state.cliques_by_order[ord];
+    if (cliques.empty()) { fprintf(stderr, "oracle: choose() on an empty clique list (reference unwrap panics)\n"); abort(); }
+    const size_t ci = gen_index(rng, cliques.size());             // SliceRandom::choose
+    const std::vector<Node>& cl = cliques[ci];
+    std::vector<size_t> perm = random_perm(0, cl.size(), rng);
+    Transition t;
+    for (size_t i = 0; i < cl.size(); i++)
+      for (size_t j = 0; j < cl.size(); j++) {
+        bool pre = state.graph.has_edge(cl[perm[i]], cl[perm[j]]);
+        bool post = state.graph.has_edge(cl[i], cl[j]);
+        if (pre != post) t.change_edges.push_back({{cl[perm[i]], cl[perm[j]]}, post});
+      }
+    if (tr) { tr->a = (u32)ci; tr->b = 0; tr->dm0 = (u32)ord; tr->dm1 = (u32)t.change_edges.size(); }
+    return t;
+  }
+  // Transition::clique_swap  src/lib.rs:235-290
+  Transition clique_swap(TraceRec* tr) {
+    const size_t ord = clique_order_distribution.sample(rng);
+    const auto& cliques = state.cliques_by_order[ord];
+    if (cliques.empty()) { fprintf(stderr, "oracle: choose() on an empty clique list (reference unwrap panics)\n"); abort(); }
+    const size_t i1 = gen_index(rng, cliques.size());
+    const size_t i2 = gen_index(rng, cliques.size());
+    const std::vector<Node>&m1 = cliques[i1], &m2 = cliques[i2];
+    std::vector<Node> c = vec_intersect(m1, m2);
+    std::vector<Node> d = c;
+    for (Node x : vec_setminus(m1, c)) d.push_back(x);
+    for (Node x : vec_setminus(m2, c)) d.push_back(x);
+    const size_t n_c = c.size(), n_d = d.size(), n_a = m1.size() - n_c;
+    std::vector<size_t> perm_c = random_perm(0, n_c, rng);
+    std::vector<size_t> perm_a = random_perm(n_c, n_c + n_a, rng);
+    std::vector<size_t> perm_b = random_perm(n_c + n_a, n_d, rng);
+    std::vector<size_t> perm_d = perm_c;
+    perm_d.insert(perm_d.end(), perm_b.begin(), perm_b.end());
+    perm_d.insert(perm_d.end(), perm_a.begin(), perm_a.end());
+    std::vector<std::pair<Node, Node>> new_edges, old_edges;
+    auto visit = [&](const std::vector<size_t>& idx) {
+      for (size_t i : idx)
+        for (size_t j : idx)
+          if (state.graph.has_edge(d[i], d[j])) {
+            new_edges.push_back({d[perm_d[i]], d[perm_d[j]]});
+            old_edges.push_back({d[i], d[j]});
+          }
+    };
+    std::vector<size_t> first, second;
+    for (size_t i = 0; i < n_c + n_a; i++) first.push_back(i);
+    for (size_t i = 0; i < n_c; i++) second.push_back(i);
+    for (size_t i = n_c + n_a; i < n_d; i++) second.push_back(i);
+    visit(first);
+    visit(second);
+    std::sort(new_edges.begin(), new_edges.end());
+    new_edges.erase(std::unique(new_edges.begin(), new_edges.end()), new_edges.end());
+    std::sort(old_edges.begin(), old_edges.end());
+    old_edges.erase(std::unique(old_edges.begin(), old_edges.end()), old_edges.end());
+    Transition t;
+    for (const auto& ne : new_edges) {
+      auto it = std::find(old_edges.begin(), old_edges.end(), ne);
+      if (it != old_edges.end()) old_edges.erase(it);             // retain(|e| e != ne): the list is deduplicated
+      else t.change_edges.push_back({{ne.first, ne.second}, true});
+    }
+    for (const auto& oe : old_edges) t.change_edges.push_back({{oe.first, oe.second}, false});
+    if (tr) { tr->a = (u32)i1; tr->b = (u32)i2; tr->dm0 = (u32)ord; tr->dm1 = (u32)t.change_edges.size(); }
+    return t;
+  }
   // one iteration of MCMCSampler::next  src/lib.rs:182-192
   int step(TraceRec* tr) {
     if (tr) memset(tr, 0, sizeof(*tr));
@@ -492,7 +635,9 @@ struct Sampler {
     Transition t;
     if (kind == 0) t = single_edge_flip(tr);
     else if (kind == 1) t = double_edge_move(tr);
-    else return -1;                                               // clique moves: SURVEY §8f next row
+    else if (state.cliques_by_order.empty()) return -1;           // built without cliques
+    else if (kind == 2) t = clique_permute(tr);
+    else t = clique_swap(tr);
     std::vector<u64> pre, post;
     u32 K = 0;
     state.apply_transition(t, pre, post, &K);
@@ -656,7 +801,13 @@ void* orc_sampler_new(u32 n, u64 ne, const u32* edges, u64 seed, double target_r
                       const double* move_weights, u64 sample_distance, int nthreads, int* err) {
   *err = 0;
   Sampler* s = new Sampler();
-  s->state = State::create(graph_from(n, ne, edges), nthreads);
+  const bool with_cliques = move_weights[2] != 0.0 || move_weights[3] != 0.0;
+  s->state = State::create(graph_from(n, ne, edges), nthreads, with_cliques);
+  if (with_cliques) {                                             // src/bin/sample.rs:87-88
+    std::vector<double> w;
+    for (const auto& cs : s->state.cliques_by_order) w.push_back(std::pow((double)cs.size(), 0.2));
+    if (!s->clique_order_distribution.init(w.data(), w.size())) { *err = -11; delete s; return nullptr; }
+  }
   s->rng = Xoshiro256SS::seed_from_u64(seed);
   Bounds target;
   for (size_t d = 0; d < s->state.flag_count.size(); d++) {
@@ -730,6 +881,18 @@ int orc_revert(void* h, const u32* edits3, int nedits, const u64* pre, int prele
   return 0;
 }
 int orc_bounds_check(void* h) { Sampler* s = (Sampler*)h; return s->bounds.check(s->state); }
+// maximal cliques in the assumed order: sizes_out[ncliques], verts_out[sum sizes] (either may be null) -> ncliques
+u64 orc_maximal_cliques(u32 n, u64 ne, const u32* edges, u32* sizes_out, u32* verts_out, u64* total_verts) {
+  auto cl = compute_maximal_cliques(graph_from(n, ne, edges));
+  u64 tot = 0;
+  for (size_t i = 0; i < cl.size(); i++) {
+    if (sizes_out) sizes_out[i] = (u32)cl[i].size();
+    for (Node v : cl[i]) { if (verts_out) verts_out[tot] = v; tot++; }
+  }
+  if (total_verts) *total_verts = tot;
+  return cl.size();
+}
+
 // undirected clique counts of the normalised graph (Bounds::calculate's `ncliques`)
 int orc_ncliques(u32 n, u64 ne, const u32* edges, int nthreads, u64* out, int* len) {
   Graph g = graph_from(n, ne, edges);

@@ -178,11 +178,51 @@ def test_rejections_happen_and_revert_restores(kernel, ctx, graphs):
     s.close()
 
 
-def test_clique_moves_are_refused_loudly(ctx, graphs):
-    n, e = graphs["counterexample_any_order"]
-    with pytest.raises(fcm.FcmError) as ei:
-        fcm.initialize_new_sampler(ctx, n, e, [0], simple=False)
-    assert ei.value.code == fcm._native.FCM_EUNSUPPORTED
+@pytest.mark.parametrize("kernel", [0, 2])
+@pytest.mark.parametrize("name,seed,steps,weights", [
+    ("counterexample_any_order", 5, 4000, ds.MOVE_DISTRIBUTION),
+    ("counterexample_seo_greedy_5_start", 1, 3000, ds.MOVE_DISTRIBUTION),
+    ("c2_chunglu_279", 0, 3000, ds.MOVE_DISTRIBUTION),
+    ("c2_chunglu_279", 7, 1500, (0.0, 0.0, 1.0, 0.0)),
+    ("c2_chunglu_279", 8, 1500, (0.0, 0.0, 0.0, 1.0)),
+    ("bug_calc_relax_de", 2, 3000, (0.25, 0.25, 0.25, 0.25))])
+def test_clique_moves_trace_parity(name, seed, steps, weights, kernel, ctx, graphs):
+    # Transition::clique_permute / clique_swap (src/lib.rs:214-290) mixed with the simple moves: trace
+    # (move kind, chosen cliques, order, number of edits, |nbhd|, accept), counts, containers, RNG
+    n, e = graphs[name]
+    s = fcm.initialize_new_sampler(ctx, n, e, [seed], target_relaxation=0.01, simple=False)
+    s.close()
+    fc0 = fcm.flagser_count(n, e, ctx)
+    o = orc.Sampler(n, e, seed, 0.01, move_weights=weights)
+    w = o.read()
+    b = ds.Bounds(w["bounds_min"], w["bounds_max"])
+    s = fcm.MCMCSampler(ctx, n, e, [seed], b, fc0, weights, w["sample_distance"])
+    s.set_kernel(kernel)
+    for chunk in (1, 5, steps):
+        got, want = s.step_trace(chunk, 0), o.steps(chunk)
+        for f in FIELDS:
+            if not np.array_equal(got[f], want[f]):
+                i = int(np.nonzero(got[f] != want[f])[0][0])
+                raise AssertionError("trace field %s differs first at proposal %d: got %s want %s" % (f, i, got[i], want[i]))
+    compare_chain(s, 0, o)
+    kinds = np.bincount(want["flags"] & 3, minlength=4)
+    assert kinds[2] + kinds[3] > 0
+    r = s.read(0)
+    assert ds.trim(r["flag_count"]) == fcm.flagser_count(n, r["edges"], ctx)
+    s.close()
+
+
+def test_clique_moves_many_chains_untraced(ctx, graphs):
+    n, e = graphs["c2_chunglu_279"]
+    seeds = list(range(40, 52))
+    s = fcm.initialize_new_sampler(ctx, n, e, seeds, target_relaxation=0.01, simple=False)
+    s.step(1200)
+    s.status()
+    for k in (0, 5, 11):
+        o = orc.Sampler(n, e, seeds[k], 0.01, move_weights=ds.MOVE_DISTRIBUTION)
+        o.steps(1200, trace=False)
+        compare_chain(s, k, o)
+    s.close()
 
 
 def test_c3_full_size_chains(ctx, graphs, expected):
