@@ -38,7 +38,7 @@ enum {
   FCM_ENOTADJ = -6,            /* an edit names a pair that is not adjacent in the underlying
                                   undirected graph (reference: HashMap index panic, src/lib.rs:104) */
   FCM_EASSERT = -7,            /* reference assert!(s >= p) would fail (src/lib.rs:65,86) */
-  FCM_EUNSUPPORTED = -8,       /* e.g. clique moves (move_weights[2..3] != 0): SURVEY §8f next row */
+  FCM_EUNSUPPORTED = -8,       /* a clique move was drawn on an ensemble created without clique moves */
   FCM_ELIMIT = -9              /* neighbourhood larger than the kernel's local-matrix capacity */
 };
 
@@ -111,7 +111,12 @@ int fcm_graph_info(const fcm_graph* g, uint32_t* n, uint64_t* nedges, uint32_t* 
  *    Xoshiro256StarStar::seed_from_u64(seeds[k]) (src/bin/sample.rs:86).
  *    flag_count0/len0 = the initial flagser_count of the graph (State::new, src/lib.rs:51).
  *    move_weights[4] = MOVE_DISTRIBUTION (src/bin/sample.rs:16-17): flip, double-edge move,
- *    clique permute, clique swap; the last two must be 0 (FCM_EUNSUPPORTED otherwise).
+ *    clique permute, clique swap (src/lib.rs:214-290).  When one of the last two is non-zero the
+ *    maximal cliques of the underlying undirected graph are enumerated at creation (State::new,
+ *    src/lib.rs:41-49; order handed to `choose`: every clique ascending, cliques lexicographic) and
+ *    clique_order_distribution = WeightedIndex(len^0.2) (src/bin/sample.rs:87-88) is built.
+ *    Trace records of clique moves: a, b = index of the chosen clique(s) within their order,
+ *    dm0 = order index, dm1 = number of change_edges, K = |edgeset_neighborhood|.
  * ---------------------------------------------------------------------------------------------- */
 int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, const uint32_t (*edges)[2],
                         uint32_t nchains, const uint64_t* seeds,
