@@ -870,7 +870,7 @@ __device__ void sort_dedup_u64(u64* a, int& n) {       // lane 0, short lists: i
 // kind 2 = clique_permute, 3 = clique_swap.  The chain's RNG state (after the move-kind draw) and all
 // other state are in HBM (the hot stretch has been closed).  Returns 0 or an FCM_E* code.
 __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned char* wb, int lane, int kind,
-                                        fcm_trace_rec* tr_out, bool red, bool instr) {
+                                        fcm_trace_rec* tr_out, int force_full, bool red, bool instr) {
   const WarpSmem s = carve(wb, p.Kcap, p.KWcap);
   int* const sflag = (int*)(wb + SM_FLAG);
   ChainState* const st = &p.st[chain];
@@ -1005,7 +1005,70 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
   const u64 fc = st->flag_count[lane];
   int len = st->fc_len, K = 0, prelen = 0, postlen = 0, rc = 0;
   u64 fnew = fc;
-  if (nedit) {
+  // DELTA form: post - pre = sum over the edits, applied one after the other, of +-(simplices through
+  // the edited edge in the graph as it stands then) - every term is the single-edge count of the flip
+  // path, on the static common-neighbour list of that pair.  Lists beyond FAST_C (or kernel kind 1)
+  // take the reference's two counts of the whole union neighbourhood instead; same flag_count.
+  bool fast = !force_full;
+  for (int t = 0; t < nedit && fast; t++) {
+    const u32 pair = s.edits[2 * t] >> 1;
+    fast = __ldg(&p.nb_off[pair + 1]) - __ldg(&p.nb_off[pair]) <= FAST_C;
+  }
+  bool bits_applied = false;
+  if (nedit && fast) {
+    if (instr && !build_nbhd(p, s.edits, nedit, s.verts, K, lane)) rc = FCM_ELIMIT;
+    if (lane < 8) s.dflag[lane] = 0;
+    s.deep[lane] = 0;
+    __syncwarp();
+    int cnt[DELTA_SD];
+#pragma unroll
+    for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
+    int tri = 0, edges = 0;
+#pragma unroll 1
+    for (int t = 0; t < nedit && !rc; t++) {
+      const u32 slot = s.edits[2 * t];
+      const bool add = s.edits[2 * t + 1] != 0;
+      const int sign = add ? 1 : -1;
+      const uint2 ft = slot_edge(p, slot);               // the edge u -> v
+      const u32 o = __ldg(&p.nb_off[slot >> 1]);
+      const int cc = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - o);
+      Gathered ga;
+      gather_pair(p, cb, o, cc, ft.x, ft.y, s.cv, s.rowoff, s.A, lane, ga);
+      const u64 X = ga.inU & ga.inV, Y = ga.outU & ga.inV, Z = ga.outU & ga.outV;
+      edges += sign;
+      tri += sign * (__popcll(X) + __popcll(Y) + __popcll(Z));
+      count_through_edge<u64>(X, Y, Z, cc, s.A, lane, sign, cnt, s.deep, s.dflag);
+      __syncwarp();
+      if (lane == 0) {                                  // the next edit sees this one
+        u32* const w = &cb[ft.x * W32 + (ft.y >> 5)];
+        const u32 m = 1u << (ft.y & 31);
+        if (red) { if (add) atomicOr(w, m); else atomicAnd(w, ~m); }
+        else { const u32 wv = __ldcg(w); *w = add ? (wv | m) : (wv & ~m); }
+        __threadfence_block();
+      }
+      __syncwarp();
+    }
+    bits_applied = true;
+    if (!rc && s.dflag[FL_ERR]) rc = s.dflag[FL_ERR];
+    if (!rc) {
+#pragma unroll
+      for (int k = 0; k < DELTA_SD; k++) {
+        const int tot = __reduce_add_sync(FULL, cnt[k]);
+        if (lane == 0) s.deep[k + 3] += (u64)(long long)tot;
+      }
+      if (lane == 0) { s.deep[2] += (u64)(long long)tri; s.deep[1] += (u64)(long long)edges; }
+      __syncwarp();
+      fnew = fc + s.deep[lane];
+      if (__any_sync(FULL, (long long)fnew < 0)) rc = FCM_EASSERT;
+      // post.len() exceeds the old length iff a simplex of a new dimension exists afterwards (src/lib.rs:72-74)
+      const u32 nz = __ballot_sync(FULL, fnew != 0);
+      len = max(len, nz ? 32 - __clz((int)nz) : 0);
+    }
+    __syncwarp();
+    s.deep[lane] = 0;
+    if (lane < 8) s.dflag[lane] = 0;
+    __syncwarp();
+  } else if (nedit) {
     rc = transition_counts(p, c, s, nedit, lane, K, prelen, postlen);
     if (!rc) {
       const u64 pr = lane < min(prelen, len) ? s.pre[lane] : 0;
@@ -1024,19 +1087,23 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
       const bool add = (s.edits[2 * t + 1] != 0) != (pass == 1);
       if (add) c_add_edge(c, slot, lane); else c_remove_edge(c, slot, lane);
     }
-  if (ok && lane == 0)
-    for (int t = 0; t < nedit; t++) {                   // adjacency rows + orientation bits
+  if (lane == 0 && (ok != bits_applied || ok))
+    for (int t = 0; t < nedit; t++) {                   // adjacency rows (set, or taken back after a rejected delta pass) + orientation bits
       const u32 slot = s.edits[2 * t];
-      const bool add = s.edits[2 * t + 1] != 0;
-      const uint2 ft = slot_edge(p, slot);
-      u32* const w = &cb[ft.x * W32 + (ft.y >> 5)];
-      const u32 m = 1u << (ft.y & 31);
-      if (red) { if (add) atomicOr(w, m); else atomicAnd(w, ~m); }
-      else *w = add ? (*w | m) : (*w & ~m);
-      u32* const o = &c.ori[slot >> 5];
-      const u32 om = 1u << (slot & 31);
-      const u32 ov = __ldcg(o);
-      *o = add ? (ov | om) : (ov & ~om);
+      const bool add = (s.edits[2 * t + 1] != 0) == ok;
+      if (ok != bits_applied) {
+        const uint2 ft = slot_edge(p, slot);
+        u32* const w = &cb[ft.x * W32 + (ft.y >> 5)];
+        const u32 m = 1u << (ft.y & 31);
+        if (red) { if (add) atomicOr(w, m); else atomicAnd(w, ~m); }
+        else { const u32 wv = __ldcg(w); *w = add ? (wv | m) : (wv & ~m); }
+      }
+      if (ok) {
+        u32* const o = &c.ori[slot >> 5];
+        const u32 om = 1u << (slot & 31);
+        const u32 ov = __ldcg(o);
+        *o = add ? (ov | om) : (ov & ~om);
+      }
     }
   __syncwarp();
   if (ok) st->flag_count[lane] = fnew;
@@ -1066,7 +1133,7 @@ __device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned ch
   u64* const sdeep = (u64*)(wb + SM_DEEP);
   int* const sflag = (int*)(wb + SM_FLAG);
   const int kind = (int)park[PK_KIND];
-  if (kind >= 2) return clique_step(p, chain, wb, lane, kind, tr_out, red, instr);
+  if (kind >= 2) return clique_step(p, chain, wb, lane, kind, tr_out, force_full, red, instr);
   const u32 slot = park[PK_SLOT], delme = park[PK_DELME], idx = park[PK_IDX], didx = park[PK_DIDX], dpair = park[PK_DPAIR];
   const u32 last = park[PK_LAST], qpos = park[PK_QPOS], ta = park[PK_TA], tb = park[PK_TB], tdm0 = park[PK_TDM0], tdm1 = park[PK_TDM1];
   const int cA = (int)park[PK_CA], cD = (int)park[PK_CD];
