@@ -31,6 +31,8 @@ sys.path.insert(0, ROOT)
 
 METRIC = "mcmc_proposals_per_sec"
 UNIT = "proposals/s"
+CHAIN_DRAM_BYTES_PER_PROPOSAL = 4326       # measured, see roofline.traffic_source
+RECOUNT_DRAM_BYTES_C4 = 10.42e9 + 0.47e9   # ncu --set full of count_local_kernel<8> on C4, one GPU (profiles/r01_d_count_local_stack.ncu.txt)
 N_C3, W_C3 = 2000, 32                      # vertices, 64-bit words per adjacency row (ceil(n/64))
 
 
@@ -210,6 +212,7 @@ def main():
     ap.add_argument("--proposals", type=int, default=2000, help="proposals per chain per step")
     ap.add_argument("--no-recount", action="store_true", help="skip the C4 recount leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-clique-mix", action="store_true", help="skip the default-move-mix leg")
     ap.add_argument("--recount-graph", default="c4_geo_31346")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
@@ -336,7 +339,10 @@ def main():
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "chain_step_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": CHAIN_DRAM_BYTES_PER_PROPOSAL * float(args.chains) * P,
+                     "traffic_source": "ncu --set full of chain_step_kernel (profiles/r01_b_chain_step_clique_index.ncu.txt): "
+                                       "dram read 8.177 GB + write 0.682 GB for 4096 x 500 proposals = %d B/proposal, scaled to this launch" % CHAIN_DRAM_BYTES_PER_PROPOSAL,
+                     "peak_source": peak_src,
                      "model": "8*W*K + 4*(K-2) + 16 bytes per non-empty proposal (SURVEY 8d), W=%d, mean K=%.2f, "
                               "non-empty fraction %.3f (both measured over the instrumented warm-up steps of the same chains)" % (W_C3, meanK, nonempty_frac),
                      "kernel_ms": kern_ms},
@@ -345,6 +351,31 @@ def main():
         "value_instrumented": value_instr,
         "clique_index": {"built": info["have_index"], "bytes": info["index_bytes"]},
     }
+
+    # ---- default move mix [0.1,0.1,0.6,0.2] (clique_permute / clique_swap included, src/bin/sample.rs:17) ----
+    if not args.no_clique_mix:
+        t0 = time.perf_counter()
+        sc = fcm.initialize_new_sampler(ctx, n, e, seeds, target_relaxation=0.01, simple=False)
+        create_s = time.perf_counter() - t0
+        Pc = max(args.proposals // 10, 1)
+        sc.set_stats(False)
+        for _ in range(max(args.warmup, 1)):
+            sc.step(Pc)
+        barrier()
+        ctx.timer_begin()
+        for _ in range(args.steps):
+            sc.step(Pc)
+        cms = max_over_ranks(ctx.timer_end())
+        barrier()
+        sc.status()
+        rc_ = sc.read_all()
+        line["default_mix"] = {"metric": METRIC, "value": float(args.chains) * Pc * args.steps * ngpu / (cms * 1e-3), "unit": UNIT,
+                               "move_distribution": [0.1, 0.1, 0.6, 0.2], "proposals_per_chain_per_step": Pc,
+                               "ms_per_step": cms / max(args.steps, 1),
+                               "acceptance_ratio": float(rc_["accepted"].sum()) / max(float(rc_["sampled"].sum()), 1.0),
+                               "create_s": create_s,
+                               "what": "same graph and chains with the CLI's default move mix; clique moves run on the cold path"}
+        sc.close()
 
     # ---- full recount (C4), sharded by source vertex + allreduce --------------------------------
     if not args.no_recount:
@@ -386,9 +417,11 @@ def main():
                     "d2h_bytes_per_step": 8 * len(counts), "what": "fcm_count_unweighted(host edge list) on one GPU: upload, build bit rows + CSR, count, download"},
             "roofline": {"bound": "hbm", "kernel": "count_local_kernel", "achieved": rbytes * args.steps / (rms_max * 1e-3) / 1e9 / ngpu,
                          "peak": peak, "unit": "GB/s", "frac": rbytes * args.steps / (rms_max * 1e-3) / 1e9 / ngpu / peak,
-                         "traffic": None, "peak_source": peak_src,
-                         "model": "8*ceil(n/64) bytes per enumerated simplex (dense-row model, SURVEY 8d); the block-local kernel "
-                                  "gathers each source's k x k tile once, so it may exceed 1.0"},
+                         "traffic": RECOUNT_DRAM_BYTES_C4 if (ngpu == 1 and args.recount_graph == "c4_geo_31346") else None,
+                         "peak_source": peak_src,
+                         "model": "8*ceil(n/64) bytes per enumerated simplex (dense-row model, SURVEY 8d). The tile kernel gathers each "
+                                  "source's k x k bits once and intersects in shared memory, so the fraction exceeds 1 by design: "
+                                  "measured DRAM traffic is ~1 % of the model (traffic key); the kernel is issue-bound (DESIGN.md 3.2)"},
         }
         g.close()
 

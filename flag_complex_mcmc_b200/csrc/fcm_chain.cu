@@ -1600,7 +1600,11 @@ int fcm_chain_launch_replicate(fcm_ensemble* e) {
 
 template <bool IDX, bool INSTR>
 static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
-  const EnsParams& p = e->p;
+  EnsParams p = e->p;
+  // ensembles with clique moves size the local matrix M for the union neighbourhood of two cliques; when
+  // every common-neighbour list fits the delta path and the full counts are not forced, M is never
+  // touched: one word per row keeps the per-warp tile small and more chains resident
+  if (e->cliques && !e->force_full && p.maxc <= FAST_C) p.KWcap = 1;
   const size_t per_warp = chain_smem_per_warp_mode(p.Kcap, p.KWcap, !IDX, e->cliques != 0);
   // warps per block: the choice that keeps most warps resident on one SM (big neighbourhood tiles of
   // ensembles with clique moves fit better in smaller blocks)
