@@ -155,7 +155,7 @@ def cpu_recount(n, e, cores, stride):
     return int(c.sum()) / dt, int(c.sum()), dt
 
 
-def run_reference(args):
+def run_reference(args, emit):
     """--impl reference: the reference's CPU algorithm for the path (oracle port; the Rust crate
     cannot be built here: no rustc, un-vendored crates) on all host cores, same config/metric."""
     rank = env_int("RANK", 0)
@@ -185,7 +185,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -216,8 +216,17 @@ def main():
     ap.add_argument("--recount-graph", default="c4_geo_31346")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
+    # stdout carries exactly one JSON line: anything a library prints there (NCCL's version banner ...)
+    # goes to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(obj) + "\n").encode())
     if args.impl == "reference":
-        return run_reference(args)
+        return run_reference(args, emit)
 
     import torch
     import flag_complex_mcmc_b200 as fcm
@@ -442,7 +451,7 @@ def main():
                                                          "in %.2f s incl. bit-matrix build" % (args.recount_graph, rs, rdt)}
     ctx.close()
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

@@ -1,5 +1,6 @@
 // fcm_api.cu — the extern "C" surface of libfcm.so (include/fcm.h) and the host-side setup.
 #include "fcm_internal.cuh"
+#include <vector>
 
 #include <algorithm>
 #include <cmath>
@@ -195,6 +196,61 @@ extern "C" int fcm_graph_count(fcm_graph* g, uint32_t part, uint32_t nparts, uin
   int l = FCM_MAXD;
   while (l > 0 && counts[l - 1] == 0) l--;
   *len = l;
+  return FCM_OK;
+}
+
+// flag_complex::for_each_cell (src/bin/all_cxs.rs:60-64) as a bulk call: every cell of dimension
+// dim_min..dim_max, one row of dim_max + 1 vertex ids (padded with 0xffffffff), rows in the order
+// the recursion meets them when candidates are walked in ascending order (lexicographic, a prefix
+// before its extensions).
+extern "C" int fcm_graph_cells(fcm_graph* g, int dim_min, int dim_max, uint32_t* cells_out, uint64_t cap, uint64_t* ncells) {
+  REQUIRE(g && ncells, "graph/ncells is null");
+  REQUIRE(dim_min >= 0 && dim_max >= dim_min, "need 0 <= dim_min <= dim_max");
+  REQUIRE(cap == 0 || cells_out, "cells_out is null");
+  USE(g->ctx);
+  cudaStream_t s = g->ctx->stream;
+  const size_t stride = (size_t)dim_max + 1;
+  u32* cells_dev = nullptr;
+  unsigned long long* n_dev = nullptr;
+  FCM_CUDA(cudaMalloc(&n_dev, 8));
+  if (cap) { cudaError_t ce = cudaMalloc(&cells_dev, cap * stride * 4); if (ce != cudaSuccess) { cudaFree(n_dev); fcm_set_error("cudaMalloc of the cell buffer failed"); return FCM_ENOMEM; } }
+  int rc = fcm_cells_launch(g, (u32)dim_min, (u32)dim_max, cells_dev, cap, n_dev);
+  unsigned long long total = 0;
+  u32 ctrl[CT_WORDS] = {0};
+  if (!rc) {
+    cudaError_t ce = cudaMemcpyAsync(&total, n_dev, 8, cudaMemcpyDeviceToHost, s);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(ctrl, g->ctrl, sizeof(ctrl), cudaMemcpyDeviceToHost, s);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(s);
+    if (ce != cudaSuccess) { fcm_set_error("for_each_cell: %s", cudaGetErrorString(ce)); rc = FCM_ECUDA; }
+  }
+  if (!rc && total <= cap && total) {
+    cudaError_t ce = cudaMemcpy(cells_out, cells_dev, (size_t)total * stride * 4, cudaMemcpyDeviceToHost);
+    if (ce != cudaSuccess) { fcm_set_error("for_each_cell: %s", cudaGetErrorString(ce)); rc = FCM_ECUDA; }
+    else {
+      // the device meets the cells in no particular order: put them in the recursion's order.
+      // FCM_NONE padding sorts a prefix AFTER its extensions, so compare lengths first on ties.
+      std::vector<size_t> idx((size_t)total);
+      for (size_t i = 0; i < idx.size(); i++) idx[i] = i;
+      auto less = [&](size_t a, size_t b) {
+        const u32 *x = cells_out + a * stride, *y = cells_out + b * stride;
+        for (size_t t = 0; t < stride; t++) {
+          if (x[t] == y[t]) continue;
+          if (x[t] == FCM_NONE) return true;              // x is a proper prefix of y: first
+          if (y[t] == FCM_NONE) return false;
+          return x[t] < y[t];
+        }
+        return false;
+      };
+      std::sort(idx.begin(), idx.end(), less);
+      std::vector<u32> tmp((size_t)total * stride);
+      for (size_t i = 0; i < idx.size(); i++) memcpy(&tmp[i * stride], cells_out + idx[i] * stride, stride * 4);
+      memcpy(cells_out, tmp.data(), tmp.size() * 4);
+    }
+  }
+  cudaFree(n_dev);
+  if (cells_dev) cudaFree(cells_dev);
+  if (rc) return rc;
+  *ncells = total;
   return FCM_OK;
 }
 

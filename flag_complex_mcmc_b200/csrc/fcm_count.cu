@@ -173,12 +173,25 @@ __device__ __noinline__ void deep_count(const u64 (&P0)[WK], int lvl, const u64*
   }
 }
 
-template <int WK>
+// for_each_cell (flag_complex::for_each_cell, src/bin/all_cxs.rs:60-64): where the cells of dimension
+// emit_min..emit_max go.  Row r of `cells` = the vertices (v0..vd) of one cell, padded with FCM_NONE.
+struct EmitArgs { u32 emit_min, emit_max, stride; u32* cells; u64 cap; unsigned long long* ncells; };
+
+__device__ __forceinline__ void emit_cell(const EmitArgs& ea, u32 v0, const u32* verts, u64 e, u32 d) {
+  if (d < ea.emit_min || d > ea.emit_max) return;
+  const u64 row = atomicAdd(ea.ncells, 1ULL);
+  if (row >= ea.cap) return;
+  u32* out = ea.cells + row * ea.stride;
+  out[0] = v0;
+  for (u32 t = 0; t < ea.stride - 1; t++) out[1 + t] = t < d ? verts[(e >> (10 * t)) & 1023u] : FCM_NONE;
+}
+
+template <int WK, bool EMIT>
 __global__ void __launch_bounds__(LocalCfg<WK>::THREADS, LocalCfg<WK>::MINBLOCKS)
 count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
                    const u32* __restrict__ csr, const u32* __restrict__ order, u32 W, u32 nv_total,
                    u32 part, u32 nparts, u32 kcap, u32* __restrict__ ctrl,
-                   u32* __restrict__ overflow, u64* __restrict__ counts) {
+                   u32* __restrict__ overflow, u64* __restrict__ counts, const EmitArgs ea) {
   using Cfg = LocalCfg<WK>;
   constexpr int LS = Cfg::LS, NT = Cfg::THREADS, NW = NT / 32, BPL = Cfg::BPL, MAXIDS = Cfg::MAXIDS;
   constexpr int RL = MAXIDS - 1;                        // cnt[r]: flag_count index 3 + r (tuples of 2 + r ids)
@@ -215,6 +228,12 @@ count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
       continue;
     }
     if (tid == 0) { c0 += 1; c01 += k; }
+    if constexpr (EMIT) {                               // the vertex and its out-edges
+      if (tid == 0) emit_cell(ea, v0, nullptr, 0, 0);
+      if (ea.emit_min <= 1 && ea.emit_max >= 1)
+        for (u32 i = tid; i < k; i += NT) { const u32 v1 = csr[o0 + i]; emit_cell(ea, v0, &v1, 0, 1); }
+      if (ea.emit_max < 2) continue;
+    }
     if (k < 2) continue;                                // no 2-simplex possible
     for (u32 i = tid; i < k; i += NT) verts[i] = csr[o0 + i];
     __syncthreads();
@@ -273,7 +292,7 @@ count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
 #pragma unroll
           for (int d = 1; d < 32; d <<= 1) { const u32 tt = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += tt; }
           const u32 c1 = __shfl_sync(0xffffffffu, incl, 31);
-          if (c1 < 2) continue;                         // a lone triangle has no 3-simplex above it
+          if (!EMIT && c1 < 2) continue;                // a lone triangle has no 3-simplex above it
           u32 o = top + incl - pc;
           while (bits) {
             const u32 j = lane * BPL + (__ffs((int)bits) - 1);
@@ -306,11 +325,15 @@ count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
           for (int y = 0; y < WK; y++) pc += __popcll(P[y]);
 #pragma unroll
           for (int r = 0; r < RL; r++) cnt[r] += (d == (u32)(2 + r)) ? pc : 0u;
+          if constexpr (EMIT) {
+            emit_cell(ea, v0, verts, e, d);
+            if (d >= ea.emit_max) pc = 0;               // nothing deeper is asked for
+          }
         }
         top -= take;
         // children: one entry per member of P.  A lone candidate has no child simplex of its own (the
         // graph has no self loops: P & L[j] = 0 for P = {j}), so it is not pushed.
-        if (pc < 2) pc = 0;
+        if (!EMIT && pc < 2) pc = 0;
         const bool deep = pc && d >= (u32)MAXIDS;
         const u32 want = deep ? 0u : pc;
         u32 incl = want;
@@ -448,13 +471,13 @@ count_dense_kernel(const u64* __restrict__ adj, const u32* __restrict__ tasks, u
 // ---------------------------------------------------------------------------------------------------
 // launcher
 // ---------------------------------------------------------------------------------------------------
-template <int WK>
-static int launch_local(fcm_graph* g, u32 part, u32 nparts, u32 kcap) {
+template <int WK, bool EMIT>
+static int launch_local(fcm_graph* g, u32 part, u32 nparts, u32 kcap, const EmitArgs& ea) {
   fcm_ctx* c = g->ctx;
   constexpr int LS = LocalCfg<WK>::LS;
   constexpr int LOCAL_THREADS = LocalCfg<WK>::THREADS;
   size_t smem = (size_t)kcap * LS * 8 + (size_t)(kcap + (kcap & 1)) * 4 + (size_t)(LOCAL_THREADS / 32) * stack_cap(kcap) * 8;
-  auto kern = count_local_kernel<WK>;
+  auto kern = count_local_kernel<WK, EMIT>;
   FCM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
   FCM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, LOCAL_THREADS, smem));
@@ -462,7 +485,7 @@ static int launch_local(fcm_graph* g, u32 part, u32 nparts, u32 kcap) {
   u32 ntasks = g->n > part ? (g->n - part + nparts - 1) / nparts : 0;
   u32 blocks = (u32)std::min<u64>((u64)c->sm_count * per_sm, std::max<u32>(ntasks, 1));
   kern<<<blocks, LOCAL_THREADS, smem, c->stream>>>(g->adj, g->csr_off, g->csr, g->order, g->W, g->n,
-                                                   part, nparts, kcap, g->ctrl, g->overflow, g->counts);
+                                                   part, nparts, kcap, g->ctrl, g->overflow, g->counts, ea);
   c->launches++;
   FCM_CUDA(cudaGetLastError());
   return FCM_OK;
@@ -500,11 +523,12 @@ int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts) {
   u32 kcap;
   // (rows: the actual largest out-degree rounded up to 32, so that more CTAs fit one SM)
   kcap = std::min<u32>(1024u, std::max<u32>(32u, (kmax + 31u) & ~31u));
-  if (kmax <= 64) rc = launch_local<1>(g, part, nparts, kcap);
-  else if (kmax <= 128) rc = launch_local<2>(g, part, nparts, kcap);
-  else if (kmax <= 256) rc = launch_local<4>(g, part, nparts, kcap);
-  else if (kmax <= 512) rc = launch_local<8>(g, part, nparts, kcap);
-  else rc = launch_local<16>(g, part, nparts, kcap);
+  const EmitArgs none = {0, 0, 0, nullptr, 0, nullptr};
+  if (kmax <= 64) rc = launch_local<1, false>(g, part, nparts, kcap, none);
+  else if (kmax <= 128) rc = launch_local<2, false>(g, part, nparts, kcap, none);
+  else if (kmax <= 256) rc = launch_local<4, false>(g, part, nparts, kcap, none);
+  else if (kmax <= 512) rc = launch_local<8, false>(g, part, nparts, kcap, none);
+  else rc = launch_local<16, false>(g, part, nparts, kcap, none);
   if (rc) return rc;
   if (kmax > kcap) {
     // sources that did not fit the tile were appended to g->overflow; their number is only known
@@ -515,4 +539,24 @@ int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts) {
     if (nover) return launch_dense(g, g->overflow, nover, 0, 1, &g->ctrl[CT_TICKET2], true);
   }
   return FCM_OK;
+}
+
+// for_each_cell: the cells of dimension dim_min..dim_max of the whole graph into cells_dev (rows of
+// dim_max + 1 vertices); *ncells_dev counts every cell found, also those beyond cap.
+int fcm_cells_launch(fcm_graph* g, u32 dim_min, u32 dim_max, u32* cells_dev, u64 cap, unsigned long long* ncells_dev) {
+  fcm_ctx* c = g->ctx;
+  FCM_CUDA(cudaMemsetAsync(g->counts, 0, FCM_MAXD * 8, c->stream));
+  FCM_CUDA(cudaMemsetAsync(g->ctrl, 0, CT_WORDS * 4, c->stream));
+  FCM_CUDA(cudaMemsetAsync(ncells_dev, 0, 8, c->stream));
+  if (g->n == 0) return FCM_OK;
+  const u32 kmax = g->maxout;
+  if (kmax > 1024) { fcm_set_error("for_each_cell: out-degree %u exceeds the 1024-column tile", kmax); return FCM_ELIMIT; }
+  if (dim_max > (u32)LocalCfg<1>::MAXIDS) { fcm_set_error("for_each_cell: dim_max > %d", LocalCfg<1>::MAXIDS); return FCM_ELIMIT; }
+  const u32 kcap = std::min<u32>(1024u, std::max<u32>(32u, (kmax + 31u) & ~31u));
+  const EmitArgs ea = {dim_min, dim_max, dim_max + 1, cells_dev, cap, ncells_dev};
+  if (kmax <= 64) return launch_local<1, true>(g, 0, 1, kcap, ea);
+  if (kmax <= 128) return launch_local<2, true>(g, 0, 1, kcap, ea);
+  if (kmax <= 256) return launch_local<4, true>(g, 0, 1, kcap, ea);
+  if (kmax <= 512) return launch_local<8, true>(g, 0, 1, kcap, ea);
+  return launch_local<16, true>(g, 0, 1, kcap, ea);
 }

@@ -55,6 +55,7 @@ enum { CT_TICKET = 0, CT_NOVER = 1, CT_ERR = 2, CT_TICKET2 = 3, CT_WORDS = 8 };
 
 // fcm_count.cu
 int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts);
+int fcm_cells_launch(fcm_graph* g, u32 dim_min, u32 dim_max, u32* cells_dev, u64 cap, unsigned long long* ncells_dev);
 int fcm_graph_build_device(fcm_graph* g, const uint2* edges_dev, u64 ne_in, int normalise,
                            std::vector<u64>& off_host);
 

@@ -189,6 +189,16 @@ class DeviceGraph:
         """`graph.flagser_count()`: list without trailing zeros."""
         return trim(self.count_shard(0, 1))
 
+    def cells(self, dim_min, dim_max):
+        """All cells of dimension dim_min..dim_max: (ncells, dim_max + 1) uint32 rows (v0..vd, padded
+        with 0xffffffff) in the recursion's order (flag_complex::for_each_cell)."""
+        cnt = C.c_uint64()
+        check(lib().fcm_graph_cells(self.h, int(dim_min), int(dim_max), None, 0, C.byref(cnt)))
+        out = np.zeros((cnt.value, dim_max + 1), dtype=np.uint32)
+        if cnt.value:
+            check(lib().fcm_graph_cells(self.h, int(dim_min), int(dim_max), ptr(out), cnt.value, C.byref(cnt)))
+        return out
+
     def close(self):
         if self.h:
             lib().fcm_graph_destroy(self.h)
@@ -230,6 +240,21 @@ def flagser_count(n, edges, ctx=None):
 
 
 count_cells = flagser_count      # flag_complex::count_cells (src/bin/all_cxs.rs:123)
+
+
+def for_each_cell(n, edges, f, dim_min, dim_max, ctx=None):
+    """flag_complex::for_each_cell(&G, &mut F, min, max) (src/bin/all_cxs.rs:60-64): F(cell) for every
+    cell of dimension dim_min..dim_max, cell = list of its vertices (v0..vd); enumerated on the GPU."""
+    own = ctx is None
+    ctx = Context(0) if own else ctx
+    g = DeviceGraph(ctx, n, edges)
+    try:
+        for row in g.cells(dim_min, dim_max):
+            f([int(x) for x in row if x != 0xFFFFFFFF])
+    finally:
+        g.close()
+        if own:
+            ctx.close()
 
 
 def undirected_edges(edges):

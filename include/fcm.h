@@ -96,6 +96,13 @@ int fcm_graph_count(fcm_graph* g, uint32_t part, uint32_t nparts, uint64_t* coun
 /* Same, asynchronous on the context stream: result stays in a device buffer of FCM_MAXD u64
  * (pointer returned through counts_dev) so that a collective can consume it without a host hop. */
 int fcm_graph_count_async(fcm_graph* g, uint32_t part, uint32_t nparts, uint64_t** counts_dev);
+/* flag_complex::for_each_cell(&G, &mut F, min, max) (src/bin/all_cxs.rs:60-64,79-83) as a bulk call:
+ * every cell of dimension dim_min..dim_max (dim_max <= 6) as one row of dim_max + 1 vertex ids
+ * (v0..vd, padded with 0xffffffff), rows in the order the recursion meets them with candidates in
+ * ascending order.  *ncells = number of such cells; rows are written only when *ncells <= cap
+ * (call with cap = 0 first to size the buffer).  Synchronous. */
+int fcm_graph_cells(fcm_graph* g, int dim_min, int dim_max, uint32_t* cells_out, uint64_t cap,
+                    uint64_t* ncells);
 /* which kernel to use: 0 = auto (block-local relabelled kernel, dense-row kernel for sources whose
  * out-degree exceeds the shared-memory tile), 1 = force dense-row kernel (the roofline model's
  * "one adjacency row per simplex" kernel).  Results are identical. */

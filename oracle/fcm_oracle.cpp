@@ -942,4 +942,39 @@ void orc_edgebits_save(u64 nslots, const u32* slots, u64 ne, const u32* edges, u
   if (bit != 1) out[o++] = byte;
 }
 
+// flag_complex::for_each_cell(&G, &mut F, min, max) (external crate; used src/bin/all_cxs.rs:60-64,79-83):
+// the flagser recursion calling F with the vertex list of every cell of dimension min..max, sources
+// and candidates in ascending order (ASSUMED callback order: the crate is not on disk).
+// rows of (max + 1) ids padded with 0xffffffff; returns the number of cells (rows beyond cap dropped)
+static void cells_rec(const BitRows& m, const u64* P, std::vector<u32>& cur, int dmin, int dmax, u32* out, u64 cap, u64& n) {
+  const int d = (int)cur.size() - 1;
+  if (d >= dmin && d <= dmax) {
+    if (n < cap) { for (int t = 0; t <= dmax; t++) out[n * (dmax + 1) + t] = t <= d ? cur[t] : 0xffffffffu; }
+    n++;
+  }
+  if (d >= dmax) return;
+  std::vector<u64> Q(m.W);
+  for (u32 k = 0; k < m.W; k++) {
+    u64 bits = P[k];
+    while (bits) {
+      u32 w = k * 64 + __builtin_ctzll(bits);
+      bits &= bits - 1;
+      const u64* rw = m.row(w);
+      for (u32 j = 0; j < m.W; j++) Q[j] = P[j] & rw[j];
+      cur.push_back(w);
+      cells_rec(m, Q.data(), cur, dmin, dmax, out, cap, n);
+      cur.pop_back();
+    }
+  }
+}
+u64 orc_cells(u32 n, u64 ne, const u32* edges, int dmin, int dmax, u32* out, u64 cap) {
+  Graph g = graph_from(n, ne, edges);
+  BitRows m(g.n);
+  for (const Edge& e : g.edges.items) m.set(e.a, e.b);
+  u64 cnt = 0;
+  std::vector<u32> cur;
+  for (u32 v = 0; v < n; v++) { cur.assign(1, v); cells_rec(m, m.row(v), cur, dmin, dmax, out, cap, cnt); }
+  return cnt;
+}
+
 }  // extern "C"

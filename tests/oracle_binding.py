@@ -70,6 +70,8 @@ def lib():
     L.orc_edgebits_slots.restype = u64
     L.orc_edgebits_save.argtypes = [u64, vp, u64, vp, vp]
     L.orc_edgebits_save.restype = None
+    L.orc_cells.argtypes = [u32, u64, vp, i32, i32, vp, u64]
+    L.orc_cells.restype = u64
     _lib = L
     return L
 
@@ -131,6 +133,15 @@ def edgebits_save(slots, edges):
     sl, e = _e(slots), _e(edges)
     out = np.zeros((sl.shape[0] + 7) // 8, dtype=np.uint8)
     lib().orc_edgebits_save(sl.shape[0], _p(sl), e.shape[0], _p(e), _p(out))
+    return out
+
+
+def cells(n, edges, dmin, dmax):
+    """for_each_cell in the recursion's order -> (ncells, dmax + 1) uint32, padded with 0xffffffff"""
+    e = _e(edges)
+    cnt = lib().orc_cells(int(n), e.shape[0], _p(e), int(dmin), int(dmax), None, 0)
+    out = np.zeros((cnt, dmax + 1), dtype=np.uint32)
+    lib().orc_cells(int(n), e.shape[0], _p(e), int(dmin), int(dmax), _p(out), cnt)
     return out
 
 

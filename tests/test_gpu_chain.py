@@ -245,6 +245,36 @@ def test_c3_full_size_chains(ctx, graphs, expected):
     s.close()
 
 
+def test_c3_full_size_default_move_mix(ctx, graphs):
+    # BASELINE config C3 with the CLI's default move mix (clique moves included): many chains run
+    # untraced; sampled chains are compared with the oracle (counts, containers, RNG state), and every
+    # chain keeps |V|, |E| and the incremental == full recount invariant
+    n, e = graphs["c3_er_2000"]
+    nch, steps = 64, 600
+    s = fcm.initialize_new_sampler(ctx, n, e, list(range(nch)), simple=False)
+    s.step(steps)
+    s.status()
+    allr = s.read_all()
+    assert (allr["sampled"] == steps).all()
+    assert (allr["flag_counts"][:, 0] == 2000).all() and (allr["flag_counts"][:, 1] == 199938).all()
+    for k in (3, 63):
+        o = orc.Sampler(n, e, k, move_weights=ds.MOVE_DISTRIBUTION, nthreads=8)
+        o.steps(steps, trace=False)
+        compare_chain(s, k, o)
+    r = s.read(31)
+    assert ds.trim(r["flag_count"]) == fcm.flagser_count(n, r["edges"], ctx)
+    # the three ways to the same chain: delta path from the clique index, from the rows, full counts
+    for kernel in (1, 2):
+        s2 = fcm.initialize_new_sampler(ctx, n, e, [3], simple=False)
+        s2.set_kernel(kernel)
+        got = s2.step_trace(150, 0)
+        o = orc.Sampler(n, e, 3, move_weights=ds.MOVE_DISTRIBUTION, nthreads=8)
+        assert_trace_equal(got, o.steps(150))
+        compare_chain(s2, 0, o)
+        s2.close()
+    s.close()
+
+
 @pytest.mark.parametrize("n,p,pd,steps,minlen", [(30, 0.3, 0.5, 1500, 6), (50, 0.25, 0.8, 1000, 7), (12, 0.7, 0.2, 600, 8)])
 def test_delta_path_deep_and_double_heavy(n, p, pd, steps, minlen, ctx):
     # dense graphs with many double edges: common neighbours carry several tags and the simplices

@@ -7,6 +7,7 @@ import pytest
 import oracle_binding as orc
 import flag_complex_mcmc_b200 as fcm
 from flag_complex_mcmc_b200 import _native as N
+from flag_complex_mcmc_b200 import directed_scm as ds
 from tools import synth
 
 pytestmark = pytest.mark.gpu
@@ -138,4 +139,32 @@ def test_c4_full_size_known_answer(ctx, expected):
     for part in range(8):
         tot += g.count_shard(part, 8)
     assert fcm.directed_scm.trim(tot) == got
+    g.close()
+
+
+@pytest.mark.parametrize("name,dmin,dmax", [("counterexample_any_order", 0, 3), ("c2_chunglu_279", 2, 2),
+                                            ("c2_chunglu_279", 0, 6), ("counterexample_seo_greedy_5_start", 1, 4)])
+def test_for_each_cell_matches_oracle_rows(name, dmin, dmax, ctx, graphs):
+    # flag_complex::for_each_cell (src/bin/all_cxs.rs:60-64): same cells, same order as the recursion
+    n, e = graphs[name]
+    g = ds.DeviceGraph(ctx, n, e)
+    got = g.cells(dmin, dmax)
+    want = orc.cells(n, e, dmin, dmax)
+    assert got.shape == want.shape
+    assert np.array_equal(got, want)
+    fc = g.flagser_count()                                # the plain count still works on the same handle
+    assert fc == orc.count(n, e)
+    g.close()
+    seen = []
+    ds.for_each_cell(n, e, seen.append, 2, 2, ctx)
+    assert seen == [[int(x) for x in r if x != 0xFFFFFFFF] for r in orc.cells(n, e, 2, 2)]
+
+
+def test_for_each_cell_local_subgraph_like_all_cxs(ctx):
+    # the use in src/bin/all_cxs.rs:57-64: 2-cells of a small induced neighbourhood graph, as sorted sets
+    e = rand_graph(24, 0.4, 5, pdouble=0.2)
+    g = ds.DeviceGraph(ctx, 24, e)
+    got = sorted(tuple(sorted(int(x) for x in r)) for r in g.cells(2, 2))
+    want = sorted(tuple(sorted(int(x) for x in r)) for r in orc.cells(24, e, 2, 2))
+    assert got == want and len(got) == g.flagser_count()[2]
     g.close()

@@ -211,3 +211,16 @@ def test_save_flag_file_round_trip(tmp_path, graphs):
     assert n2 == n3 == n
     assert np.array_equal(e2, e3)
     assert sorted(map(tuple, e2.tolist())) == sorted(map(tuple, e.tolist()))
+
+
+def test_cells_oracle_counts_and_order(graphs, expected):
+    # for_each_cell restatement: per-dimension row counts == flagser_count, rows in recursion order
+    n, e = graphs["counterexample_any_order"]
+    fc = orc.count(n, e)
+    rows = orc.cells(n, e, 0, len(fc) - 1)
+    dims = (rows != 0xFFFFFFFF).sum(axis=1) - 1
+    assert [int((dims == d).sum()) for d in range(len(fc))] == fc
+    as_tuples = [tuple(int(x) for x in r if x != 0xFFFFFFFF) for r in rows]
+    assert as_tuples == sorted(as_tuples)                 # a prefix sorts before its extensions
+    e3 = np.array([[0, 1], [1, 2], [0, 2]], dtype=np.uint32)
+    assert orc.cells(3, e3, 1, 2).tolist() == [[0, 1, 0xFFFFFFFF], [0, 1, 2], [0, 2, 0xFFFFFFFF], [1, 2, 0xFFFFFFFF]]
