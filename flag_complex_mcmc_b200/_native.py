@@ -23,6 +23,7 @@ SYMBOLS = [
     "fcm_ensemble_step_trace", "fcm_ensemble_read", "fcm_ensemble_read_all", "fcm_ensemble_status",
     "fcm_ensemble_info", "fcm_ensemble_set_stats", "fcm_ensemble_index_info", "fcm_apply", "fcm_revert", "fcm_bounds_check",
     "fcm_ensemble_edgebits_info", "fcm_ensemble_edgebits_slots", "fcm_ensemble_edgebits",
+    "fcm_ensemble_read_doubles", "fcm_ensemble_restore",
 ]
 
 
@@ -93,6 +94,8 @@ def lib():
     L.fcm_ensemble_edgebits_info.argtypes = [vp, P(u64), P(u64)]
     L.fcm_ensemble_edgebits_slots.argtypes = [vp, vp]
     L.fcm_ensemble_edgebits.argtypes = [vp, u32, u32, vp]
+    L.fcm_ensemble_read_doubles.argtypes = [vp, u32, vp, P(u64)]
+    L.fcm_ensemble_restore.argtypes = [vp, u32, vp, u64, vp, u64, vp, vp, i32, u64, u64]
     for name in SYMBOLS:
         f = getattr(L, name)
         if f.restype is C.c_int and name not in ("fcm_abi_version", "fcm_device_count"):

@@ -7,10 +7,12 @@
 // P = out(v0) ∩ ... ∩ out(vd); each member of P closes a (d+1)-simplex.
 //
 // Two kernels, identical results:
-//   count_local_kernel<WK>  one CTA per source vertex v0.  out(v0) is relabelled 0..k-1 and the
+//   count_local_kernel<WK, EMIT>  one CTA per source vertex v0.  out(v0) is relabelled 0..k-1 and the
 //       k x k induced adjacency is gathered ONCE from the packed HBM rows into shared memory
 //       (k*WK 64-bit words).  Every deeper intersection is then a WK-word AND in shared memory
-//       instead of a W-word row read (C4: WK <= 8 against W = 490), one DFS per thread.
+//       instead of a W-word row read (C4: WK <= 8 against W = 490); the simplices under v0 go through
+//       a per-warp stack of pending tuples, one simplex per lane per step (see the kernel).
+//       EMIT = true additionally writes the cells of a dimension range out (for_each_cell).
 //   count_dense_kernel      one warp per source vertex, candidate sets of full row width staged
 //       in a per-warp stack, rows read with coalesced 128-bit loads, popc + warp reduce.  This is
 //       the "one adjacency row per simplex" kernel of the roofline model; it also

@@ -694,6 +694,87 @@ extern "C" int fcm_ensemble_edgebits(fcm_ensemble* e, uint32_t chain_first, uint
   return FCM_OK;
 }
 
+// ---- checkpoint / resume of one chain: the device analogue of io::save_state / load_state
+//      (src/io.rs:51-62).  What a chain IS beyond the static structures: its two edge containers in
+//      order (that order decides every later sample_edge), the RNG state and the counters. ----
+extern "C" int fcm_ensemble_read_doubles(fcm_ensemble* e, uint32_t chain, uint32_t* pairs_out, uint64_t* ndouble_out) {
+  REQUIRE(e && ndouble_out, "ensemble/ndouble_out is null");
+  REQUIRE(chain < e->p.nchains, "chain out of range");
+  std::vector<ChainState> st;
+  int rc = fetch_states(e, st, chain, 1);
+  if (rc) return rc;
+  const u32 nd = st[0].ND;
+  *ndouble_out = nd;
+  if (pairs_out && nd) {
+    std::vector<u32> dbl(nd);
+    FCM_CUDA(cudaMemcpyAsync(dbl.data(), e->p.dbl + (u64)chain * e->p.stride32, (size_t)nd * 4, cudaMemcpyDeviceToHost, e->ctx->stream));
+    FCM_CUDA(cudaStreamSynchronize(e->ctx->stream));
+    for (u32 i = 0; i < nd; i++) {                     // [min, max] as sample_double_edge returns it
+      const uint2 ab = e->pair_ab_host[dbl[i]];
+      pairs_out[2 * i] = ab.y; pairs_out[2 * i + 1] = ab.x;
+    }
+  }
+  return FCM_OK;
+}
+
+extern "C" int fcm_ensemble_restore(fcm_ensemble* e, uint32_t chain, const uint32_t* edges, uint64_t nedges,
+                                    const uint32_t* doubles, uint64_t ndouble, const uint64_t* rng4,
+                                    const uint64_t* flag_count, int len, uint64_t sampled, uint64_t accepted) {
+  REQUIRE(e && rng4 && flag_count, "ensemble/rng4/flag_count is null");
+  REQUIRE(chain < e->p.nchains, "chain out of range");
+  REQUIRE((nedges == 0 || edges) && (ndouble == 0 || doubles), "edges/doubles is null");
+  REQUIRE(len >= 0 && len <= FCM_MAXD, "flag_count longer than FCM_MAXD");
+  FCM_CUDA(cudaSetDevice(e->ctx->device));
+  const EnsParams& p = e->p;
+  const u64 nslots = 2 * p.npairs;
+  std::vector<u32> blk(p.stride32, 0);
+  u32* items = blk.data() + p.off_items;
+  u32* pos = blk.data() + p.off_pos;
+  u32* dbl = blk.data() + p.off_dbl;
+  u32* dblpos = blk.data() + p.off_dblpos;
+  u32* ori = blk.data() + p.off_ori;
+  u64* adj = (u64*)blk.data();
+  for (u64 i = 0; i < nslots; i++) pos[i] = FCM_NONE;
+  for (u64 i = 0; i < p.npairs; i++) dblpos[i] = FCM_NONE;
+  REQUIRE(nedges <= nslots, "more edges than directed slots");
+  for (u64 i = 0; i < nedges; i++) {
+    const u32 a = edges[2 * i], b = edges[2 * i + 1];
+    auto it = a == b ? e->pairmap.end() : e->pairmap.find(pkey(std::max(a, b), std::min(a, b)));
+    if (it == e->pairmap.end()) { fcm_set_error("restore: edge %llu = (%u,%u) is not a pair of the underlying undirected graph", (unsigned long long)i, a, b); return FCM_ENOTADJ; }
+    const u32 slot = 2 * it->second + (a > b ? 0u : 1u);
+    if (pos[slot] != FCM_NONE) { fcm_set_error("restore: edge (%u,%u) listed twice", a, b); return FCM_EINVAL; }
+    pos[slot] = (u32)i; items[i] = slot;
+    adj[(size_t)a * p.W + (b >> 6)] |= 1ULL << (b & 63);
+    ori[slot >> 5] |= 1u << (slot & 31);
+  }
+  for (u64 q = 0; q < p.npairs; q++)
+    if (pos[2 * q] == FCM_NONE && pos[2 * q + 1] == FCM_NONE) { fcm_set_error("restore: pair (%u,%u) has lost both directions", e->pair_ab_host[q].x, e->pair_ab_host[q].y); return FCM_EINVAL; }
+  for (u64 i = 0; i < ndouble; i++) {
+    const u32 a = doubles[2 * i], b = doubles[2 * i + 1];
+    auto it = a == b ? e->pairmap.end() : e->pairmap.find(pkey(std::max(a, b), std::min(a, b)));
+    if (it == e->pairmap.end() || pos[2 * it->second] == FCM_NONE || pos[2 * it->second + 1] == FCM_NONE || dblpos[it->second] != FCM_NONE) {
+      fcm_set_error("restore: double-edge entry %llu = (%u,%u) is not a double edge of the edge list (or listed twice)", (unsigned long long)i, a, b);
+      return FCM_EINVAL;
+    }
+    dblpos[it->second] = (u32)i; dbl[i] = it->second;
+  }
+  u64 have_double = 0;
+  for (u64 q = 0; q < p.npairs; q++) have_double += pos[2 * q] != FCM_NONE && pos[2 * q + 1] != FCM_NONE;
+  if (have_double != ndouble) { fcm_set_error("restore: the edge list has %llu double edges, the double-edge list %llu", (unsigned long long)have_double, (unsigned long long)ndouble); return FCM_EINVAL; }
+  ChainState cs;
+  memset(&cs, 0, sizeof(cs));
+  memcpy(cs.rng, rng4, 32);
+  cs.sampled = sampled; cs.accepted = accepted;
+  for (int d = 0; d < len; d++) cs.flag_count[d] = flag_count[d];
+  cs.fc_len = len; cs.E = (u32)nedges; cs.ND = (u32)ndouble;
+  cudaStream_t s = e->ctx->stream;
+  FCM_CUDA(cudaStreamSynchronize(s));
+  FCM_CUDA(cudaMemcpyAsync((u32*)p.adj + (u64)chain * p.stride32, blk.data(), p.stride32 * 4, cudaMemcpyHostToDevice, s));
+  FCM_CUDA(cudaMemcpyAsync(p.st + chain, &cs, sizeof(cs), cudaMemcpyHostToDevice, s));
+  FCM_CUDA(cudaStreamSynchronize(s));
+  return FCM_OK;
+}
+
 // ---- explicit-edit API: State::apply_transition / revert_transition (src/lib.rs:61-95) ----
 static int upload_edits(fcm_ensemble* e, const uint32_t* edits3, int nedits) {
   REQUIRE(nedits >= 0 && nedits <= FCM_MAXEDIT, "too many edits (FCM_MAXEDIT = 64)");

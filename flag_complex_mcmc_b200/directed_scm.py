@@ -430,6 +430,23 @@ class MCMCSampler:
         check(lib().fcm_bounds_check(self.h, int(chain), C.byref(ok)))
         return bool(ok.value)
 
+    # -- io::save_state / load_state (src/io.rs:51-62): checkpoint / resume of one chain --
+    def checkpoint(self, chain=0):
+        r = self.read(chain, want_edges=True)
+        nd = C.c_uint64()
+        dbl = np.zeros((max(r["ndouble"], 1), 2), dtype=np.uint32)
+        check(lib().fcm_ensemble_read_doubles(self.h, int(chain), ptr(dbl), C.byref(nd)))
+        return {"edges": r["edges"], "doubles": dbl[:nd.value].copy(), "rng": np.asarray(r["rng"], dtype=np.uint64),
+                "flag_count": np.asarray(r["flag_count"], dtype=np.uint64), "sampled": r["sampled"], "accepted": r["accepted"]}
+
+    def restore(self, chain, ck):
+        e = edges_array(ck["edges"])
+        d = edges_array(ck["doubles"])
+        rng = np.ascontiguousarray(np.asarray(ck["rng"], dtype=np.uint64))
+        fc = np.ascontiguousarray(np.asarray(ck["flag_count"], dtype=np.uint64))
+        check(lib().fcm_ensemble_restore(self.h, int(chain), ptr(e), int(e.shape[0]), ptr(d), int(d.shape[0]), ptr(rng),
+                                         ptr(fc), int(fc.size), int(ck["sampled"]), int(ck["accepted"])))
+
     # -- io::BitOutput (src/io.rs:128-212): samples packed on the device --
     def edgebits_info(self):
         ns, nb = C.c_uint64(), C.c_uint64()
@@ -516,3 +533,26 @@ class BitOutput:
     def flush(self):
         if self.current_file is not None:
             self.current_file.flush()
+
+
+def save_state(fname, sample_number, sampler, chain=0):
+    """io::save_state (src/io.rs:51-56): (sample_number, chain state) to `fname` via a temp file + rename."""
+    import os
+    ck = sampler.checkpoint(chain)
+    tmp = fname + ".tmp"
+    with open(tmp, "wb") as f:
+        np.savez(f, sample_number=np.int64(sample_number), sample_distance=np.int64(sampler.sample_distance),
+                 bounds_min=np.asarray(sampler.bounds.flag_count_min, dtype=np.uint64),
+                 bounds_max=np.asarray(sampler.bounds.flag_count_max, dtype=np.uint64),
+                 sampled=np.uint64(ck["sampled"]), accepted=np.uint64(ck["accepted"]),
+                 **{k: ck[k] for k in ("edges", "doubles", "rng", "flag_count")})
+    os.replace(tmp, fname)
+
+
+def load_state(fname, sampler, chain=0):
+    """io::load_state (src/io.rs:58-62) into chain `chain` of `sampler` -> sample_number."""
+    z = np.load(fname)
+    sampler.restore(chain, {k: z[k] for k in ("edges", "doubles", "rng", "flag_count")} |
+                    {"sampled": int(z["sampled"]), "accepted": int(z["accepted"])})
+    sampler.set_bounds(Bounds([int(x) for x in z["bounds_min"]], [int(x) for x in z["bounds_max"]]))
+    return int(z["sample_number"])

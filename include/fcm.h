@@ -209,6 +209,19 @@ int fcm_ensemble_edgebits_slots(fcm_ensemble* e, uint32_t* slots_out);
  * and writes nchains rows of nbytes bytes to out (host). */
 int fcm_ensemble_edgebits(fcm_ensemble* e, uint32_t chain_first, uint32_t nchains, uint8_t* out);
 
+/* ------------------------------------------------------------------------------------------------
+ * 6. Checkpoint / resume of a chain: the device analogue of io::save_state / load_state
+ *    (src/io.rs:51-62).  A chain is its edge container in order (fcm_ensemble_read: edges_out), its
+ *    double-edge container in order (fcm_ensemble_read_doubles: [min,max] pairs), the RNG state, the
+ *    counters and flag_count.  fcm_ensemble_restore puts such a state into chain `chain` of an
+ *    ensemble created from a graph with the same underlying undirected graph; the chain then
+ *    continues exactly as the checkpointed one would have.
+ * ---------------------------------------------------------------------------------------------- */
+int fcm_ensemble_read_doubles(fcm_ensemble* e, uint32_t chain, uint32_t* pairs_out, uint64_t* ndouble_out);
+int fcm_ensemble_restore(fcm_ensemble* e, uint32_t chain, const uint32_t* edges, uint64_t nedges,
+                         const uint32_t* doubles, uint64_t ndouble, const uint64_t* rng4,
+                         const uint64_t* flag_count, int len, uint64_t sampled, uint64_t accepted);
+
 #ifdef __cplusplus
 }
 #endif

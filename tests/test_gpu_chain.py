@@ -376,3 +376,42 @@ def test_edgebits_match_bitoutput_of_the_chain_graph(name, kernel, ctx, graphs, 
     n2, e2 = ds.read_flag_file(str(tmp_path / "out" / "graph.flag"))
     assert n2 == n and sorted(map(tuple, e2.tolist())) == sorted(map(tuple, e.tolist()))
     s.close()
+
+
+@pytest.mark.parametrize("simple", [True, False])
+def test_checkpoint_restore_resumes_exactly(simple, ctx, graphs, tmp_path):
+    # io::save_state / load_state (src/io.rs:51-62): a restored chain continues as the original would
+    n, e = graphs["c2_chunglu_279"]
+    mw = ds.MOVE_DISTRIBUTION_SIMPLE if simple else ds.MOVE_DISTRIBUTION
+    s = fcm.initialize_new_sampler(ctx, n, e, [3, 4], simple=simple)
+    s.step(800)
+    f = str(tmp_path / "state.npz")
+    fcm.save_state(f, 7, s, chain=1)
+    ck = s.checkpoint(1)
+    assert ck["doubles"].shape[0] == s.read(1)["ndouble"]
+    s.step(500)
+    want = s.read(1)
+    s2 = fcm.initialize_new_sampler(ctx, n, e, [99, 100, 101], simple=simple)
+    assert fcm.load_state(f, s2, chain=2) == 7
+    s2.step(500)
+    got = s2.read(2)
+    for k in ("flag_count", "rng", "sampled", "accepted", "nedges", "ndouble"):
+        assert got[k] == want[k], k
+    assert np.array_equal(got["edges"], want["edges"])
+    assert np.array_equal(s2.checkpoint(2)["doubles"], s.checkpoint(1)["doubles"])
+    o = orc.Sampler(n, e, 4, 0.01, move_weights=mw)
+    o.steps(1300, trace=False)
+    compare_chain(s2, 2, o)
+    o0 = orc.Sampler(n, e, 99, 0.01, move_weights=mw)     # the neighbours of the restored chain are untouched
+    o0.steps(500, trace=False)
+    compare_chain(s2, 0, o0)
+    bad = dict(ck)
+    bad["edges"] = ck["edges"].copy()
+    bad["edges"][0] = [0, 0]
+    with pytest.raises(fcm.FcmError):
+        s2.restore(1, bad)
+    bad["edges"] = ck["edges"][:-1]
+    with pytest.raises(fcm.FcmError):
+        s2.restore(1, bad)
+    s.close()
+    s2.close()
