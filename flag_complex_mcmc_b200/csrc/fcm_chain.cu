@@ -278,7 +278,7 @@ __device__ int local_count_any(const u64* M, int K, int KW, int lane, u64* out, 
 enum { FL_DEEP = 0, FL_TOP = 1, FL_ERR = 2, FL_RC = 3, FL_K = 4, FL_LEN = 5, FL_OVF = 6, FL_E = 8, FL_ND = 9, FL_ACC = 10, FL_FCLEN = 11 };
 enum { PK_KIND = 0, PK_SLOT, PK_DELME, PK_IDX, PK_DIDX, PK_DPAIR, PK_LAST, PK_QPOS, PK_TA, PK_TB, PK_TDM0, PK_TDM1,
        PK_CA, PK_CD, PK_OA, PK_OD, PK_ORIA, PK_ORID };
-#define CQ_MAXPAIRS 256                 // entries of new_edges / old_edges in clique_swap (src/lib.rs:256-270)
+#define CQ_MAXPAIRS 192                 // entries of new_edges / old_edges in clique_swap (src/lib.rs:256-270): two disjoint 9-cliques; 28 warps of 7.8 KB fit one SM
 #define CQ_BYTES (3 * FCM_MAXCQ * 4 + 2 * CQ_MAXPAIRS * 8 + 64)
 struct WarpSmem {
   u64 *M, *fc, *pre, *post;
@@ -1604,7 +1604,10 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
   // ensembles with clique moves size the local matrix M for the union neighbourhood of two cliques; when
   // every common-neighbour list fits the delta path and the full counts are not forced, M is never
   // touched: one word per row keeps the per-warp tile small and more chains resident
-  if (e->cliques && !e->force_full && p.maxc <= FAST_C) p.KWcap = 1;
+  if (e->cliques && !e->force_full && p.maxc <= FAST_C) {
+    p.KWcap = 1;
+    if (!INSTR) p.Kcap = 8;                             // the vertex list is only built for the statistic K
+  }
   const size_t per_warp = chain_smem_per_warp_mode(p.Kcap, p.KWcap, !IDX, e->cliques != 0);
   // warps per block: the choice that keeps most warps resident on one SM (big neighbourhood tiles of
   // ensembles with clique moves fit better in smaller blocks)
@@ -1613,7 +1616,8 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
     size_t best = 0;
     for (int w = 4; w >= 1; w >>= 1) {
       if (per_warp * w > e->ctx->smem_optin) continue;
-      const size_t resident = std::min<size_t>(7, (size_t)(227 * 1024) / (per_warp * w + 1024)) * w;
+      // blocks per SM: registers (72 per thread, 64 K per SM => 28 warps) and shared memory
+      const size_t resident = std::min<size_t>(28 / w, (size_t)(227 * 1024) / (per_warp * w + 1024)) * w;
       if (resident > best) { best = resident; wpb = w; }
     }
   }
