@@ -938,11 +938,13 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
   const int n_d = (int)hdr[0], n_c = (int)hdr[1], n_a = (int)hdr[2];
   // ---- has_edge among d: lane j probes column d[j] of row d[i] ----
   {
-    const u32 col = lane < n_d ? dv[lane] : 0u;
-    for (int i = 0; i < n_d; i++) {
-      const u32 w = lane < n_d ? __ldcg(&cb[dv[i] * W32 + (col >> 5)]) : 0u;
-      const u32 b = __ballot_sync(FULL, lane < n_d && ((w >> (col & 31)) & 1u));
-      if (lane == 0) H[i] = b;
+    // every (i, j) probe is an independent load: all of them are in flight together
+    if (lane < n_d) H[lane] = 0;
+    __syncwarp();
+    for (int t = lane; t < n_d * n_d; t += 32) {
+      const int i = t / n_d, j = t - i * n_d;
+      const u32 col = dv[j];
+      if ((__ldcg(&cb[dv[i] * W32 + (col >> 5)]) >> (col & 31)) & 1u) atomicOr(&H[i], 1u << j);
     }
   }
   __syncwarp();
@@ -1032,18 +1034,39 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
       const uint2 ft = slot_edge(p, slot);               // the edge u -> v
       const u32 o = __ldg(&p.nb_off[slot >> 1]);
       const int cc = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - o);
-      Gathered ga;
-      gather_pair(p, cb, o, cc, ft.x, ft.y, s.cv, s.rowoff, s.A, lane, ga);
-      const u64 X = ga.inU & ga.inV, Y = ga.outU & ga.inV, Z = ga.outU & ga.outV;
       edges += sign;
-      tri += sign * (__popcll(X) + __popcll(Y) + __popcll(Z));
-      count_through_edge<u64>(X, Y, Z, cc, s.A, lane, sign, cnt, s.deep, s.dflag);
+      if (red && cc <= NARROW_C) {
+        // the pair's triangles and 4-cliques from the static clique index, their orientation from the
+        // chain's orientation bits (kept current edit by edit below): two round trips instead of c rows
+        const uint4 i0 = __ldg(&p.pinfo[2 * (slot >> 1)]), i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]);
+        u32* const sA32 = (u32*)(wb + SM_A);
+        OriReq r;
+        idx_issue(p, c.ori, i0.z, cc, i0.w, (int)i1.y, ft.x == i0.x, lane, r);
+        const G32 g = idx_finish(p, c.ori, i0.w, (int)i1.y, r, sA32, lane);
+        const u32 a32v = sA32[lane];
+        __syncwarp();
+        s.A[lane] = a32v;                               // count_through_edge reads 64-bit rows
+        __syncwarp();
+        const u32 X = g.inU & g.inV, Y = g.outU & g.inV, Z = g.outU & g.outV;
+        tri += sign * (__popc(X) + __popc(Y) + __popc(Z));
+        count_through_edge<u32>(X, Y, Z, cc, s.A, lane, sign, cnt, s.deep, s.dflag);
+      } else {
+        Gathered ga;
+        gather_pair(p, cb, o, cc, ft.x, ft.y, s.cv, s.rowoff, s.A, lane, ga);
+        const u64 X = ga.inU & ga.inV, Y = ga.outU & ga.inV, Z = ga.outU & ga.outV;
+        tri += sign * (__popcll(X) + __popcll(Y) + __popcll(Z));
+        count_through_edge<u64>(X, Y, Z, cc, s.A, lane, sign, cnt, s.deep, s.dflag);
+      }
       __syncwarp();
-      if (lane == 0) {                                  // the next edit sees this one
+      if (lane == 0) {                                  // the next edit sees this one: row bit + orientation bit
         u32* const w = &cb[ft.x * W32 + (ft.y >> 5)];
         const u32 m = 1u << (ft.y & 31);
         if (red) { if (add) atomicOr(w, m); else atomicAnd(w, ~m); }
         else { const u32 wv = __ldcg(w); *w = add ? (wv | m) : (wv & ~m); }
+        u32* const ow = &c.ori[slot >> 5];
+        const u32 om = 1u << (slot & 31);
+        const u32 ov = __ldcg(ow);
+        *ow = add ? (ov | om) : (ov & ~om);
         __threadfence_block();
       }
       __syncwarp();
@@ -1081,29 +1104,35 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
   const bool ok = bounds_ok(p, fnew, lane);
   // containers: the edits in order; a rejected transition is applied and reverted like the reference
   // does (src/lib.rs:186-191), which leaves the containers in a different ORDER than before
+  {
+    // the serial container replay below walks pos / dblpos of every edited slot: touch them all at once
+    // first so that the replay finds them in cache
+    u32 touch = 0;
+    for (int t = lane; t < nedit; t += 32) {
+      const u32 slot = s.edits[2 * t];
+      touch += c.pos[slot] + c.pos[slot ^ 1] + c.dblpos[slot >> 1];
+    }
+    if (touch == 0x9e3779b9u && lane == 33) sflag[FL_OVF] = 0;    // keeps the loads alive, never true
+  }
   for (int pass = 0; pass < (ok ? 1 : 2); pass++)
     for (int t = 0; t < nedit; t++) {
       const u32 slot = s.edits[2 * t];
       const bool add = (s.edits[2 * t + 1] != 0) != (pass == 1);
       if (add) c_add_edge(c, slot, lane); else c_remove_edge(c, slot, lane);
     }
-  if (lane == 0 && (ok != bits_applied || ok))
-    for (int t = 0; t < nedit; t++) {                   // adjacency rows (set, or taken back after a rejected delta pass) + orientation bits
+  if (lane == 0 && ok != bits_applied)
+    for (int t = 0; t < nedit; t++) {                   // rows + orientation bits: set after the full counts, or taken back after a rejected delta pass
       const u32 slot = s.edits[2 * t];
       const bool add = (s.edits[2 * t + 1] != 0) == ok;
-      if (ok != bits_applied) {
-        const uint2 ft = slot_edge(p, slot);
-        u32* const w = &cb[ft.x * W32 + (ft.y >> 5)];
-        const u32 m = 1u << (ft.y & 31);
-        if (red) { if (add) atomicOr(w, m); else atomicAnd(w, ~m); }
-        else { const u32 wv = __ldcg(w); *w = add ? (wv | m) : (wv & ~m); }
-      }
-      if (ok) {
-        u32* const o = &c.ori[slot >> 5];
-        const u32 om = 1u << (slot & 31);
-        const u32 ov = __ldcg(o);
-        *o = add ? (ov | om) : (ov & ~om);
-      }
+      const uint2 ft = slot_edge(p, slot);
+      u32* const w = &cb[ft.x * W32 + (ft.y >> 5)];
+      const u32 m = 1u << (ft.y & 31);
+      if (red) { if (add) atomicOr(w, m); else atomicAnd(w, ~m); }
+      else { const u32 wv = __ldcg(w); *w = add ? (wv | m) : (wv & ~m); }
+      u32* const o = &c.ori[slot >> 5];
+      const u32 om = 1u << (slot & 31);
+      const u32 ov = __ldcg(o);
+      *o = add ? (ov | om) : (ov & ~om);
     }
   __syncwarp();
   if (ok) st->flag_count[lane] = fnew;
