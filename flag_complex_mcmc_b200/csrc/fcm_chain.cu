@@ -1043,13 +1043,34 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
         OriReq r;
         idx_issue(p, c.ori, i0.z, cc, i0.w, (int)i1.y, ft.x == i0.x, lane, r);
         const G32 g = idx_finish(p, c.ori, i0.w, (int)i1.y, r, sA32, lane);
-        const u32 a32v = sA32[lane];
-        __syncwarp();
-        s.A[lane] = a32v;                               // count_through_edge reads 64-bit rows
-        __syncwarp();
-        const u32 X = g.inU & g.inV, Y = g.outU & g.inV, Z = g.outU & g.outV;
-        tri += sign * (__popc(X) + __popc(Y) + __popc(Z));
-        count_through_edge<u32>(X, Y, Z, cc, s.A, lane, sign, cnt, s.deep, s.dflag);
+        // first the flip path's tagged single-mask graph (<= 32 tagged copies, <= DELTA_SD + 1 vertices);
+        // when it does not fit, the general tagged count on the same gathered rows
+        Tagged tg;
+        bool done = false;
+        if (hot_tag(g, cc, false, sA32, (u32*)(wb + SM_AT), (u32*)(wb + SM_SRC), lane, tg)) {
+          int save[DELTA_SD];
+#pragma unroll
+          for (int k = 0; k < DELTA_SD; k++) save[k] = cnt[k];
+          hot_count(tg.come, tg.row, (const u32*)(wb + SM_AT), lane, sign, cnt, &sflag[FL_OVF]);
+          __syncwarp();
+          if (!sflag[FL_OVF]) { tri += sign * __popc(tg.come); done = true; }
+          else {
+#pragma unroll
+            for (int k = 0; k < DELTA_SD; k++) cnt[k] = save[k];
+            __syncwarp();
+            if (lane == 0) sflag[FL_OVF] = 0;
+            __syncwarp();
+          }
+        }
+        if (!done) {
+          const u32 a32v = sA32[lane];
+          __syncwarp();
+          s.A[lane] = a32v;                             // count_through_edge reads 64-bit rows
+          __syncwarp();
+          const u32 X = g.inU & g.inV, Y = g.outU & g.inV, Z = g.outU & g.outV;
+          tri += sign * (__popc(X) + __popc(Y) + __popc(Z));
+          count_through_edge<u32>(X, Y, Z, cc, s.A, lane, sign, cnt, s.deep, s.dflag);
+        }
       } else {
         Gathered ga;
         gather_pair(p, cb, o, cc, ft.x, ft.y, s.cv, s.rowoff, s.A, lane, ga);
