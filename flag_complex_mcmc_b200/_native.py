@@ -19,7 +19,7 @@ SYMBOLS = [
     "fcm_ctx_timer_begin", "fcm_ctx_timer_end", "fcm_ctx_launches",
     "fcm_graph_create", "fcm_graph_create_normalised", "fcm_graph_destroy", "fcm_graph_count",
     "fcm_graph_count_async", "fcm_graph_set_kernel", "fcm_graph_info", "fcm_graph_cells",
-    "fcm_ensemble_create", "fcm_ensemble_destroy", "fcm_ensemble_set_bounds", "fcm_ensemble_set_kernel", "fcm_ensemble_step",
+    "fcm_edge_neighborhoods", "fcm_ensemble_create", "fcm_ensemble_destroy", "fcm_ensemble_set_bounds", "fcm_ensemble_set_kernel", "fcm_ensemble_step",
     "fcm_ensemble_step_trace", "fcm_ensemble_read", "fcm_ensemble_read_all", "fcm_ensemble_status",
     "fcm_ensemble_info", "fcm_ensemble_set_stats", "fcm_ensemble_index_info", "fcm_apply", "fcm_revert", "fcm_bounds_check",
     "fcm_ensemble_edgebits_info", "fcm_ensemble_edgebits_slots", "fcm_ensemble_edgebits",
@@ -76,6 +76,7 @@ def lib():
     L.fcm_graph_set_kernel.argtypes = [vp, i32]
     L.fcm_graph_info.argtypes = [vp, P(u32), P(u64), P(u32), P(u32)]
     L.fcm_graph_cells.argtypes = [vp, i32, i32, vp, u64, P(u64)]
+    L.fcm_edge_neighborhoods.argtypes = [vp, u32, u64, vp, P(u64), P(u64), vp, vp, vp]
     L.fcm_ensemble_create.argtypes = [vp, u32, u64, vp, u32, vp, vp, i32, vp, i32, vp, i32, vp, P(vp)]
     L.fcm_ensemble_destroy.argtypes = [vp]
     L.fcm_ensemble_set_bounds.argtypes = [vp, vp, i32, vp, i32]

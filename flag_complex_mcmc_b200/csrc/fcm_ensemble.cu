@@ -145,6 +145,155 @@ static std::vector<std::vector<u32>> maximal_cliques(u32 n, const std::vector<st
   return all;
 }
 
+// ---- compute_edge_neighborhoods (src/lib.rs:331-356) on the device: for every adjacent pair (big, small)
+//      the ascending list of common undirected neighbours = the set bits of und[big] & und[small].
+//      One warp per pair: a counting pass, offsets by prefix sum, a compaction pass (lane l owns word
+//      l of every 32-word chunk; warp scan of the popcounts gives each lane its place in the list). ----
+__global__ void und_bits_kernel(const uint2* __restrict__ pairs, u64 np, u32 W, u64* __restrict__ und) {
+  for (u64 q = (u64)blockIdx.x * blockDim.x + threadIdx.x; q < np; q += (u64)gridDim.x * blockDim.x) {
+    const uint2 ab = pairs[q];
+    atomicOr((unsigned long long*)&und[(u64)ab.x * W + (ab.y >> 6)], 1ULL << (ab.y & 63));
+    atomicOr((unsigned long long*)&und[(u64)ab.y * W + (ab.x >> 6)], 1ULL << (ab.x & 63));
+  }
+}
+// dbl (may be null): bit rows of the DOUBLE edges.  The reference builds its adjacency lists from the
+// directed edges without deduplication (src/lib.rs:333-336), so a common neighbour w joined to both a
+// and b by double edges appears TWICE in the list of (a, b); with dbl given the lists carry that
+// multiplicity (the API-visible map), without it they are sets (what the chains use).
+__global__ void nbhd_count_kernel(const uint2* __restrict__ pairs, u64 np, u32 W, const u64* __restrict__ und,
+                                  const u64* __restrict__ dbl, u32* __restrict__ cnt) {
+  const int lane = threadIdx.x & 31;
+  const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
+  for (u64 q = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < np; q += nwarps) {
+    const uint2 ab = pairs[q];
+    const u64 *ra = und + (u64)ab.x * W, *rb = und + (u64)ab.y * W;
+    u32 c = 0;
+    for (u32 w = lane; w < W; w += 32) {
+      c += __popcll(__ldg(&ra[w]) & __ldg(&rb[w]));
+      if (dbl) c += __popcll(__ldg(&dbl[(u64)ab.x * W + w]) & __ldg(&dbl[(u64)ab.y * W + w]));
+    }
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0) cnt[q] = c;
+  }
+}
+__global__ void nbhd_fill_kernel(const uint2* __restrict__ pairs, u64 np, u32 W, const u64* __restrict__ und,
+                                 const u64* __restrict__ dbl, const u64* __restrict__ off, u32* __restrict__ list) {
+  const int lane = threadIdx.x & 31;
+  const u64 nwarps = ((u64)gridDim.x * blockDim.x) >> 5;
+  for (u64 q = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < np; q += nwarps) {
+    const uint2 ab = pairs[q];
+    const u64 *ra = und + (u64)ab.x * W, *rb = und + (u64)ab.y * W;
+    u64 base = off[q];
+    for (u32 w0 = 0; w0 < W; w0 += 32) {
+      const u32 w = w0 + lane;
+      u64 bits = w < W ? (__ldg(&ra[w]) & __ldg(&rb[w])) : 0ULL;
+      const u64 twice = (dbl && w < W) ? (__ldg(&dbl[(u64)ab.x * W + w]) & __ldg(&dbl[(u64)ab.y * W + w])) : 0ULL;
+      const u32 c = __popcll(bits) + __popcll(twice);
+      u32 incl = c;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) { const u32 t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
+      u64 o = base + incl - c;
+      while (bits) {
+        const int b = __ffsll((long long)bits) - 1;
+        bits &= bits - 1;
+        list[o++] = w * 64 + b;
+        if ((twice >> b) & 1ULL) list[o++] = w * 64 + b;
+      }
+      base += __shfl_sync(0xffffffffu, incl, 31);
+    }
+  }
+}
+
+// pairs (big, small) -> nb_off[npairs + 1] (exclusive prefix), nb_list, maxc.  Temporary device memory only.
+static int edge_neighborhoods_device(fcm_ctx* ctx, u32 n, const std::vector<uint2>& pair_ab,
+                                     std::vector<u64>& nb_off, std::vector<u32>& nb_list, u32* maxc_out,
+                                     const std::vector<uint2>* double_pairs = nullptr) {
+  const u64 np = pair_ab.size();
+  nb_off.assign(np + 1, 0);
+  nb_list.assign(1, 0);
+  *maxc_out = 0;
+  if (np == 0) return FCM_OK;
+  const u32 W = ((n + 63) / 64 + 1) & ~1u;
+  cudaStream_t s = ctx->stream;
+  uint2* d_pairs = nullptr; u64* d_und = nullptr; u32* d_cnt = nullptr; u64* d_off = nullptr; u32* d_list = nullptr;
+  uint2* d_dpairs = nullptr; u64* d_dbl = nullptr;
+  auto cleanup = [&]() { cudaFree(d_pairs); cudaFree(d_und); cudaFree(d_cnt); cudaFree(d_off); cudaFree(d_list); cudaFree(d_dpairs); cudaFree(d_dbl); };
+#define N_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { fcm_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); cleanup(); return e__ == cudaErrorMemoryAllocation ? FCM_ENOMEM : FCM_ECUDA; } } while (0)
+  N_CUDA(cudaMalloc(&d_pairs, np * 8));
+  N_CUDA(cudaMalloc(&d_und, (size_t)n * W * 8));
+  N_CUDA(cudaMalloc(&d_cnt, np * 4));
+  N_CUDA(cudaMemcpyAsync(d_pairs, pair_ab.data(), np * 8, cudaMemcpyHostToDevice, s));
+  N_CUDA(cudaMemsetAsync(d_und, 0, (size_t)n * W * 8, s));
+  const int tb = 256;
+  const int gb = (int)std::min<u64>((np + tb - 1) / tb, (u64)ctx->sm_count * 16);
+  und_bits_kernel<<<gb, tb, 0, s>>>(d_pairs, np, W, d_und);
+  if (double_pairs) {
+    N_CUDA(cudaMalloc(&d_dbl, (size_t)n * W * 8));
+    N_CUDA(cudaMemsetAsync(d_dbl, 0, (size_t)n * W * 8, s));
+    if (!double_pairs->empty()) {
+      N_CUDA(cudaMalloc(&d_dpairs, double_pairs->size() * 8));
+      N_CUDA(cudaMemcpyAsync(d_dpairs, double_pairs->data(), double_pairs->size() * 8, cudaMemcpyHostToDevice, s));
+      und_bits_kernel<<<gb, tb, 0, s>>>(d_dpairs, double_pairs->size(), W, d_dbl);
+      ctx->launches++;
+    }
+  }
+  const int gw = (int)std::min<u64>((np * 32 + tb - 1) / tb, (u64)ctx->sm_count * 32);
+  nbhd_count_kernel<<<gw, tb, 0, s>>>(d_pairs, np, W, d_und, d_dbl, d_cnt);
+  ctx->launches += 2;
+  N_CUDA(cudaGetLastError());
+  std::vector<u32> cnt(np);
+  N_CUDA(cudaMemcpyAsync(cnt.data(), d_cnt, np * 4, cudaMemcpyDeviceToHost, s));
+  N_CUDA(cudaStreamSynchronize(s));
+  u32 maxc = 0;
+  for (u64 q = 0; q < np; q++) { maxc = std::max(maxc, cnt[q]); nb_off[q + 1] = nb_off[q] + cnt[q]; }
+  *maxc_out = maxc;
+  const u64 total = nb_off[np];
+  nb_list.assign(std::max<u64>(total, 1), 0);
+  if (total) {
+    N_CUDA(cudaMalloc(&d_off, (np + 1) * 8));
+    N_CUDA(cudaMalloc(&d_list, total * 4));
+    N_CUDA(cudaMemcpyAsync(d_off, nb_off.data(), (np + 1) * 8, cudaMemcpyHostToDevice, s));
+    nbhd_fill_kernel<<<gw, tb, 0, s>>>(d_pairs, np, W, d_und, d_dbl, d_off, d_list);
+    ctx->launches++;
+    N_CUDA(cudaGetLastError());
+    N_CUDA(cudaMemcpyAsync(nb_list.data(), d_list, total * 4, cudaMemcpyDeviceToHost, s));
+    N_CUDA(cudaStreamSynchronize(s));
+  }
+#undef N_CUDA
+  cleanup();
+  return FCM_OK;
+}
+
+// State::compute_edge_neighborhoods (src/lib.rs:331-356) as a call of its own (src/bin/edgeset_nbhd.rs
+// prints these lists): pairs in order of first appearance in the edge list, key [big, small].
+extern "C" int fcm_edge_neighborhoods(fcm_ctx* ctx, uint32_t n, uint64_t nedges, const uint32_t (*edges)[2],
+                                      uint64_t* npairs_out, uint64_t* list_len_out, uint32_t* pairs_out,
+                                      uint64_t* off_out, uint32_t* list_out) {
+  REQUIRE(ctx && npairs_out && list_len_out, "ctx/npairs_out/list_len_out is null");
+  REQUIRE(nedges == 0 || edges, "edges is null");
+  FCM_CUDA(cudaSetDevice(ctx->device));
+  std::vector<uint2> pair_ab, double_pairs;
+  std::unordered_map<u64, u32> seen;                 // pair -> directions met (bit 0: big -> small, bit 1: small -> big)
+  seen.reserve(nedges * 2);
+  for (u64 i = 0; i < nedges; i++) {
+    const u32 a = edges[i][0], b = edges[i][1];
+    if (a >= n || b >= n || a == b) { fcm_set_error("edge %llu = (%u,%u): vertex id >= n or self loop", (unsigned long long)i, a, b); return FCM_EINVAL; }
+    const u32 big = std::max(a, b), small = std::min(a, b), dir = a > b ? 1u : 2u;
+    auto ins = seen.emplace(pkey(big, small), dir);
+    if (ins.second) pair_ab.push_back(make_uint2(big, small));
+    else if ((ins.first->second | dir) == 3u && ins.first->second != 3u) { ins.first->second = 3u; double_pairs.push_back(make_uint2(big, small)); }
+  }
+  std::vector<u64> off; std::vector<u32> list; u32 maxc = 0;
+  int rc = edge_neighborhoods_device(ctx, n, pair_ab, off, list, &maxc, &double_pairs);
+  if (rc) return rc;
+  *npairs_out = pair_ab.size();
+  *list_len_out = off[pair_ab.size()];
+  if (pairs_out) memcpy(pairs_out, pair_ab.data(), pair_ab.size() * 8);
+  if (off_out) memcpy(off_out, off.data(), off.size() * 8);
+  if (list_out && off[pair_ab.size()]) memcpy(list_out, list.data(), off[pair_ab.size()] * 4);
+  return FCM_OK;
+}
+
 extern "C" int fcm_ensemble_destroy(fcm_ensemble* e) {
   if (!e) return FCM_OK;
   if (e->ctx) { cudaSetDevice(e->ctx->device); cudaStreamSynchronize(e->ctx->stream); }
@@ -219,29 +368,10 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     for (int t = 0; t < nthreads; t++) th.emplace_back([&, t]() { for (u32 v = t; v < n; v += nthreads) std::sort(und[v].begin(), und[v].end()); });
     for (auto& t : th) t.join();
   }
-  std::vector<u64> nb_off(p.npairs + 1, 0);   // 64-bit while summing; uploaded as u32
-  auto intersect = [&](u32 a, u32 b, u32* outp) -> u32 {
-    const std::vector<u32>&A = und[a], &B = und[b];
-    size_t i = 0, j = 0; u32 c = 0;
-    while (i < A.size() && j < B.size()) {
-      if (A[i] == B[j]) { if (outp) outp[c] = A[i]; c++; i++; j++; }
-      else if (A[i] < B[j]) i++; else j++;
-    }
-    return c;
-  };
-  {
-    std::vector<std::thread> th;
-    for (int t = 0; t < nthreads; t++) th.emplace_back([&, t]() { for (u64 q = t; q < p.npairs; q += nthreads) nb_off[q + 1] = intersect(pair_ab[q].x, pair_ab[q].y, nullptr); });
-    for (auto& t : th) t.join();
-  }
+  std::vector<u64> nb_off;                    // 64-bit while summing; uploaded as u32
+  std::vector<u32> nb_list;
   u32 maxc = 0;
-  for (u64 q = 0; q < p.npairs; q++) { maxc = std::max<u32>(maxc, (u32)nb_off[q + 1]); nb_off[q + 1] += nb_off[q]; }
-  std::vector<u32> nb_list(std::max<u64>(nb_off[p.npairs], 1));
-  {
-    std::vector<std::thread> th;
-    for (int t = 0; t < nthreads; t++) th.emplace_back([&, t]() { for (u64 q = t; q < p.npairs; q += nthreads) intersect(pair_ab[q].x, pair_ab[q].y, &nb_list[nb_off[q]]); });
-    for (auto& t : th) t.join();
-  }
+  if ((rc = edge_neighborhoods_device(ctx, n, pair_ab, nb_off, nb_list, &maxc))) return fail(rc);
   p.maxc = maxc;
 
   // ---- static clique index (hot path of chain_step_kernel): for every pair the slots of the edges

@@ -257,6 +257,20 @@ def for_each_cell(n, edges, f, dim_min, dim_max, ctx=None):
             ctx.close()
 
 
+def compute_edge_neighborhoods(ctx, n, edges):
+    """State::compute_edge_neighborhoods (src/lib.rs:331-356) on the GPU -> {(big, small): [common
+    undirected neighbours, ascending]} in order of first appearance of the pair."""
+    e = edges_array(edges)
+    npairs, ll = C.c_uint64(), C.c_uint64()
+    check(lib().fcm_edge_neighborhoods(ctx.h, int(n), int(e.shape[0]), ptr(e), C.byref(npairs), C.byref(ll), None, None, None))
+    pairs = np.zeros((npairs.value, 2), dtype=np.uint32)
+    off = np.zeros(npairs.value + 1, dtype=np.uint64)
+    lst = np.zeros(max(ll.value, 1), dtype=np.uint32)
+    check(lib().fcm_edge_neighborhoods(ctx.h, int(n), int(e.shape[0]), ptr(e), C.byref(npairs), C.byref(ll),
+                                       ptr(pairs), ptr(off), ptr(lst)))
+    return {(int(a), int(b)): [int(x) for x in lst[int(off[q]):int(off[q + 1])]] for q, (a, b) in enumerate(pairs)}
+
+
 def undirected_edges(edges):
     """[a,b] with a > b once per adjacent pair (src/lib.rs:344 asserts a > b)."""
     e = edges_array(edges)

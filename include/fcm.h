@@ -111,6 +111,17 @@ int fcm_graph_set_kernel(fcm_graph* g, int kind);
 int fcm_graph_info(const fcm_graph* g, uint32_t* n, uint64_t* nedges, uint32_t* words_per_row,
                    uint32_t* max_out_degree);
 
+/* State::compute_edge_neighborhoods (src/lib.rs:331-356; printed by src/bin/edgeset_nbhd.rs): for every
+ * adjacent pair, key [big, small], the ascending common undirected neighbours - computed on the
+ * device (bit-row AND + compaction).  Pairs come in order of first appearance in the edge list.
+ * As in the reference, whose adjacency lists are built from the directed edges without deduplication
+ * (src/lib.rs:333-336), a neighbour joined to BOTH endpoints by double edges is listed twice.
+ * Call with the three buffers NULL to get *npairs and *list_len, then with pairs_out[2*npairs],
+ * off_out[npairs+1] (exclusive prefix), list_out[list_len]. */
+int fcm_edge_neighborhoods(fcm_ctx* ctx, uint32_t n, uint64_t nedges, const uint32_t (*edges)[2],
+                           uint64_t* npairs, uint64_t* list_len, uint32_t* pairs_out,
+                           uint64_t* off_out, uint32_t* list_out);
+
 /* ------------------------------------------------------------------------------------------------
  * 4. Ensemble of independent chains on one device: MCMCSampler (src/lib.rs:164-198), one warp per
  *    chain.  All chains start from the same graph (edge order = insertion order of the edge list,

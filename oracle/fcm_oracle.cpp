@@ -977,4 +977,24 @@ u64 orc_cells(u32 n, u64 ne, const u32* edges, int dmin, int dmax, u32* out, u64
   return cnt;
 }
 
+// State::compute_edge_neighborhoods (src/lib.rs:331-356) for a graph: pairs [big, small] sorted, CSR lists.
+// pairs_out[2*npairs], off_out[npairs+1], list_out[total] (any may be null) -> npairs; *total_out = list length
+u64 orc_edge_neighborhoods(u32 n, u64 ne, const u32* edges, u32* pairs_out, u64* off_out, u32* list_out, u64* total_out) {
+  Graph g = graph_from(n, ne, edges);
+  auto m = State::compute_edge_neighborhoods(g);
+  std::vector<u64> keys;
+  for (auto& kv : m) keys.push_back(kv.first);
+  std::sort(keys.begin(), keys.end());
+  u64 tot = 0;
+  for (size_t q = 0; q < keys.size(); q++) {
+    const auto& l = m[keys[q]];
+    if (pairs_out) { pairs_out[2 * q] = (u32)(keys[q] >> 32); pairs_out[2 * q + 1] = (u32)keys[q]; }
+    if (off_out) off_out[q] = tot;
+    for (Node v : l) { if (list_out) list_out[tot] = v; tot++; }
+  }
+  if (off_out) off_out[keys.size()] = tot;
+  if (total_out) *total_out = tot;
+  return keys.size();
+}
+
 }  // extern "C"

@@ -72,6 +72,8 @@ def lib():
     L.orc_edgebits_save.restype = None
     L.orc_cells.argtypes = [u32, u64, vp, i32, i32, vp, u64]
     L.orc_cells.restype = u64
+    L.orc_edge_neighborhoods.argtypes = [u32, u64, vp, vp, vp, vp, P(u64)]
+    L.orc_edge_neighborhoods.restype = u64
     _lib = L
     return L
 
@@ -143,6 +145,18 @@ def cells(n, edges, dmin, dmax):
     out = np.zeros((cnt, dmax + 1), dtype=np.uint32)
     lib().orc_cells(int(n), e.shape[0], _p(e), int(dmin), int(dmax), _p(out), cnt)
     return out
+
+
+def edge_neighborhoods(n, edges):
+    """compute_edge_neighborhoods -> {(big, small): [common undirected neighbours]}"""
+    e = _e(edges)
+    tot = C.c_uint64()
+    npairs = lib().orc_edge_neighborhoods(int(n), e.shape[0], _p(e), None, None, None, C.byref(tot))
+    pairs = np.zeros((npairs, 2), dtype=np.uint32)
+    off = np.zeros(npairs + 1, dtype=np.uint64)
+    lst = np.zeros(max(tot.value, 1), dtype=np.uint32)
+    lib().orc_edge_neighborhoods(int(n), e.shape[0], _p(e), _p(pairs), _p(off), _p(lst), C.byref(tot))
+    return {(int(a), int(b)): [int(x) for x in lst[int(off[q]):int(off[q + 1])]] for q, (a, b) in enumerate(pairs)}
 
 
 def read_flag_file(path):

@@ -168,3 +168,21 @@ def test_for_each_cell_local_subgraph_like_all_cxs(ctx):
     want = sorted(tuple(sorted(int(x) for x in r)) for r in orc.cells(24, e, 2, 2))
     assert got == want and len(got) == g.flagser_count()[2]
     g.close()
+
+
+@pytest.mark.parametrize("name", ["counterexample_any_order", "c2_chunglu_279", "counterexample_seo_greedy_5_start", "c3_er_2000"])
+def test_edge_neighborhoods_match_oracle(name, ctx, graphs):
+    # State::compute_edge_neighborhoods (src/lib.rs:331-356): same keys [big, small], same sorted lists
+    n, e = graphs[name]
+    got = ds.compute_edge_neighborhoods(ctx, n, e)
+    want = orc.edge_neighborhoods(n, e)
+    assert got == want
+    # order of the device result: first appearance of the pair in the edge list
+    first = []
+    seen = set()
+    for a, b in e.tolist():
+        k = (max(a, b), min(a, b))
+        if k not in seen:
+            seen.add(k)
+            first.append(k)
+    assert list(got.keys()) == first

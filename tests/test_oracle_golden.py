@@ -224,3 +224,9 @@ def test_cells_oracle_counts_and_order(graphs, expected):
     assert as_tuples == sorted(as_tuples)                 # a prefix sorts before its extensions
     e3 = np.array([[0, 1], [1, 2], [0, 2]], dtype=np.uint32)
     assert orc.cells(3, e3, 1, 2).tolist() == [[0, 1, 0xFFFFFFFF], [0, 1, 2], [0, 2, 0xFFFFFFFF], [1, 2, 0xFFFFFFFF]]
+
+
+def test_edge_neighborhoods_oracle_toy():
+    # triangle 0-1-2 plus pendant 3-2: the pair (1,0) has the common neighbour 2, (3,2) has none
+    e = np.array([[0, 1], [1, 2], [2, 0], [3, 2]], dtype=np.uint32)
+    assert orc.edge_neighborhoods(4, e) == {(1, 0): [2], (2, 0): [1], (2, 1): [0], (3, 2): []}
