@@ -61,6 +61,12 @@ extern "C" int fcm_ctx_create(int device, fcm_ctx** out) {
   FCM_CUDA(cudaGetDeviceProperties(&prop, device));
   c->sm_count = prop.multiProcessorCount;
   c->smem_optin = prop.sharedMemPerBlockOptin;
+  {
+    cudaMemPool_t pool;
+    FCM_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+    unsigned long long keep = ~0ULL;                    // freed graph memory stays in the pool for the next graph
+    FCM_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+  }
   FCM_CUDA(cudaStreamCreateWithFlags(&c->own, cudaStreamNonBlocking));
   c->stream = c->own;
   FCM_CUDA(cudaEventCreate(&c->ev0));
@@ -121,16 +127,16 @@ static int graph_create(fcm_ctx* c, u32 n, u64 ne, const uint32_t (*edges)[2], i
   int rc = FCM_OK;
   uint2* edges_dev = nullptr;
   std::vector<u64> off;
-  auto fail = [&](int code) { if (edges_dev) cudaFree(edges_dev); fcm_graph_destroy(g); return code; };
+  auto fail = [&](int code) { fcm_pool_free(edges_dev, c->stream); fcm_graph_destroy(g); return code; };
 #define G_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { fcm_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); return fail(FCM_ECUDA); } } while (0)
-  G_CUDA(cudaMalloc(&g->adj, std::max<size_t>((size_t)n * g->W, 2) * 8));
-  G_CUDA(cudaMalloc(&g->csr_off, ((size_t)n + 1) * 8));
-  G_CUDA(cudaMalloc(&g->order, std::max<u32>(n, 1) * 4));
-  G_CUDA(cudaMalloc(&g->overflow, std::max<u32>(n, 1) * 4));
-  G_CUDA(cudaMalloc(&g->counts, FCM_MAXD * 8));
-  G_CUDA(cudaMalloc(&g->ctrl, CT_WORDS * 4));
+  G_CUDA(fcm_pool_alloc(&g->adj, std::max<size_t>((size_t)n * g->W, 2) * 8, c->stream));
+  G_CUDA(fcm_pool_alloc(&g->csr_off, ((size_t)n + 1) * 8, c->stream));
+  G_CUDA(fcm_pool_alloc(&g->order, std::max<u32>(n, 1) * 4, c->stream));
+  G_CUDA(fcm_pool_alloc(&g->overflow, std::max<u32>(n, 1) * 4, c->stream));
+  G_CUDA(fcm_pool_alloc(&g->counts, FCM_MAXD * 8, c->stream));
+  G_CUDA(fcm_pool_alloc(&g->ctrl, CT_WORDS * 4, c->stream));
   if (ne) {
-    G_CUDA(cudaMalloc(&edges_dev, ne * 8));
+    G_CUDA(fcm_pool_alloc(&edges_dev, ne * 8, c->stream));
     G_CUDA(cudaMemcpyAsync(edges_dev, edges, ne * 8, cudaMemcpyHostToDevice, c->stream));
   }
   rc = fcm_graph_build_device(g, edges_dev, ne, normalise, off);
@@ -142,7 +148,7 @@ static int graph_create(fcm_ctx* c, u32 n, u64 ne, const uint32_t (*edges)[2], i
   std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) { return off[a + 1] - off[a] > off[b + 1] - off[b]; });
   if (n) G_CUDA(cudaMemcpyAsync(g->order, order.data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
   G_CUDA(cudaStreamSynchronize(c->stream));
-  if (edges_dev) cudaFree(edges_dev);
+  fcm_pool_free(edges_dev, c->stream);
 #undef G_CUDA
   *out = g;
   return FCM_OK;
@@ -156,8 +162,9 @@ extern "C" int fcm_graph_create_normalised(fcm_ctx* c, uint32_t n, uint64_t ne, 
 extern "C" int fcm_graph_destroy(fcm_graph* g) {
   if (!g) return FCM_OK;
   if (g->ctx) cudaSetDevice(g->ctx->device);
-  cudaFree(g->adj); cudaFree(g->csr_off); cudaFree(g->csr); cudaFree(g->order);
-  cudaFree(g->overflow); cudaFree(g->counts); cudaFree(g->ctrl); cudaFree(g->scratch);
+  cudaStream_t s = g->ctx ? g->ctx->stream : nullptr;
+  fcm_pool_free(g->adj, s); fcm_pool_free(g->csr_off, s); fcm_pool_free(g->csr, s); fcm_pool_free(g->order, s);
+  fcm_pool_free(g->overflow, s); fcm_pool_free(g->counts, s); fcm_pool_free(g->ctrl, s); fcm_pool_free(g->scratch, s);
   delete g;
   return FCM_OK;
 }

@@ -100,7 +100,7 @@ int fcm_graph_build_device(fcm_graph* g, const uint2* edges_dev, u64 ne_in, int 
   g->maxout = maxout;
   g->ne = off_host[g->n];
   FCM_CUDA(cudaMemcpyAsync(g->csr_off, off_host.data(), (g->n + 1) * 8, cudaMemcpyHostToDevice, s));
-  FCM_CUDA(cudaMalloc(&g->csr, std::max<u64>(g->ne, 1) * 4));
+  FCM_CUDA(fcm_pool_alloc(&g->csr, std::max<u64>(g->ne, 1) * 4, s));
   if (g->n) {
     int blocks = (g->n * 32 + 255) / 256;
     row_to_csr_kernel<<<blocks, 256, 0, s>>>(g->adj, g->n, g->W, g->csr_off, g->csr);
@@ -543,9 +543,9 @@ static int launch_dense(fcm_graph* g, const u32* tasks, u32 ntasks_total, u32 pa
   u32 blocks = (u32)c->sm_count * 4;
   size_t need = (size_t)blocks * DENSE_WARPS * MAXL_DENSE * g->W;
   if (need > g->scratch_words) {
-    if (g->scratch) FCM_CUDA(cudaFree(g->scratch));
+    fcm_pool_free(g->scratch, c->stream);
     g->scratch = nullptr; g->scratch_words = 0;
-    FCM_CUDA(cudaMalloc(&g->scratch, need * 8));
+    FCM_CUDA(fcm_pool_alloc(&g->scratch, need * 8, c->stream));
     g->scratch_words = need;
   }
   count_dense_kernel<<<blocks, DENSE_WARPS * 32, 0, c->stream>>>(g->adj, tasks, ntasks_total, part, nparts,

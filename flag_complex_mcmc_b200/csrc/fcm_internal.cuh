@@ -50,6 +50,13 @@ struct fcm_graph {
   int kernel_kind = 0;
 };
 
+// Device memory of graphs comes from the device's stream-ordered pool (its release threshold is
+// raised at fcm_ctx_create, so the memory of a destroyed graph serves the next one: flagser_count is
+// called over and over on small graphs by the research binaries, src/bin/all_cxs.rs:57-83).
+template <typename T>
+static inline cudaError_t fcm_pool_alloc(T** p, size_t bytes, cudaStream_t s) { return cudaMallocAsync((void**)p, bytes, s); }
+static inline void fcm_pool_free(void* p, cudaStream_t s) { if (p) cudaFreeAsync(p, s); }
+
 // device control words
 enum { CT_TICKET = 0, CT_NOVER = 1, CT_ERR = 2, CT_TICKET2 = 3, CT_WORDS = 8 };
 
