@@ -395,11 +395,14 @@ def main():
             g.count_shard(rank, ngpu)
         barrier()
         l0 = ctx.launches
+        rclk = Clocks(local)
+        rclk.start()
         ctx.timer_begin()
-        for _ in range(args.steps):
+        for _ in range(max(args.steps, 50)):                   # >= 50 counts: long enough for the clock sampler
             g.count_async(rank, ngpu)
-        rms = ctx.timer_end()
-        rl = ctx.launches - l0
+        rms = ctx.timer_end() * args.steps / max(args.steps, 50)
+        rl = (ctx.launches - l0) * args.steps // max(args.steps, 50)
+        rclocks = rclk.stop()
         barrier()
         part = g.count_shard(rank, ngpu)
         tot = torch.from_numpy(part.astype(np.int64)).cuda()
@@ -421,7 +424,7 @@ def main():
         line["recount"] = {
             "metric": "full_recount_simplices_per_sec", "value": rvalue, "unit": "simplices/s", "graph": args.recount_graph,
             "n": n4, "nedges": int(e4.shape[0]), "flag_count": counts, "simplices": simplices, "ms_per_count": rms_max / max(args.steps, 1),
-            "gpu_launches": int(rl), "sharding": "source vertices, degree-descending round-robin over %d rank(s) + allreduce(sum) of uint64[32]" % ngpu,
+            "gpu_launches": int(rl), "clocks": rclocks, "sharding": "source vertices, degree-descending round-robin over %d rank(s) + allreduce(sum) of uint64[32]" % ngpu,
             "e2e": {"value": simplices / re2e if rank == 0 else None, "unit": "simplices/s", "h2d_bytes_per_step": int(e4.nbytes),
                     "d2h_bytes_per_step": 8 * len(counts), "what": "fcm_count_unweighted(host edge list) on one GPU: upload, build bit rows + CSR, count, download"},
             "roofline": {"bound": "hbm", "kernel": "count_local_kernel", "achieved": rbytes * args.steps / (rms_max * 1e-3) / 1e9 / ngpu,

@@ -20,7 +20,6 @@
 #include "fcm_internal.cuh"
 
 #include <algorithm>
-#include <cstdlib>
 
 #define DENSE_WARPS 4
 #define MAXL_DENSE (FCM_MAXD - 1)   // level l holds candidates for vertex index l+1
@@ -134,7 +133,7 @@ template <int WK> struct LocalCfg {
   static constexpr int MAXIDS = 6;                                 // ids per stack entry (10 bits each + depth)
   static constexpr int BPL = 2 * WK;                               // bits of a row each lane extracts (32 lanes x BPL = 64*WK)
 };
-__host__ __device__ constexpr u32 stack_cap(u32 kcap) { return kcap + 64; }   // entries per warp (>= kcap + 32; a full stack falls back to deep_count)
+__host__ __device__ constexpr u32 stack_cap(u32 kcap) { return kcap + 128; }   // entries per warp (>= kcap + 32; a full stack falls back to deep_count)
 
 // P = candidates for the vertex of index `lvl` (non-empty, already counted).  Generic levels: explicit
 // stack in local memory, counts through shared atomics (rare: dimension > REG_LEVELS + 2).
@@ -194,7 +193,7 @@ __global__ void __launch_bounds__(LocalCfg<WK>::THREADS, LocalCfg<WK>::MINBLOCKS
 count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
                    const u32* __restrict__ csr, const u32* __restrict__ order, u32 W, u32 nv_total,
                    u32 part, u32 nparts, u32 kcap, u32* __restrict__ ctrl,
-                   u32* __restrict__ overflow, u64* __restrict__ counts, const EmitArgs ea, const int csr_gather) {
+                   u32* __restrict__ overflow, u64* __restrict__ counts, const EmitArgs ea) {
   using Cfg = LocalCfg<WK>;
   constexpr int LS = Cfg::LS, NT = Cfg::THREADS, NW = NT / 32, BPL = Cfg::BPL, MAXIDS = Cfg::MAXIDS;
   constexpr int RL = MAXIDS - 1;                        // cnt[r]: flag_count index 3 + r (tuples of 2 + r ids)
@@ -240,48 +239,9 @@ count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
     if (k < 2) continue;                                // no 2-simplex possible
     for (u32 i = tid; i < k; i += NT) verts[i] = csr[o0 + i];
     __syncthreads();
-    // ---- gather the k x k induced adjacency ----
-    if (csr_gather) {
-      // through the out-LISTS: row i = { rank of u in out(v0) : u in out(v_i) and u in out(v0) }.  out(v0) is
-      // staged as a bitmap (the adjacency row of v0) with per-word prefix counts, so that membership and
-      // rank are two shared-memory reads; the lists are read coalesced (4 B per candidate instead of a
-      // 32-byte sector per probed bit: a quarter of the L2 traffic of the probe gather below).
-      u64* row0 = (u64*)(stacks + (size_t)NW * scap);
-      u32* pre = (u32*)(row0 + W);
-      u32* L32 = (u32*)L;
-      for (u32 w = tid; w < W; w += NT) row0[w] = __ldg(&adj[(u64)v0 * W + w]);
-      for (u32 i = tid; i < k * (2 * LS); i += NT) L32[i] = 0;
-      __syncthreads();
-      if (warp == 0) {                                  // exclusive prefix of the word popcounts
-        u32 base = 0;
-        for (u32 w0 = 0; w0 < W; w0 += 32) {
-          const u32 w = w0 + lane;
-          const u32 c = w < W ? __popcll(row0[w]) : 0u;
-          u32 incl = c;
-#pragma unroll
-          for (int d = 1; d < 32; d <<= 1) { const u32 tt = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += tt; }
-          if (w < W) pre[w] = base + incl - c;
-          base += __shfl_sync(0xffffffffu, incl, 31);
-        }
-      }
-      __syncthreads();
-      for (u32 i = warp; i < k; i += NW) {
-        const u32 vi = verts[i];
-        const u64 oi = __ldg(&csr_off[vi]);
-        const u32 di = (u32)(__ldg(&csr_off[vi + 1]) - oi);
-        u32* dst = L32 + (size_t)i * (2 * LS);
-        for (u32 t = lane; t < di; t += 32) {
-          const u32 u = __ldg(&csr[oi + t]);
-          const u64 wv = row0[u >> 6];
-          if ((wv >> (u & 63)) & 1ULL) {
-            const u32 j = pre[u >> 6] + __popcll(wv & ((1ULL << (u & 63)) - 1ULL));
-            atomicOr(&dst[j >> 5], 1u << (j & 31));
-          }
-        }
-      }
-    } else {
-      // by probing: tasks = (32 rows) x (32 columns); a lane owns a column, the loads of 8 rows are in
-      // flight together, lane r keeps the ballot of row r (graphs whose rows do not fit shared memory)
+    // ---- gather the k x k induced adjacency.  Tasks = (32 rows) x (32 columns); a lane owns a column,
+    //      the loads of 8 rows are in flight together, lane r keeps the ballot of row r ----
+    {
       u32* L32 = (u32*)L;
       const u32 nch = (k + 31) >> 5;
       for (u32 task = warp; task < nch * nch; task += NW) {
@@ -519,9 +479,6 @@ static int launch_local(fcm_graph* g, u32 part, u32 nparts, u32 kcap, const Emit
   constexpr int LS = LocalCfg<WK>::LS;
   constexpr int LOCAL_THREADS = LocalCfg<WK>::THREADS;
   size_t smem = (size_t)kcap * LS * 8 + (size_t)(kcap + (kcap & 1)) * 4 + (size_t)(LOCAL_THREADS / 32) * stack_cap(kcap) * 8;
-  // the list gather stages the adjacency row of the source vertex (bitmap + prefix counts: 12 B per word)
-  const int csr_gather = (size_t)g->W * 12 <= 16 * 1024 && !getenv("FCM_PROBE_GATHER");
-  if (csr_gather) smem += (size_t)g->W * 12;
   auto kern = count_local_kernel<WK, EMIT>;
   FCM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
@@ -530,7 +487,7 @@ static int launch_local(fcm_graph* g, u32 part, u32 nparts, u32 kcap, const Emit
   u32 ntasks = g->n > part ? (g->n - part + nparts - 1) / nparts : 0;
   u32 blocks = (u32)std::min<u64>((u64)c->sm_count * per_sm, std::max<u32>(ntasks, 1));
   kern<<<blocks, LOCAL_THREADS, smem, c->stream>>>(g->adj, g->csr_off, g->csr, g->order, g->W, g->n,
-                                                   part, nparts, kcap, g->ctrl, g->overflow, g->counts, ea, csr_gather);
+                                                   part, nparts, kcap, g->ctrl, g->overflow, g->counts, ea);
   c->launches++;
   FCM_CUDA(cudaGetLastError());
   return FCM_OK;
