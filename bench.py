@@ -71,6 +71,31 @@ class Clocks:
         self.p = None
 
     def start(self):
+        # NVML in a thread (a sample every 5 ms: the timed region can be ~100 ms); nvidia-smi -lms as the fallback
+        self.rows, self.halt, self.t = [], threading.Event(), None
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            mx = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            bits = [nv.nvmlClocksThrottleReasonHwSlowdown, nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                    nv.nvmlClocksThrottleReasonSwThermalSlowdown, nv.nvmlClocksThrottleReasonSwPowerCap]
+
+            def loop():
+                while True:
+                    try:
+                        r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                        self.rows.append([str(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))), str(mx)] +
+                                         ["Active" if r & b else "Not Active" for b in bits])
+                    except Exception:
+                        pass
+                    if self.halt.wait(0.005):
+                        return
+            self.t = threading.Thread(target=loop, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.t = None
         try:
             self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
@@ -81,30 +106,37 @@ class Clocks:
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
-        if not self.p:
-            return out
-        try:
-            self.p.terminate()
-            self.p.wait(timeout=5)
-        except Exception:
-            pass
-        try:
-            self.f.flush()
-            self.f.seek(0)
-            rows = [ln.strip().split(",") for ln in self.f.read().splitlines() if ln.strip()]
-            sm = sorted(float(r[0]) for r in rows if len(r) >= 6)
-            if sm:
-                out["sm_mhz"] = sm[len(sm) // 2]
-                out["sm_max_mhz"] = float(rows[0][1])
-                names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-                for i, nm in enumerate(names):
-                    if any(r[2 + i].strip().lower().startswith("active") for r in rows if len(r) >= 6):
-                        out["reasons"].append(nm)
-                out["samples"] = len(sm)
-            self.f.close()
-            os.unlink(self.f.name)
-        except Exception:
-            pass
+        rows = []
+        if getattr(self, "t", None):
+            self.halt.set()
+            self.t.join(timeout=5)
+            rows = list(self.rows)
+            out["source"] = "nvml"
+        elif self.p:
+            try:
+                self.p.terminate()
+                self.p.wait(timeout=5)
+            except Exception:
+                pass
+            try:
+                self.f.flush()
+                self.f.seek(0)
+                rows = [ln.strip().split(",") for ln in self.f.read().splitlines() if ln.strip()]
+                self.f.close()
+                os.unlink(self.f.name)
+            except Exception:
+                pass
+            out["source"] = "nvidia-smi"
+        rows = [r for r in rows if len(r) >= 6]
+        sm = sorted(float(r[0]) for r in rows)
+        if sm:
+            out["sm_mhz"] = sm[len(sm) // 2]
+            out["sm_max_mhz"] = float(rows[0][1])
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            for i, nm in enumerate(names):
+                if any(r[2 + i].strip().lower().startswith("active") for r in rows):
+                    out["reasons"].append(nm)
+            out["samples"] = len(sm)
         return out
 
 

@@ -278,8 +278,8 @@ __device__ int local_count_any(const u64* M, int K, int KW, int lane, u64* out, 
 enum { FL_DEEP = 0, FL_TOP = 1, FL_ERR = 2, FL_RC = 3, FL_K = 4, FL_LEN = 5, FL_OVF = 6, FL_E = 8, FL_ND = 9, FL_ACC = 10, FL_FCLEN = 11 };
 enum { PK_KIND = 0, PK_SLOT, PK_DELME, PK_IDX, PK_DIDX, PK_DPAIR, PK_LAST, PK_QPOS, PK_TA, PK_TB, PK_TDM0, PK_TDM1,
        PK_CA, PK_CD, PK_OA, PK_OD, PK_ORIA, PK_ORID };
-#define CQ_MAXPAIRS 192                 // entries of new_edges / old_edges in clique_swap (src/lib.rs:256-270): two disjoint 9-cliques; 28 warps of 7.8 KB fit one SM
-#define CQ_BYTES (3 * FCM_MAXCQ * 4 + 2 * CQ_MAXPAIRS * 8 + 64)
+#define CQ_SCRATCH 160                  // u32 words behind the header: clique_swap's rank / row tables (128) + perm_a while it is drawn (32)
+#define CQ_BYTES (3 * FCM_MAXCQ * 4 + 64 + CQ_SCRATCH * 4)
 struct WarpSmem {
   u64 *M, *fc, *pre, *post;
   u32 *verts, *edits, *cq;
@@ -829,9 +829,9 @@ __device__ __forceinline__ void update_adjacency(const EnsParams& p, u32* cb, u3
 
 // ---------------------------------------------------------------------------------------------------
 // clique moves: Transition::clique_permute / clique_swap (src/lib.rs:214-290).  Cold path: lane 0
-// builds the transition in shared memory (the draws, util::random_perm, vec_intersect / vec_setminus,
-// the sort / dedup / contains logic of clique_swap), the warp gathers the has_edge bits it needs and
-// then runs the reference's literal apply_transition: full pre/post counts of the union neighbourhood.
+// makes the draws (util::random_perm, vec_intersect / vec_setminus), the warp gathers the has_edge bits
+// of d x d, builds the edit list in the reference's push order (lane i = row i) and counts the edits
+// one after the other as single-edge deltas.
 // ---------------------------------------------------------------------------------------------------
 // rand 0.8 UniformInt<u32>::sample_single(0, range) as used by seq::gen_index (choose / shuffle):
 // next_u32 = upper half of next_u64 (rand_xoshiro 0.6), 32 x 32 widening multiply, rejection zone
@@ -846,7 +846,9 @@ __device__ __forceinline__ u32 gen_range_u32(Rng& g, u32 range) {
 // util::random_perm(l, h) (src/util.rs:28-32): out[0..h-l) = shuffle of l..h
 __device__ void random_perm_dev(Rng& g, u32 l, u32 h, u32* out) {
   const u32 len = h - l;
+#pragma unroll 1
   for (u32 i = 0; i < len; i++) out[i] = l + i;
+#pragma unroll 1
   for (u32 i = len; i-- > 1;) {
     const u32 j = gen_range_u32(g, i + 1);
     const u32 t = out[i]; out[i] = out[j]; out[j] = t;
@@ -859,12 +861,6 @@ __device__ u32 find_pair(const EnsParams& p, u32 a, u32 b) {
   while (lo < hi) { const u64 mid = (lo + hi) >> 1; if (__ldg(&p.pkeys[mid]) < key) lo = mid + 1; else hi = mid; }
   if (lo < p.npairs && __ldg(&p.pkeys[lo]) == key) return __ldg(&p.pkey_pair[lo]);
   return FCM_NONE;
-}
-__device__ void sort_dedup_u64(u64* a, int& n) {       // lane 0, short lists: insertion sort + unique
-  for (int i = 1; i < n; i++) { const u64 x = a[i]; int j = i; while (j > 0 && a[j - 1] > x) { a[j] = a[j - 1]; j--; } a[j] = x; }
-  int m = 0;
-  for (int i = 0; i < n; i++) if (i == 0 || a[i] != a[m - 1]) a[m++] = a[i];
-  n = m;
 }
 
 // kind 2 = clique_permute, 3 = clique_swap.  The chain's RNG state (after the move-kind draw) and all
@@ -880,8 +876,7 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
   u32* const perm = s.cq + FCM_MAXCQ;                   // perm_d (swap) / perm (permute)
   u32* const H = s.cq + 2 * FCM_MAXCQ;                  // H[i] bit j = has_edge(d[i], d[j])
   u32* const hdr = s.cq + 3 * FCM_MAXCQ;                // [0] n_d [1] n_c [2] n_a [3] status [4] i1 [5] i2 [6] ord [7] nedit
-  u64* const newe = (u64*)(hdr + 16);
-  u64* const olde = newe + CQ_MAXPAIRS;
+  u32* const R = hdr + 16;                              // clique_swap: [0,32) rank of d[i], [32,64) index in d of a rank, [64,96) new rows, [96,128) old rows
   // ---- the draws and the vertex lists (lane 0) ----
   if (lane == 0) {
     Rng g; g.s0 = st->rng[0]; g.s1 = st->rng[1]; g.s2 = st->rng[2]; g.s3 = st->rng[3];
@@ -899,6 +894,7 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
       if (k > FCM_MAXCQ) status = FCM_ELIMIT;
       else {
         const u32* cl = p.cq_verts + p.cq_base[ord] + (u64)i1 * k;
+#pragma unroll 1
         for (u32 i = 0; i < k; i++) dv[i] = __ldg(&cl[i]);
         n_d = k; n_c = k;
         random_perm_dev(g, 0, k, perm);
@@ -912,20 +908,28 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
       else {
         // c = vec_intersect(m1, m2) in m1's order; d = c ++ (m1 - c) ++ (m2 - c)
         u32 inm2 = 0, inm1 = 0;                         // bit i: m1[i] is in m2 / m2[i] is in m1
-        for (u32 i = 0; i < k; i++)
+#pragma unroll 1
+        for (u32 i = 0; i < k; i++) {
+          const u32 x = __ldg(&m1[i]);
+#pragma unroll 1
           for (u32 j = 0; j < k; j++)
-            if (__ldg(&m1[i]) == __ldg(&m2[j])) { inm2 |= 1u << i; inm1 |= 1u << j; }
+            if (x == __ldg(&m2[j])) { inm2 |= 1u << i; inm1 |= 1u << j; }
+        }
         n_c = (u32)__popc(inm2); n_a = k - n_c;
         if (2 * k - n_c > FCM_MAXCQ) status = FCM_ELIMIT;
         else {
+#pragma unroll 1
           for (u32 i = 0; i < k; i++) if ((inm2 >> i) & 1u) dv[n_d++] = __ldg(&m1[i]);
+#pragma unroll 1
           for (u32 i = 0; i < k; i++) if (!((inm2 >> i) & 1u)) dv[n_d++] = __ldg(&m1[i]);
+#pragma unroll 1
           for (u32 i = 0; i < k; i++) if (!((inm1 >> i) & 1u)) dv[n_d++] = __ldg(&m2[i]);
           // perm_d = perm_c ++ perm_b ++ perm_a, drawn in the order c, a, b (src/lib.rs:247-251)
-          u32* const tmp = (u32*)olde;                  // free until the transition is built
+          u32* const tmp = R + 128;
           random_perm_dev(g, 0, n_c, perm);
           random_perm_dev(g, n_c, n_c + n_a, tmp);      // perm_a
           random_perm_dev(g, n_c + n_a, n_d, perm + n_c);   // perm_b sits right behind perm_c
+#pragma unroll 1
           for (u32 i = 0; i < n_a; i++) perm[n_c + (n_d - n_c - n_a) + i] = tmp[i];
         }
       }
@@ -948,46 +952,83 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
     }
   }
   __syncwarp();
-  // ---- the transition: change_edges as (from, to, add) in s.edits, then as (slot, add) ----
-  if (lane == 0) {
-    int ne = 0, status = 0;
+  // ---- the transition: change_edges as (from, to, add) in s.edits, then as (slot, add).  Lane i owns
+  //      row i of d; every lane writes its own edits at the position a warp prefix sum gives it, which
+  //      is the reference's push order ----
+  {
     u32* const ed = s.edits;                            // 2 words per edit: (from << 16 | to) indices into d, add
-    auto push = [&](u32 from, u32 to, u32 add) {
-      if (ne >= FCM_MAXEDIT) { status = FCM_ELIMIT; return; }
-      ed[2 * ne] = (from << 16) | to; ed[2 * ne + 1] = add; ne++;
-    };
+    u32 first = 0, second = 0, addbits = 0;             // this lane's edits: bits of `first`, then of `second`
+    u32 from = 0;
     if (kind == 2) {
-      for (int i = 0; i < n_d; i++)
-        for (int j = 0; j < n_d; j++) {
-          const u32 pre = (H[perm[i]] >> perm[j]) & 1u, post = (H[i] >> j) & 1u;
-          if (pre != post) push(perm[i], perm[j], post);
-        }
+      // clique_permute (src/lib.rs:214-232): for i, for j: perm[i] -> perm[j] takes the state of i -> j
+      if (lane < n_d) {
+        const u32 hp = H[perm[lane]];
+        u32 pre = 0;
+#pragma unroll 1
+        for (int j = 0; j < n_d; j++) pre |= ((hp >> perm[j]) & 1u) << j;
+        addbits = H[lane];
+        first = pre ^ addbits;
+        from = perm[lane];
+      }
     } else {
-      // new_edges / old_edges as keys (from vertex << 32 | to vertex): [Node;2] order = numeric order
-      int nn = 0, no = 0;
-      auto visit = [&](int i, int j) {
-        if (!((H[i] >> j) & 1u)) return;
-        if (nn >= CQ_MAXPAIRS) { status = FCM_ELIMIT; return; }
-        newe[nn++] = ((u64)dv[perm[i]] << 32) | dv[perm[j]];
-        olde[no++] = ((u64)dv[i] << 32) | dv[j];
-      };
-      for (int i = 0; i < n_c + n_a; i++) for (int j = 0; j < n_c + n_a; j++) visit(i, j);
-      for (int ii = 0; ii < n_d - n_a; ii++) {
-        const int i = ii < n_c ? ii : ii + n_a;
-        for (int jj = 0; jj < n_d - n_a; jj++) visit(i, jj < n_c ? jj : jj + n_a);
+      // clique_swap (src/lib.rs:234-290): new_edges / old_edges are sorted and deduplicated as [Node; 2],
+      // i.e. by (from, to) vertex ids: with vertices replaced by their rank among d both sets are 32 x 32
+      // bit matrices; the pushes are new \ old in key order (add), then old \ new in key order (remove)
+      u32 rk = 0;
+      if (lane < n_d) {
+        const u32 x = dv[lane];
+#pragma unroll 1
+        for (int j = 0; j < n_d; j++) rk += dv[j] < x;
+        R[lane] = rk; R[32 + rk] = (u32)lane;
       }
-      sort_dedup_u64(newe, nn);
-      sort_dedup_u64(olde, no);
-      auto local = [&](u32 vtx) { for (int i = 0; i < n_d; i++) if (dv[i] == vtx) return (u32)i; return 0u; };
-      for (int x = 0; x < nn && !status; x++) {
-        int at = -1;
-        for (int y = 0; y < no; y++) if (olde[y] == newe[x]) { at = y; break; }
-        if (at >= 0) { for (int y = at; y + 1 < no; y++) olde[y] = olde[y + 1]; no--; }
-        else push(local((u32)(newe[x] >> 32)), local((u32)newe[x]), 1u);
+      R[64 + lane] = 0; R[96 + lane] = 0;
+      __syncwarp();
+      if (lane < n_d) {
+        const int nca = n_c + n_a;
+        const u32 mCA = nca >= 32 ? ~0u : (1u << nca) - 1u, mC = n_c >= 32 ? ~0u : (1u << n_c) - 1u;
+        const u32 mAll = n_d >= 32 ? ~0u : (1u << n_d) - 1u, mCB = mC | (mAll & ~mCA);
+        u32 h = H[lane] & (lane < n_c ? mAll : lane < nca ? mCA : mCB);
+        u32 ow = 0, nw = 0;
+        while (h) {
+          const int j = __ffs((int)h) - 1;
+          h &= h - 1;
+          ow |= 1u << R[j];
+          nw |= 1u << R[perm[j]];
+        }
+        R[96 + rk] = ow;
+        R[64 + R[perm[lane]]] = nw;
       }
-      for (int y = 0; y < no && !status; y++) push(local((u32)(olde[y] >> 32)), local((u32)olde[y]), 0u);
+      __syncwarp();
+      const u32 nw = R[64 + lane], ow = R[96 + lane];   // lane = rank of the from vertex
+      first = nw & ~ow; second = ow & ~nw; addbits = first;
+      from = R[32 + lane];
     }
-    hdr[3] = (u32)status; hdr[7] = (u32)ne;
+    // positions: all `first` edits of the warp in lane order, then all `second` edits
+    const int c1 = __popc(first), c2 = __popc(second);
+    int p1 = c1, p2 = c2;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int a1 = __shfl_up_sync(FULL, p1, d), a2 = __shfl_up_sync(FULL, p2, d);
+      if (lane >= d) { p1 += a1; p2 += a2; }
+    }
+    const int n1 = __shfl_sync(FULL, p1, 31), n2 = __shfl_sync(FULL, p2, 31);
+    const int ne = n1 + n2;
+    if (ne <= FCM_MAXEDIT) {
+      int at = p1 - c1;
+      while (first) {
+        const int j = __ffs((int)first) - 1;
+        first &= first - 1;
+        const u32 to = kind == 2 ? perm[j] : R[32 + j];
+        ed[2 * at] = (from << 16) | to; ed[2 * at + 1] = (addbits >> j) & 1u; at++;
+      }
+      at = n1 + p2 - c2;
+      while (second) {
+        const int j = __ffs((int)second) - 1;
+        second &= second - 1;
+        ed[2 * at] = (from << 16) | R[32 + j]; ed[2 * at + 1] = 0u; at++;
+      }
+    }
+    if (lane == 0) { hdr[3] = ne <= FCM_MAXEDIT ? 0u : (u32)FCM_ELIMIT; hdr[7] = (u32)ne; }
   }
   __syncwarp();
   if (hdr[3]) { const int e = (int)hdr[3]; if (lane == 0) st->err = e; return e; }
