@@ -854,12 +854,15 @@ __device__ void random_perm_dev(Rng& g, u32 l, u32 h, u32* out) {
     const u32 t = out[i]; out[i] = out[j]; out[j] = t;
   }
 }
-// pair id of the adjacent pair {a, b} (binary search in the sorted keys) or FCM_NONE
+// pair id of the adjacent pair {a, b} or FCM_NONE: binary search among the keys of the bigger vertex
 __device__ u32 find_pair(const EnsParams& p, u32 a, u32 b) {
-  const u64 key = ((u64)max(a, b) << 32) | min(a, b);
-  u64 lo = 0, hi = p.npairs;
-  while (lo < hi) { const u64 mid = (lo + hi) >> 1; if (__ldg(&p.pkeys[mid]) < key) lo = mid + 1; else hi = mid; }
-  if (lo < p.npairs && __ldg(&p.pkeys[lo]) == key) return __ldg(&p.pkey_pair[lo]);
+  const u32 big = max(a, b);
+  const u64 key = ((u64)big << 32) | min(a, b);
+  u32 lo = __ldg(&p.pkey_begin[big]);
+  const u32 end = __ldg(&p.pkey_begin[big + 1]);
+  u32 hi = end;
+  while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (__ldg(&p.pkeys[mid]) < key) lo = mid + 1; else hi = mid; }
+  if (lo < end && __ldg(&p.pkeys[lo]) == key) return __ldg(&p.pkey_pair[lo]);
   return FCM_NONE;
 }
 
@@ -1033,13 +1036,22 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
   __syncwarp();
   if (hdr[3]) { const int e = (int)hdr[3]; if (lane == 0) st->err = e; return e; }
   const int nedit = (int)hdr[7];
-  for (int t = lane; t < nedit; t += 32) {              // (from, to) -> slot
-    const u32 ft = s.edits[2 * t], from = dv[ft >> 16], to = dv[ft & 0xffffu];
-    const u32 pair = find_pair(p, from, to);
-    s.edits[2 * t] = pair == FCM_NONE ? FCM_NONE : 2 * pair + (from > to ? 0u : 1u);
+  bool fast = !force_full;
+  {
+    bool bad = false, narrow = true;
+    for (int t = lane; t < nedit; t += 32) {            // (from, to) -> slot; is every list short enough for the delta form?
+      const u32 ft = s.edits[2 * t], from = dv[ft >> 16], to = dv[ft & 0xffffu];
+      const u32 pair = find_pair(p, from, to);
+      if (pair == FCM_NONE) bad = true;
+      else {
+        s.edits[2 * t] = 2 * pair + (from > to ? 0u : 1u);
+        narrow &= __ldg(&p.nb_off[pair + 1]) - __ldg(&p.nb_off[pair]) <= FAST_C;
+      }
+    }
+    if (__any_sync(FULL, bad)) { if (lane == 0) st->err = FCM_ENOTADJ; return FCM_ENOTADJ; }
+    fast = fast && __all_sync(FULL, narrow);
   }
   __syncwarp();
-  for (int t = 0; t < nedit; t++) if (s.edits[2 * t] == FCM_NONE) { if (lane == 0) st->err = FCM_ENOTADJ; return FCM_ENOTADJ; }
   // ---- State::apply_transition (src/lib.rs:61-79) ----
   Chain c;
   c.adj = (u64*)cb; c.items = cb + p.off_items; c.pos = cb + p.off_pos; c.dbl = cb + p.off_dbl; c.dblpos = cb + p.off_dblpos;
@@ -1052,11 +1064,6 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
   // the edited edge in the graph as it stands then) - every term is the single-edge count of the flip
   // path, on the static common-neighbour list of that pair.  Lists beyond FAST_C (or kernel kind 1)
   // take the reference's two counts of the whole union neighbourhood instead; same flag_count.
-  bool fast = !force_full;
-  for (int t = 0; t < nedit && fast; t++) {
-    const u32 pair = s.edits[2 * t] >> 1;
-    fast = __ldg(&p.nb_off[pair + 1]) - __ldg(&p.nb_off[pair]) <= FAST_C;
-  }
   bool bits_applied = false;
   if (nedit && fast) {
     if (instr && !build_nbhd(p, s.edits, nedit, s.verts, K, lane)) rc = FCM_ELIMIT;
@@ -1072,17 +1079,20 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
       const u32 slot = s.edits[2 * t];
       const bool add = s.edits[2 * t + 1] != 0;
       const int sign = add ? 1 : -1;
-      const uint2 ft = slot_edge(p, slot);               // the edge u -> v
-      const u32 o = __ldg(&p.nb_off[slot >> 1]);
-      const int cc = (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - o);
+      // index path: the pair's static entry holds its endpoints, list offset and length (one load, not three)
+      uint4 i0 = make_uint4(0, 0, 0, 0), i1 = i0;
+      if (red) { i0 = __ldg(&p.pinfo[2 * (slot >> 1)]); i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]); }
+      // the edge u -> v; dir 0 of a slot = big -> small
+      const uint2 ft = red ? ((slot & 1) ? make_uint2(i0.y, i0.x) : make_uint2(i0.x, i0.y)) : slot_edge(p, slot);
+      const u32 o = red ? i0.z : __ldg(&p.nb_off[slot >> 1]);
+      const int cc = red ? (int)i1.x : (int)(__ldg(&p.nb_off[(slot >> 1) + 1]) - o);
       edges += sign;
       if (red && cc <= NARROW_C) {
         // the pair's triangles and 4-cliques from the static clique index, their orientation from the
         // chain's orientation bits (kept current edit by edit below): two round trips instead of c rows
-        const uint4 i0 = __ldg(&p.pinfo[2 * (slot >> 1)]), i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]);
         u32* const sA32 = (u32*)(wb + SM_A);
         OriReq r;
-        idx_issue(p, c.ori, i0.z, cc, i0.w, (int)i1.y, ft.x == i0.x, lane, r);
+        idx_issue(p, c.ori, i0.z, cc, i0.w, (int)i1.y, !(slot & 1), lane, r);
         const G32 g = idx_finish(p, c.ori, i0.w, (int)i1.y, r, sA32, lane);
         // first the flip path's tagged single-mask graph (<= 32 tagged copies, <= DELTA_SD + 1 vertices);
         // when it does not fit, the general tagged count on the same gathered rows

@@ -450,11 +450,14 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   std::vector<u32> cq_verts;
   std::vector<u64> pkeys(p.npairs);
   std::vector<u32> pkey_pair(p.npairs);
+  std::vector<u32> pkey_begin((size_t)n + 1, 0);
   {
     std::vector<u32> rk(p.npairs);
     for (u64 q = 0; q < p.npairs; q++) rk[q] = (u32)q;
     std::sort(rk.begin(), rk.end(), [&](u32 x, u32 y) { return pkey(pair_ab[x].x, pair_ab[x].y) < pkey(pair_ab[y].x, pair_ab[y].y); });
     for (u64 r = 0; r < p.npairs; r++) { pkeys[r] = pkey(pair_ab[rk[r]].x, pair_ab[rk[r]].y); pkey_pair[r] = rk[r]; }
+    for (u64 r = 0; r < p.npairs; r++) pkey_begin[(size_t)(pkeys[r] >> 32) + 1]++;
+    for (u32 v = 0; v < n; v++) pkey_begin[v + 1] += pkey_begin[v];
   }
   if (want_cliques) {
     std::vector<std::vector<u32>> cl = maximal_cliques(n, und, nthreads);
@@ -546,17 +549,19 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     e->index_bytes = pinfo.size() * sizeof(uint4) + tri.size() * sizeof(uint2) + k4.size() * 4;
   }
   {
-    u64* d_keys; u32* d_kp; u32* d_cq;
+    u64* d_keys; u32* d_kp; u32* d_cq; u32* d_kb;
     if ((rc = dev_alloc(e, &d_keys, pkeys.size()))) return fail(rc);
     if ((rc = dev_alloc(e, &d_kp, pkey_pair.size()))) return fail(rc);
     if ((rc = dev_alloc(e, &d_cq, cq_verts.size()))) return fail(rc);
+    if ((rc = dev_alloc(e, &d_kb, pkey_begin.size()))) return fail(rc);
     cudaError_t ce = cudaSuccess;
     if (!pkeys.empty()) ce = cudaMemcpyAsync(d_keys, pkeys.data(), pkeys.size() * 8, cudaMemcpyHostToDevice, ctx->stream);
     if (ce == cudaSuccess && !pkey_pair.empty()) ce = cudaMemcpyAsync(d_kp, pkey_pair.data(), pkey_pair.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
     if (ce == cudaSuccess && !cq_verts.empty()) ce = cudaMemcpyAsync(d_cq, cq_verts.data(), cq_verts.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(d_kb, pkey_begin.data(), pkey_begin.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(ctx->stream);
     if (ce != cudaSuccess) { fcm_set_error("upload of the clique tables failed: %s", cudaGetErrorString(ce)); return fail(FCM_ECUDA); }
-    p.pkeys = d_keys; p.pkey_pair = d_kp; p.cq_verts = d_cq;
+    p.pkeys = d_keys; p.pkey_pair = d_kp; p.cq_verts = d_cq; p.pkey_begin = d_kb;
   }
   if ((rc = dev_alloc(e, &p.st, (size_t)nchains))) return fail(rc);
   if ((rc = dev_alloc(e, &e->edit_dev, (size_t)FCM_MAXEDIT * 2))) return fail(rc);

@@ -119,6 +119,7 @@ struct EnsParams {
   const u32* cq_verts;              // cliques of one order back to back, vertices ascending
   const u64* pkeys;                 // (big << 32 | small) of every adjacent pair, ascending
   const u32* pkey_pair;             // ... and its pair id
+  const u32* pkey_begin;            // n + 1: first key whose bigger vertex is >= v (the binary search of a pair stays in one vertex's run)
 };
 
 struct fcm_ensemble {
