@@ -1053,13 +1053,11 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
   }
   __syncwarp();
   // ---- State::apply_transition (src/lib.rs:61-79) ----
-  Chain c;
-  c.adj = (u64*)cb; c.items = cb + p.off_items; c.pos = cb + p.off_pos; c.dbl = cb + p.off_dbl; c.dblpos = cb + p.off_dblpos;
-  c.ori = cb + p.off_ori;
-  c.E = st->E; c.ND = st->ND;
-  const u64 fc = st->flag_count[lane];
+  // (the chain's containers and flag_count are only picked up behind the counts: the per-edit loop is
+  // short of registers under the hot loop's cap)
+  u32* const ori = cb + p.off_ori;
   int len = st->fc_len, K = 0, prelen = 0, postlen = 0, rc = 0;
-  u64 fnew = fc;
+  u64 fnew = 0;
   // DELTA form: post - pre = sum over the edits, applied one after the other, of +-(simplices through
   // the edited edge in the graph as it stands then) - every term is the single-edge count of the flip
   // path, on the static common-neighbour list of that pair.  Lists beyond FAST_C (or kernel kind 1)
@@ -1092,8 +1090,8 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
         // chain's orientation bits (kept current edit by edit below): two round trips instead of c rows
         u32* const sA32 = (u32*)(wb + SM_A);
         OriReq r;
-        idx_issue(p, c.ori, i0.z, cc, i0.w, (int)i1.y, !(slot & 1), lane, r);
-        const G32 g = idx_finish(p, c.ori, i0.w, (int)i1.y, r, sA32, lane);
+        idx_issue(p, ori, i0.z, cc, i0.w, (int)i1.y, !(slot & 1), lane, r);
+        const G32 g = idx_finish(p, ori, i0.w, (int)i1.y, r, sA32, lane);
         // first the flip path's tagged single-mask graph (<= 32 tagged copies, <= DELTA_SD + 1 vertices);
         // when it does not fit, the general tagged count on the same gathered rows
         Tagged tg;
@@ -1135,7 +1133,7 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
         const u32 m = 1u << (ft.y & 31);
         if (red) { if (add) atomicOr(w, m); else atomicAnd(w, ~m); }
         else { const u32 wv = __ldcg(w); *w = add ? (wv | m) : (wv & ~m); }
-        u32* const ow = &c.ori[slot >> 5];
+        u32* const ow = &ori[slot >> 5];
         const u32 om = 1u << (slot & 31);
         const u32 ov = __ldcg(ow);
         *ow = add ? (ov | om) : (ov & ~om);
@@ -1153,7 +1151,7 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
       }
       if (lane == 0) { s.deep[2] += (u64)(long long)tri; s.deep[1] += (u64)(long long)edges; }
       __syncwarp();
-      fnew = fc + s.deep[lane];
+      fnew = st->flag_count[lane] + s.deep[lane];
       if (__any_sync(FULL, (long long)fnew < 0)) rc = FCM_EASSERT;
       // post.len() exceeds the old length iff a simplex of a new dimension exists afterwards (src/lib.rs:72-74)
       const u32 nz = __ballot_sync(FULL, fnew != 0);
@@ -1164,7 +1162,10 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
     if (lane < 8) s.dflag[lane] = 0;
     __syncwarp();
   } else if (nedit) {
-    rc = transition_counts(p, c, s, nedit, lane, K, prelen, postlen);
+    Chain cf;
+    cf.adj = (u64*)cb; cf.items = cf.pos = cf.dbl = cf.dblpos = nullptr; cf.ori = ori; cf.E = cf.ND = 0;
+    rc = transition_counts(p, cf, s, nedit, lane, K, prelen, postlen);
+    const u64 fc = st->flag_count[lane];
     if (!rc) {
       const u64 pr = lane < min(prelen, len) ? s.pre[lane] : 0;
       if (__any_sync(FULL, fc < pr)) rc = FCM_EASSERT;
@@ -1172,8 +1173,13 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
       len = max(len, max(postlen, prelen));
     }
   }
+  else fnew = st->flag_count[lane];
   if (rc) { if (lane == 0) st->err = rc; return rc; }
   const bool ok = bounds_ok(p, fnew, lane);
+  Chain c;
+  c.adj = (u64*)cb; c.items = cb + p.off_items; c.pos = cb + p.off_pos; c.dbl = cb + p.off_dbl; c.dblpos = cb + p.off_dblpos;
+  c.ori = ori;
+  c.E = st->E; c.ND = st->ND;
   // containers: the edits in order; a rejected transition is applied and reverted like the reference
   // does (src/lib.rs:186-191), which leaves the containers in a different ORDER than before
   {
