@@ -415,3 +415,41 @@ def test_checkpoint_restore_resumes_exactly(simple, ctx, graphs, tmp_path):
         s2.restore(1, bad)
     s.close()
     s2.close()
+
+
+@pytest.mark.parametrize("block", range(4))
+def test_all_moves_fuzz_random_graphs(block, ctx):
+    # many small random graphs (sparse to dense, with and without double edges, overlapping maximal cliques),
+    # random move mixes and bounds: per-proposal trace, counts, containers and RNG against the oracle
+    r = np.random.default_rng(1000 + block)
+    mixes = [ds.MOVE_DISTRIBUTION, (0.0, 0.0, 1.0, 0.0), (0.0, 0.0, 0.0, 1.0), (0.25, 0.25, 0.25, 0.25), (0.0, 0.2, 0.4, 0.4)]
+    ran = rejected = 0
+    for case in range(12):
+        n = int(r.integers(5, 44))
+        e = rand_graph(n, float(r.uniform(0.08, 0.45)), int(r.integers(1 << 30)), pdouble=float(r.choice([0.0, 0.2, 0.6])))
+        if e.shape[0] == 0 or sum(orc.count(n, e)) > 60000:
+            continue                                      # one warp per chain: keep the single traced chain's counts small
+        weights = mixes[int(r.integers(len(mixes)))]
+        seed = int(r.integers(1 << 40))
+        relax = float(r.choice([0.01, 0.05, 0.5]))
+        try:
+            o = orc.Sampler(n, e, seed, relax, move_weights=weights)
+        except RuntimeError:
+            continue                                      # the reference panics on this graph (Bounds::calculate)
+        w = o.read()
+        fc0 = fcm.flagser_count(n, e, ctx)
+        s = fcm.MCMCSampler(ctx, n, e, [seed], ds.Bounds(w["bounds_min"], w["bounds_max"]), fc0, weights, w["sample_distance"])
+        s.set_kernel(int(r.choice([0, 0, 2])))
+        got, want = s.step_trace(500, 0), o.steps(500)
+        try:
+            assert_trace_equal(got, want)
+            compare_chain(s, 0, o)
+        except AssertionError as ex:
+            raise AssertionError("block %d case %d (n=%d, m=%d, mix=%s, relax=%s): %s" % (block, case, n, e.shape[0], weights, relax, ex))
+        rr = s.read(0)
+        assert ds.trim(rr["flag_count"]) == fcm.flagser_count(n, rr["edges"], ctx)
+        rejected += 500 - int(((want["flags"] >> 4) & 1).sum())
+        ran += 1
+        s.close()
+    assert ran >= 5
+    assert rejected > 0
