@@ -39,7 +39,8 @@ enum {
                                   undirected graph (reference: HashMap index panic, src/lib.rs:104) */
   FCM_EASSERT = -7,            /* reference assert!(s >= p) would fail (src/lib.rs:65,86) */
   FCM_EUNSUPPORTED = -8,       /* a clique move was drawn on an ensemble created without clique moves */
-  FCM_ELIMIT = -9              /* neighbourhood larger than the kernel's local-matrix capacity */
+  FCM_ELIMIT = -9              /* neighbourhood larger than the kernel's local-matrix capacity, or a clique move
+                                  beyond the limits stated at fcm_ensemble_create */
 };
 
 typedef struct fcm_ctx fcm_ctx;
@@ -135,6 +136,8 @@ int fcm_edge_neighborhoods(fcm_ctx* ctx, uint32_t n, uint64_t nedges, const uint
  *    clique_order_distribution = WeightedIndex(len^0.2) (src/bin/sample.rs:87-88) is built.
  *    Trace records of clique moves: a, b = index of the chosen clique(s) within their order,
  *    dm0 = order index, dm1 = number of change_edges, K = |edgeset_neighborhood|.
+ *    Limits of a clique move: the cliques of a swap hold <= 32 vertices together and a transition
+ *    <= 128 change_edges; beyond that the chain stops with the sticky error FCM_ELIMIT.
  * ---------------------------------------------------------------------------------------------- */
 int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, const uint32_t (*edges)[2],
                         uint32_t nchains, const uint64_t* seeds,
