@@ -6,7 +6,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libfcm.so")
+# FCM_LIB=<path of an experiment build, csrc/Makefile VARIANT=...> replaces the default library (measurements only)
+LIB_PATH = os.environ.get("FCM_LIB") or os.path.join(HERE, "libfcm.so")
 
 FCM_MAXD = 32
 FCM_OK, FCM_EINVAL, FCM_ENODEVICE, FCM_ECUDA, FCM_ENOMEM = 0, -1, -2, -3, -4
@@ -24,6 +25,8 @@ SYMBOLS = [
     "fcm_ensemble_info", "fcm_ensemble_set_stats", "fcm_ensemble_index_info", "fcm_apply", "fcm_revert", "fcm_bounds_check",
     "fcm_ensemble_edgebits_info", "fcm_ensemble_edgebits_slots", "fcm_ensemble_edgebits",
     "fcm_ensemble_read_doubles", "fcm_ensemble_restore",
+    "fcm_graph_status", "fcm_comm_create", "fcm_comm_connect", "fcm_comm_destroy",
+    "fcm_graph_count_allreduce_async", "fcm_graph_count_allreduce",
 ]
 
 
@@ -73,6 +76,12 @@ def lib():
     L.fcm_graph_destroy.argtypes = [vp]
     L.fcm_graph_count.argtypes = [vp, u32, u32, vp, P(i32)]
     L.fcm_graph_count_async.argtypes = [vp, u32, u32, P(vp)]
+    L.fcm_graph_status.argtypes = [vp]
+    L.fcm_comm_create.argtypes = [vp, i32, u32, u32, P(vp), vp]
+    L.fcm_comm_connect.argtypes = [vp, vp]
+    L.fcm_comm_destroy.argtypes = [vp]
+    L.fcm_graph_count_allreduce_async.argtypes = [vp, vp, P(vp)]
+    L.fcm_graph_count_allreduce.argtypes = [vp, vp, vp, P(i32)]
     L.fcm_graph_set_kernel.argtypes = [vp, i32]
     L.fcm_graph_info.argtypes = [vp, P(u32), P(u64), P(u32), P(u32)]
     L.fcm_graph_cells.argtypes = [vp, i32, i32, vp, u64, P(u64)]

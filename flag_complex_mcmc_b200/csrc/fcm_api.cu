@@ -71,6 +71,7 @@ extern "C" int fcm_ctx_create(int device, fcm_ctx** out) {
   c->stream = c->own;
   FCM_CUDA(cudaEventCreate(&c->ev0));
   FCM_CUDA(cudaEventCreate(&c->ev1));
+  FCM_CUDA(cudaHostAlloc((void**)&c->pin, FCM_PIN_WORDS * 8, cudaHostAllocDefault));
   *out = c;
   return FCM_OK;
 }
@@ -81,6 +82,7 @@ extern "C" int fcm_ctx_destroy(fcm_ctx* c) {
   cudaEventDestroy(c->ev0);
   cudaEventDestroy(c->ev1);
   cudaStreamDestroy(c->own);
+  if (c->pin) cudaFreeHost(c->pin);
   delete c;
   return FCM_OK;
 }
@@ -133,7 +135,7 @@ static int graph_create(fcm_ctx* c, u32 n, u64 ne, const uint32_t (*edges)[2], i
   G_CUDA(fcm_pool_alloc(&g->csr_off, ((size_t)n + 1) * 8, c->stream));
   G_CUDA(fcm_pool_alloc(&g->order, std::max<u32>(n, 1) * 4, c->stream));
   G_CUDA(fcm_pool_alloc(&g->overflow, std::max<u32>(n, 1) * 4, c->stream));
-  G_CUDA(fcm_pool_alloc(&g->counts, FCM_MAXD * 8, c->stream));
+  G_CUDA(fcm_pool_alloc(&g->counts, (FCM_MAXD + 1) * 8, c->stream));
   G_CUDA(fcm_pool_alloc(&g->ctrl, CT_WORDS * 4, c->stream));
   if (ne) {
     G_CUDA(fcm_pool_alloc(&edges_dev, ne * 8, c->stream));
@@ -191,14 +193,26 @@ extern "C" int fcm_graph_count_async(fcm_graph* g, uint32_t part, uint32_t npart
   if (counts_dev) *counts_dev = g->counts;
   return FCM_OK;
 }
+extern "C" int fcm_graph_status(fcm_graph* g) {
+  REQUIRE(g, "graph is null");
+  USE(g->ctx);
+  u32* const ctrl = (u32*)g->ctx->pin;
+  FCM_CUDA(cudaMemcpyAsync(ctrl, g->ctrl, CT_WORDS * 4, cudaMemcpyDeviceToHost, g->ctx->stream));
+  FCM_CUDA(cudaStreamSynchronize(g->ctx->stream));
+  if (ctrl[CT_ERR] == 3) { fcm_set_error("the all-reduce of the counts timed out: a rank never arrived"); return FCM_ECUDA; }
+  if (ctrl[CT_ERR]) { fcm_set_error("a simplex of dimension >= %d was met", FCM_MAXD); return FCM_EDIM; }
+  return FCM_OK;
+}
 extern "C" int fcm_graph_count(fcm_graph* g, uint32_t part, uint32_t nparts, uint64_t* counts, int* len) {
   REQUIRE(counts && len, "counts/len is null");
   int rc = fcm_graph_count_async(g, part, nparts, nullptr);
   if (rc) return rc;
-  u32 ctrl[CT_WORDS];
-  FCM_CUDA(cudaMemcpyAsync(counts, g->counts, FCM_MAXD * 8, cudaMemcpyDeviceToHost, g->ctx->stream));
-  FCM_CUDA(cudaMemcpyAsync(ctrl, g->ctrl, sizeof(ctrl), cudaMemcpyDeviceToHost, g->ctx->stream));
+  u64* const pin = g->ctx->pin;
+  const u32* const ctrl = (const u32*)(pin + FCM_MAXD + 1);
+  FCM_CUDA(cudaMemcpyAsync(pin, g->counts, FCM_MAXD * 8, cudaMemcpyDeviceToHost, g->ctx->stream));
+  FCM_CUDA(cudaMemcpyAsync((void*)ctrl, g->ctrl, CT_WORDS * 4, cudaMemcpyDeviceToHost, g->ctx->stream));
   FCM_CUDA(cudaStreamSynchronize(g->ctx->stream));
+  memcpy(counts, pin, FCM_MAXD * 8);
   if (ctrl[CT_ERR]) { fcm_set_error("a simplex of dimension >= %d was met", FCM_MAXD); return FCM_EDIM; }
   int l = FCM_MAXD;
   while (l > 0 && counts[l - 1] == 0) l--;

@@ -20,6 +20,7 @@
 #include "fcm_internal.cuh"
 
 #include <algorithm>
+#include <cstring>
 
 #define DENSE_WARPS 4
 #define MAXL_DENSE (FCM_MAXD - 1)   // level l holds candidates for vertex index l+1
@@ -193,7 +194,8 @@ __global__ void __launch_bounds__(LocalCfg<WK>::THREADS, LocalCfg<WK>::MINBLOCKS
 count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
                    const u32* __restrict__ csr, const u32* __restrict__ order, u32 W, u32 nv_total,
                    u32 part, u32 nparts, u32 kcap, u32* __restrict__ ctrl,
-                   u32* __restrict__ overflow, u64* __restrict__ counts, const EmitArgs ea) {
+                   u32* __restrict__ overflow, u64* __restrict__ counts, const EmitArgs ea,
+                   const __grid_constant__ CommArgs ca) {
   using Cfg = LocalCfg<WK>;
   constexpr int LS = Cfg::LS, NT = Cfg::THREADS, NW = NT / 32, BPL = Cfg::BPL, MAXIDS = Cfg::MAXIDS;
   constexpr int RL = MAXIDS - 1;                        // cnt[r]: flag_count index 3 + r (tuples of 2 + r ids)
@@ -377,6 +379,14 @@ count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
     if (cnt[r]) atomicAdd(&s_cnt[3 + r], (unsigned long long)cnt[r]);
   __syncthreads();
   if (tid < FCM_MAXD && s_cnt[tid]) atomicAdd((unsigned long long*)&counts[tid], s_cnt[tid]);
+  // the all-reduce over the ranks of the box, fused: the CTA that finishes last owns the device's totals
+  if (ca.mode != COMM_NONE) {
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_task = atomicAdd(&ctrl[CT_DONE], 1u) == gridDim.x - 1 ? 1u : 0u;
+    __syncthreads();
+    if (s_task) comm_last_cta(ca, counts, ctrl);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -384,8 +394,10 @@ count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(DENSE_WARPS * 32)
 count_dense_kernel(const u64* __restrict__ adj, const u32* __restrict__ tasks, u32 ntasks_total,
-                   u32 part, u32 nparts, u32 W, u32* __restrict__ ticket, u32* __restrict__ ctrl,
-                   u64* __restrict__ scratch, u64* __restrict__ counts) {
+                   const u32* __restrict__ ntasks_dev, u32 part, u32 nparts, u32 W, u32* __restrict__ ticket,
+                   u32* __restrict__ ctrl, u64* __restrict__ scratch, u64* __restrict__ counts,
+                   const __grid_constant__ CommArgs ca) {
+  if (ntasks_dev) ntasks_total = *ntasks_dev;             // the overflow list's length is only known on the device
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const u32 gwarp = blockIdx.x * DENSE_WARPS + wib;
   u64* P = scratch + (size_t)gwarp * MAXL_DENSE * W;     // P[l*W + x]
@@ -468,13 +480,21 @@ count_dense_kernel(const u64* __restrict__ adj, const u32* __restrict__ tasks, u
   __syncthreads();
   if (threadIdx.x < FCM_MAXD && s_cnt[threadIdx.x])
     atomicAdd((unsigned long long*)&counts[threadIdx.x], s_cnt[threadIdx.x]);
+  if (ca.mode != COMM_NONE) {
+    __shared__ u32 s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&ctrl[CT_DONE], 1u) == gridDim.x - 1 ? 1u : 0u;
+    __syncthreads();
+    if (s_last) comm_last_cta(ca, counts, ctrl);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------
 // launcher
 // ---------------------------------------------------------------------------------------------------
 template <int WK, bool EMIT>
-static int launch_local(fcm_graph* g, u32 part, u32 nparts, u32 kcap, const EmitArgs& ea) {
+static int launch_local(fcm_graph* g, u32 part, u32 nparts, u32 kcap, const EmitArgs& ea, const CommArgs& ca) {
   fcm_ctx* c = g->ctx;
   constexpr int LS = LocalCfg<WK>::LS;
   constexpr int LOCAL_THREADS = LocalCfg<WK>::THREADS;
@@ -487,16 +507,15 @@ static int launch_local(fcm_graph* g, u32 part, u32 nparts, u32 kcap, const Emit
   u32 ntasks = g->n > part ? (g->n - part + nparts - 1) / nparts : 0;
   u32 blocks = (u32)std::min<u64>((u64)c->sm_count * per_sm, std::max<u32>(ntasks, 1));
   kern<<<blocks, LOCAL_THREADS, smem, c->stream>>>(g->adj, g->csr_off, g->csr, g->order, g->W, g->n,
-                                                   part, nparts, kcap, g->ctrl, g->overflow, g->counts, ea);
+                                                   part, nparts, kcap, g->ctrl, g->overflow, g->counts, ea, ca);
   c->launches++;
   FCM_CUDA(cudaGetLastError());
   return FCM_OK;
 }
 
-static int launch_dense(fcm_graph* g, const u32* tasks, u32 ntasks_total, u32 part, u32 nparts,
-                        u32* ticket, bool tasks_count_on_device) {
+static int launch_dense(fcm_graph* g, const u32* tasks, u32 ntasks_total, const u32* ntasks_dev, u32 part, u32 nparts,
+                        u32* ticket, const CommArgs& ca) {
   fcm_ctx* c = g->ctx;
-  (void)tasks_count_on_device;
   u32 blocks = (u32)c->sm_count * 4;
   size_t need = (size_t)blocks * DENSE_WARPS * MAXL_DENSE * g->W;
   if (need > g->scratch_words) {
@@ -505,41 +524,43 @@ static int launch_dense(fcm_graph* g, const u32* tasks, u32 ntasks_total, u32 pa
     FCM_CUDA(fcm_pool_alloc(&g->scratch, need * 8, c->stream));
     g->scratch_words = need;
   }
-  count_dense_kernel<<<blocks, DENSE_WARPS * 32, 0, c->stream>>>(g->adj, tasks, ntasks_total, part, nparts,
-                                                                g->W, ticket, g->ctrl, g->scratch, g->counts);
+  count_dense_kernel<<<blocks, DENSE_WARPS * 32, 0, c->stream>>>(g->adj, tasks, ntasks_total, ntasks_dev, part, nparts,
+                                                                g->W, ticket, g->ctrl, g->scratch, g->counts, ca);
   c->launches++;
   FCM_CUDA(cudaGetLastError());
   return FCM_OK;
 }
 
-// Enqueue the count of shard (part, nparts) on the context stream; result in g->counts (device).
-int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts) {
+// Enqueue the count of shard (part, nparts) on the context stream; result in g->counts (device).  With comm the
+// last CTA of the last kernel also runs the all-reduce over the ranks (fcm_comm.cu).  Nothing here waits for
+// the device.
+int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts, const CommArgs* comm) {
   fcm_ctx* c = g->ctx;
-  FCM_CUDA(cudaMemsetAsync(g->counts, 0, FCM_MAXD * 8, c->stream));
+  CommArgs none;
+  memset(&none, 0, sizeof(none));
+  const CommArgs& ca = comm ? *comm : none;
+  FCM_CUDA(cudaMemsetAsync(g->counts, 0, (FCM_MAXD + 1) * 8, c->stream));
   FCM_CUDA(cudaMemsetAsync(g->ctrl, 0, CT_WORDS * 4, c->stream));
-  if (g->n == 0) return FCM_OK;
-  if (g->kernel_kind == 1) return launch_dense(g, g->order, g->n, part, nparts, &g->ctrl[CT_TICKET], false);
+  if (g->n == 0 && ca.mode == COMM_NONE) return FCM_OK;
+  if (g->kernel_kind == 1 || g->n == 0) return launch_dense(g, g->order, g->n, nullptr, part, nparts, &g->ctrl[CT_TICKET], ca);
   // tile: the smallest WK in {1,2,4,8,16} covering the largest out-degree (capped at 1024 columns)
   u32 kmax = g->maxout;
   int rc;
   u32 kcap;
   // (rows: the actual largest out-degree rounded up to 32, so that more CTAs fit one SM)
   kcap = std::min<u32>(1024u, std::max<u32>(32u, (kmax + 31u) & ~31u));
-  const EmitArgs none = {0, 0, 0, nullptr, 0, nullptr};
-  if (kmax <= 64) rc = launch_local<1, false>(g, part, nparts, kcap, none);
-  else if (kmax <= 128) rc = launch_local<2, false>(g, part, nparts, kcap, none);
-  else if (kmax <= 256) rc = launch_local<4, false>(g, part, nparts, kcap, none);
-  else if (kmax <= 512) rc = launch_local<8, false>(g, part, nparts, kcap, none);
-  else rc = launch_local<16, false>(g, part, nparts, kcap, none);
+  const EmitArgs noemit = {0, 0, 0, nullptr, 0, nullptr};
+  // sources that do not fit the tile are appended to g->overflow and counted by the dense-row kernel behind
+  // this one (their number stays on the device: ctrl[CT_NOVER]); the all-reduce then rides on that kernel
+  const bool spill = kmax > kcap;
+  const CommArgs& cl = spill ? none : ca;
+  if (kmax <= 64) rc = launch_local<1, false>(g, part, nparts, kcap, noemit, cl);
+  else if (kmax <= 128) rc = launch_local<2, false>(g, part, nparts, kcap, noemit, cl);
+  else if (kmax <= 256) rc = launch_local<4, false>(g, part, nparts, kcap, noemit, cl);
+  else if (kmax <= 512) rc = launch_local<8, false>(g, part, nparts, kcap, noemit, cl);
+  else rc = launch_local<16, false>(g, part, nparts, kcap, noemit, cl);
   if (rc) return rc;
-  if (kmax > kcap) {
-    // sources that did not fit the tile were appended to g->overflow; their number is only known
-    // on the device, so the dense kernel takes it from ctrl[CT_NOVER] via a tiny host hop.
-    u32 nover = 0;
-    FCM_CUDA(cudaMemcpyAsync(&nover, &g->ctrl[CT_NOVER], 4, cudaMemcpyDeviceToHost, c->stream));
-    FCM_CUDA(cudaStreamSynchronize(c->stream));
-    if (nover) return launch_dense(g, g->overflow, nover, 0, 1, &g->ctrl[CT_TICKET2], true);
-  }
+  if (spill) return launch_dense(g, g->overflow, 0, &g->ctrl[CT_NOVER], 0, 1, &g->ctrl[CT_TICKET2], ca);
   return FCM_OK;
 }
 
@@ -547,7 +568,7 @@ int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts) {
 // dim_max + 1 vertices); *ncells_dev counts every cell found, also those beyond cap.
 int fcm_cells_launch(fcm_graph* g, u32 dim_min, u32 dim_max, u32* cells_dev, u64 cap, unsigned long long* ncells_dev) {
   fcm_ctx* c = g->ctx;
-  FCM_CUDA(cudaMemsetAsync(g->counts, 0, FCM_MAXD * 8, c->stream));
+  FCM_CUDA(cudaMemsetAsync(g->counts, 0, (FCM_MAXD + 1) * 8, c->stream));
   FCM_CUDA(cudaMemsetAsync(g->ctrl, 0, CT_WORDS * 4, c->stream));
   FCM_CUDA(cudaMemsetAsync(ncells_dev, 0, 8, c->stream));
   if (g->n == 0) return FCM_OK;
@@ -556,9 +577,11 @@ int fcm_cells_launch(fcm_graph* g, u32 dim_min, u32 dim_max, u32* cells_dev, u64
   if (dim_max > (u32)LocalCfg<1>::MAXIDS) { fcm_set_error("for_each_cell: dim_max > %d", LocalCfg<1>::MAXIDS); return FCM_ELIMIT; }
   const u32 kcap = std::min<u32>(1024u, std::max<u32>(32u, (kmax + 31u) & ~31u));
   const EmitArgs ea = {dim_min, dim_max, dim_max + 1, cells_dev, cap, ncells_dev};
-  if (kmax <= 64) return launch_local<1, true>(g, 0, 1, kcap, ea);
-  if (kmax <= 128) return launch_local<2, true>(g, 0, 1, kcap, ea);
-  if (kmax <= 256) return launch_local<4, true>(g, 0, 1, kcap, ea);
-  if (kmax <= 512) return launch_local<8, true>(g, 0, 1, kcap, ea);
-  return launch_local<16, true>(g, 0, 1, kcap, ea);
+  CommArgs none;
+  memset(&none, 0, sizeof(none));
+  if (kmax <= 64) return launch_local<1, true>(g, 0, 1, kcap, ea, none);
+  if (kmax <= 128) return launch_local<2, true>(g, 0, 1, kcap, ea, none);
+  if (kmax <= 256) return launch_local<4, true>(g, 0, 1, kcap, ea, none);
+  if (kmax <= 512) return launch_local<8, true>(g, 0, 1, kcap, ea, none);
+  return launch_local<16, true>(g, 0, 1, kcap, ea, none);
 }

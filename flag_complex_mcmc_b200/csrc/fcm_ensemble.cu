@@ -352,24 +352,36 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   if (p.W == 0) p.W = 2;
 
   // ---- pairs, slots, containers: replay Graph::add_edge in edge-list order (src/io.rs:26-33) ----
+  // Pair ids are an internal numbering (the API speaks vertices).  They are dealt in (big, small) order: the
+  // pairs {x, u} with x < u then sit side by side, 2 orientation bits each, so the orientation words a
+  // proposal looks up for the triangles and 4-cliques of (u, v) fall into few 32-byte sectors - range(u),
+  // range(v) and range(w) of the common neighbours w > v - instead of one random sector per entry
+  // (measured on the C5 shard, profiles/README.md r02_b).  FCM_PAIR_ORDER=0 numbers them in order of first
+  // appearance in the edge list instead (the round-1 layout, kept for the A/B measurement).
   std::vector<uint2> pair_ab;
   std::vector<u32> items, pos, dbl, dblpos;
   std::vector<u64> adj((size_t)n * p.W, 0);
   e->pairmap.reserve(nedges * 2);
+  {
+    const char* po = getenv("FCM_PAIR_ORDER");
+    const bool sorted_ids = !(po && po[0] == '0');
+    for (u64 i = 0; i < nedges; i++) {
+      const u32 a = edges[i][0], b = edges[i][1];
+      if (a >= n || b >= n || a == b) { fcm_set_error("edge %llu = (%u,%u): vertex id >= n or self loop", (unsigned long long)i, a, b); return fail(FCM_EINVAL); }
+      const u32 big = std::max(a, b), small = std::min(a, b);
+      if (e->pairmap.emplace(pkey(big, small), (u32)pair_ab.size()).second) pair_ab.push_back(make_uint2(big, small));
+    }
+    if (sorted_ids) {
+      std::sort(pair_ab.begin(), pair_ab.end(), [](const uint2& x, const uint2& y) { return pkey(x.x, x.y) < pkey(y.x, y.y); });
+      for (size_t q = 0; q < pair_ab.size(); q++) e->pairmap[pkey(pair_ab[q].x, pair_ab[q].y)] = (u32)q;
+    }
+    pos.assign(2 * pair_ab.size(), FCM_NONE);
+    dblpos.assign(pair_ab.size(), FCM_NONE);
+  }
   for (u64 i = 0; i < nedges; i++) {
-    u32 a = edges[i][0], b = edges[i][1];
-    if (a >= n || b >= n || a == b) { fcm_set_error("edge %llu = (%u,%u): vertex id >= n or self loop", (unsigned long long)i, a, b); return fail(FCM_EINVAL); }
-    u32 big = std::max(a, b), small = std::min(a, b);
-    auto it = e->pairmap.find(pkey(big, small));
-    u32 pair;
-    if (it == e->pairmap.end()) {
-      pair = (u32)pair_ab.size();
-      e->pairmap.emplace(pkey(big, small), pair);
-      pair_ab.push_back(make_uint2(big, small));
-      pos.push_back(FCM_NONE); pos.push_back(FCM_NONE);
-      dblpos.push_back(FCM_NONE);
-    } else pair = it->second;
-    u32 slot = 2 * pair + (a > b ? 0u : 1u);
+    const u32 a = edges[i][0], b = edges[i][1];
+    const u32 pair = e->pairmap.find(pkey(std::max(a, b), std::min(a, b)))->second;
+    const u32 slot = 2 * pair + (a > b ? 0u : 1u);
     if (pos[slot] != FCM_NONE) continue;               // duplicate line: IndexSet insert is a no-op
     pos[slot] = (u32)items.size();
     items.push_back(slot);

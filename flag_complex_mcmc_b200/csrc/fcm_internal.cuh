@@ -31,7 +31,10 @@ struct fcm_ctx {
   cudaStream_t own = nullptr, stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   u64 launches = 0;
+  u64* pin = nullptr;               // FCM_PIN_WORDS of pinned host memory: small read-backs that must not take the
+                                    // driver's pageable-copy path (it blocks the other host threads' launches)
 };
+#define FCM_PIN_WORDS 128
 
 // ---- device graph for recounts ---------------------------------------------------------------------
 struct fcm_graph {
@@ -42,7 +45,7 @@ struct fcm_graph {
   u64* csr_off = nullptr;           // n + 1
   u32* csr = nullptr;               // ne, each out-list ascending
   u32* order = nullptr;             // vertices by descending out-degree
-  u64* counts = nullptr;            // FCM_MAXD
+  u64* counts = nullptr;            // FCM_MAXD + 1 ([FCM_MAXD]: ranks in error, all-reduce paths only)
   u32* ctrl = nullptr;              // [0] ticket, [1] overflow count, [2] error flag, [3] ticket2
   u32* overflow = nullptr;          // n
   u64* scratch = nullptr;           // dense-row kernel P stacks
@@ -58,10 +61,95 @@ static inline cudaError_t fcm_pool_alloc(T** p, size_t bytes, cudaStream_t s) { 
 static inline void fcm_pool_free(void* p, cudaStream_t s) { if (p) cudaFreeAsync(p, s); }
 
 // device control words
-enum { CT_TICKET = 0, CT_NOVER = 1, CT_ERR = 2, CT_TICKET2 = 3, CT_WORDS = 8 };
+enum { CT_TICKET = 0, CT_NOVER = 1, CT_ERR = 2, CT_TICKET2 = 3, CT_DONE = 4, CT_WORDS = 8 };
+// CT_ERR values: 1 bad edge list (build), 2 a simplex of dimension >= FCM_MAXD, 3 all-reduce timed out
+
+// ---- all-reduce of the per-dimension counts across the ranks of one box (fcm_comm.cu) ----------------
+// A rank's window: two slots used by alternating all-reduce calls.  Every rank adds its vector into slot s
+// of EVERY rank's window (system-scope atomics: NVLink for the peers), then bumps `arrived` there; a rank
+// reads its own slot once `arrived` == nranks and clears it for the call after the next.  (Slot s is only
+// written again by a peer that has finished the call in between, which needs this rank's contribution to
+// that call, which this rank issues after the clear: two slots suffice.)
+struct CommSlot {
+  unsigned long long sum[FCM_MAXD + 1];   // [FCM_MAXD]: number of ranks whose shard met a simplex of dimension >= FCM_MAXD
+  u32 arrived;
+  u32 pad[61];                            // 512 bytes per slot
+};
+static_assert(sizeof(CommSlot) == 512, "CommSlot layout");
+enum { COMM_NONE = 0, COMM_PEER_EPILOGUE = 1, COMM_ERR_WORD = 2 };
+struct CommArgs {                         // kernel parameter of the count kernels
+  u32 mode;                               // COMM_*: nothing / fused all-reduce by the last CTA / last CTA copies the error flag behind the counts (NCCL follows)
+  u32 nranks, rank, slot;
+  unsigned long long timeout_ns;
+  unsigned long long peer[FCM_COMM_MAXRANKS];   // rank r's window as mapped into this process
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ u32 comm_ld_acquire_sys(const u32* p) {
+  u32 v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long comm_ld_relaxed_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long comm_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// Run by every thread of the LAST CTA of a count (>= 64 threads), after all CTAs' atomics on counts[] have been
+// fenced: counts[0..FCM_MAXD) becomes the sum over all ranks, counts[FCM_MAXD] the number of ranks in error.
+__device__ __forceinline__ void comm_last_cta(const CommArgs& ca, u64* counts, u32* ctrl) {
+  const int tid = threadIdx.x;
+  __threadfence();
+  unsigned long long v = 0;
+  if (tid < FCM_MAXD) v = __ldcg((const unsigned long long*)&counts[tid]);
+  else if (tid == FCM_MAXD) v = __ldcg(&ctrl[CT_ERR]) ? 1ULL : 0ULL;
+  if (ca.mode == COMM_ERR_WORD) {
+    if (tid == FCM_MAXD) counts[FCM_MAXD] = v;
+    return;
+  }
+  if (tid <= FCM_MAXD) {
+    if (v)
+      for (u32 k = 0; k < ca.nranks; k++) {              // start with the own window: the ranks do not all hit rank 0 first
+        u32 q = ca.rank + k; if (q >= ca.nranks) q -= ca.nranks;
+        atomicAdd_system(&((CommSlot*)ca.peer[q] + ca.slot)->sum[tid], v);
+      }
+    __threadfence_system();
+  }
+  __syncthreads();
+  CommSlot* const mine = (CommSlot*)ca.peer[ca.rank] + ca.slot;
+  if (tid == 0) {
+    __threadfence_system();
+    for (u32 k = 0; k < ca.nranks; k++) {
+      u32 q = ca.rank + k; if (q >= ca.nranks) q -= ca.nranks;
+      atomicAdd_system(&((CommSlot*)ca.peer[q] + ca.slot)->arrived, 1u);
+    }
+    const unsigned long long t0 = comm_globaltimer();
+    u32 spins = 0;
+    while (comm_ld_acquire_sys(&mine->arrived) < ca.nranks) {
+      __nanosleep(64);
+      if ((++spins & 255u) == 0 && comm_globaltimer() - t0 > ca.timeout_ns) { atomicExch(&ctrl[CT_ERR], 3u); break; }
+    }
+  }
+  __syncthreads();
+  if (tid <= FCM_MAXD) {
+    __threadfence_system();
+    const unsigned long long tot = comm_ld_relaxed_sys(&mine->sum[tid]);
+    counts[tid] = tot;
+    if (tid == FCM_MAXD && tot) atomicMax(&ctrl[CT_ERR], 2u);
+    mine->sum[tid] = 0;
+  }
+  __syncthreads();
+  if (tid == 0) { mine->arrived = 0; __threadfence_system(); }
+}
+#endif
 
 // fcm_count.cu
-int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts);
+int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts, const CommArgs* comm = nullptr);
 int fcm_cells_launch(fcm_graph* g, u32 dim_min, u32 dim_max, u32* cells_dev, u64 cap, unsigned long long* ncells_dev);
 int fcm_graph_build_device(fcm_graph* g, const uint2* edges_dev, u64 ne_in, int normalise,
                            std::vector<u64>& off_host);

@@ -12,6 +12,7 @@ src/lib.rs) over libfcm.so.  Names, argument meaning and error behaviour follow 
 All counting and all chain steps run in CUDA (libfcm.so); nothing here falls back to the CPU.
 """
 import ctypes as C
+import sys
 import math
 
 import numpy as np
@@ -151,7 +152,8 @@ class Context:
 
     def __del__(self):
         try:
-            self.close()
+            if not sys.is_finalizing():                 # at interpreter exit the CUDA runtime may be gone already
+                self.close()
         except Exception:
             pass
 
@@ -189,6 +191,23 @@ class DeviceGraph:
         """`graph.flagser_count()`: list without trailing zeros."""
         return trim(self.count_shard(0, 1))
 
+    def count_allreduce(self, comm):
+        """Shard `comm.rank of comm.nranks` counted and summed over the ranks inside the library
+        (fused last-CTA epilogue over NVLink, or NCCL): every rank gets the whole graph's uint64[FCM_MAXD]."""
+        out = np.zeros(FCM_MAXD, dtype=np.uint64)
+        ln = C.c_int()
+        check(lib().fcm_graph_count_allreduce(self.h, comm.h, ptr(out), C.byref(ln)))
+        return out
+
+    def count_allreduce_async(self, comm):
+        """Enqueue count + all-reduce on the context stream; returns the device address of uint64[FCM_MAXD + 1]."""
+        p = C.c_void_p()
+        check(lib().fcm_graph_count_allreduce_async(self.h, comm.h, C.byref(p)))
+        return p.value
+
+    def status(self):
+        check(lib().fcm_graph_status(self.h))
+
     def cells(self, dim_min, dim_max):
         """All cells of dimension dim_min..dim_max: (ncells, dim_max + 1) uint32 rows (v0..vd, padded
         with 0xffffffff) in the recursion's order (flag_complex::for_each_cell)."""
@@ -206,7 +225,50 @@ class DeviceGraph:
 
     def __del__(self):
         try:
-            self.close()
+            if not sys.is_finalizing():                 # at interpreter exit the CUDA runtime may be gone already
+                self.close()
+        except Exception:
+            pass
+
+
+COMM_PEER, COMM_NCCL = 0, 1
+COMM_HANDLE_BYTES = 256
+
+
+class Comm:
+    """One rank of the recount's all-reduce (fcm_comm).  `exchange(blob) -> list of all ranks' blobs in rank
+    order` is the host's transport (torch.distributed all_gather, MPI, ...); ranks sharing a process pass
+    `Comm.connect_local([...])` instead."""
+
+    def __init__(self, ctx, rank, nranks, kind=COMM_PEER, exchange=None):
+        self.ctx, self.rank, self.nranks, self.kind = ctx, int(rank), int(nranks), int(kind)
+        self.h = C.c_void_p()
+        self.handle = np.zeros(COMM_HANDLE_BYTES, dtype=np.uint8)
+        check(lib().fcm_comm_create(ctx.h, self.kind, self.rank, self.nranks, C.byref(self.h), ptr(self.handle)))
+        if exchange is not None:
+            self.connect(exchange(self.handle))
+
+    def connect(self, handles):
+        allh = np.ascontiguousarray(np.concatenate([np.asarray(h, dtype=np.uint8).reshape(-1) for h in handles]))
+        assert allh.size == self.nranks * COMM_HANDLE_BYTES, "need one handle per rank"
+        check(lib().fcm_comm_connect(self.h, ptr(allh)))
+
+    @staticmethod
+    def connect_local(comms):
+        """Ranks living in this process (FCM_COMM_PEER): hand every comm all the handles."""
+        hs = [c.handle for c in sorted(comms, key=lambda c: c.rank)]
+        for c in comms:
+            c.connect(hs)
+
+    def close(self):
+        if self.h:
+            lib().fcm_comm_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            if not sys.is_finalizing():                 # at interpreter exit the CUDA runtime may be gone already
+                self.close()
         except Exception:
             pass
 
@@ -488,7 +550,8 @@ class MCMCSampler:
 
     def __del__(self):
         try:
-            self.close()
+            if not sys.is_finalizing():                 # at interpreter exit the CUDA runtime may be gone already
+                self.close()
         except Exception:
             pass
 

@@ -26,7 +26,7 @@ extern "C" {
 #endif
 
 #define FCM_MAXD 32            /* longest flag_count vector handled (dimension <= 31) */
-#define FCM_ABI_VERSION 1
+#define FCM_ABI_VERSION 2
 
 enum {
   FCM_OK = 0,
@@ -92,11 +92,51 @@ int fcm_graph_destroy(fcm_graph* g);
 /* Count the simplices whose source (first) vertex v0 is in shard `part` of `nparts`
  * (degree-balanced round-robin over source vertices; part 0 of 1 = whole graph).
  * counts[FCM_MAXD] is filled (zero padded); *len = top non-empty dimension + 1 OF THIS SHARD.
- * Summing the shards' vectors (NCCL allreduce, 16 x u64) gives flagser_count.  Synchronous. */
+ * Summing the shards' vectors (fcm_graph_count_allreduce below, or any all-reduce of FCM_MAXD x u64 of the
+ * caller's own) gives flagser_count.  Synchronous. */
 int fcm_graph_count(fcm_graph* g, uint32_t part, uint32_t nparts, uint64_t* counts, int* len);
 /* Same, asynchronous on the context stream: result stays in a device buffer of FCM_MAXD u64
  * (pointer returned through counts_dev) so that a collective can consume it without a host hop. */
 int fcm_graph_count_async(fcm_graph* g, uint32_t part, uint32_t nparts, uint64_t** counts_dev);
+/* Synchronise and report what the last asynchronous count on this graph met: FCM_OK, FCM_EDIM (a simplex of
+ * dimension >= FCM_MAXD: the counts are truncated) or FCM_ECUDA (all-reduce timed out / CUDA error). */
+int fcm_graph_status(fcm_graph* g);
+
+/* ------------------------------------------------------------------------------------------------
+ * 3b. The sharded recount's all-reduce, inside the library: State::new's `graph.flagser_count()`
+ *     (src/lib.rs:51, and :130) split by source vertex over the GPUs of one box.  One fcm_comm per rank
+ *     (= per GPU); the ranks may live in one process or in one process each.
+ *       FCM_COMM_PEER  every rank owns a small window in its HBM that all ranks map (cudaIpc across
+ *                      processes, peer access inside one).  The LAST CTA of the count kernel adds the
+ *                      rank's u64 vector into every rank's window with system-scope atomics over
+ *                      NVLink/NVSwitch and waits for the other ranks' contributions: count and all-reduce
+ *                      are ONE kernel launch, no host hop, no extra launch.
+ *       FCM_COMM_NCCL  ncclAllReduce(sum, uint64, FCM_MAXD + 1) enqueued on the context stream right behind
+ *                      the count kernel (libnccl.so.2 is dlopen'ed; libfcm.so has no link-time NCCL need).
+ *     Setup, both kinds: every rank calls fcm_comm_create and gets a FCM_COMM_HANDLE_BYTES blob; the host
+ *     exchanges the blobs by any means (MPI, torch.distributed all_gather, a file; memcpy when the ranks
+ *     share a process) and gives all nranks of them, in rank order, to fcm_comm_connect.  With
+ *     FCM_COMM_NCCL fcm_comm_connect is ncclCommInitRank, i.e. itself a collective: every rank must be
+ *     inside it at the same time (one thread per rank when they share a process).
+ *     Like any collective, every rank must issue the same sequence of all-reduce calls on a comm; a rank
+ *     that never arrives makes the others give up after FCM_COMM_TIMEOUT_MS (default 10000, environment)
+ *     with FCM_ECUDA, after which the comm must be destroyed.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct fcm_comm fcm_comm;
+#define FCM_COMM_HANDLE_BYTES 256
+#define FCM_COMM_MAXRANKS 16
+enum { FCM_COMM_PEER = 0, FCM_COMM_NCCL = 1 };
+int fcm_comm_create(fcm_ctx* ctx, int kind, uint32_t rank, uint32_t nranks, fcm_comm** out,
+                    uint8_t handle_out[FCM_COMM_HANDLE_BYTES]);
+int fcm_comm_connect(fcm_comm* c, const uint8_t* handles /* nranks x FCM_COMM_HANDLE_BYTES, rank order */);
+int fcm_comm_destroy(fcm_comm* c);
+/* Count shard `rank of nranks` of g (g and c on the same context) and all-reduce: afterwards EVERY rank holds
+ * the whole graph's flagser_count.  Asynchronous on the context stream; *counts_dev = device buffer of
+ * FCM_MAXD + 1 u64 (entry FCM_MAXD: number of ranks that met a simplex of dimension >= FCM_MAXD). */
+int fcm_graph_count_allreduce_async(fcm_graph* g, fcm_comm* c, uint64_t** counts_dev);
+/* Same, synchronous: counts[FCM_MAXD] zero padded, *len = top non-empty dimension + 1 of the WHOLE graph. */
+int fcm_graph_count_allreduce(fcm_graph* g, fcm_comm* c, uint64_t* counts, int* len);
+
 /* flag_complex::for_each_cell(&G, &mut F, min, max) (src/bin/all_cxs.rs:60-64,79-83) as a bulk call:
  * every cell of dimension dim_min..dim_max (dim_max <= 6) as one row of dim_max + 1 vertex ids
  * (v0..vd, padded with 0xffffffff), rows in the order the recursion meets them with candidates in

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     for name in names:
         assert hasattr(L, name), name
     assert sorted(N.SYMBOLS) == names
-    assert L.fcm_abi_version() == 1
+    assert L.fcm_abi_version() == 2
 
 
 def test_no_cpu_fallback_without_device():

@@ -26,7 +26,7 @@ def driver(tmp_path_factory):
 
 def test_cpp_host_maths_match_python_mirror_and_oracle(driver):
     r = json.loads(subprocess.check_output([driver, "selfcheck"]))
-    assert r["abi"] == 1
+    assert r["abi"] == 2
     assert r["factorial"] == [1, 1, 1, 2, 6]               # src/util.rs:65-71: (x-1)!
     assert r["binomial_5_2"] == ds.binomial(5, 2) == 12
     assert r["oeis"] == list(ds.OEIS_A058298)              # generated as n!/(n-k), equals the reference's table
