@@ -1736,8 +1736,15 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
   const u64 chunk = 1ULL << 24;                         // the kernel's per-launch counters are 32-bit
   for (u64 done = 0; done < nsteps; done += chunk) {
     const u32 now = (u32)std::min<u64>(chunk, nsteps - done);
-    chain_step_kernel<IDX, INSTR><<<blocks, wpb * 32, smem, e->ctx->stream>>>(p, now, trace_dev ? trace_dev + done : nullptr,
-                                                                     trace_chain, (u32)per_warp, e->force_full);
+    // the launch carries the L2 access-policy window of the clique index (persisting hits, streaming misses)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(blocks); cfg.blockDim = dim3(wpb * 32); cfg.dynamicSmemBytes = smem; cfg.stream = e->ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
+    attr[0].val.accessPolicyWindow = e->l2_window;
+    cfg.attrs = attr; cfg.numAttrs = e->l2_window.num_bytes ? 1 : 0;
+    FCM_CUDA(cudaLaunchKernelEx(&cfg, chain_step_kernel<IDX, INSTR>, p, now, trace_dev ? trace_dev + done : (fcm_trace_rec*)nullptr,
+                                trace_chain, (u32)per_warp, (int)e->force_full));
     e->ctx->launches++;
   }
   FCM_CUDA(cudaGetLastError());

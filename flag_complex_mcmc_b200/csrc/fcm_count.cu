@@ -136,11 +136,27 @@ template <int WK> struct LocalCfg {
 };
 __host__ __device__ constexpr u32 stack_cap(u32 kcap) { return kcap + 128; }   // entries per warp (>= kcap + 32; a full stack falls back to deep_count)
 
+// for_each_cell (flag_complex::for_each_cell, src/bin/all_cxs.rs:60-64): where the cells of dimension
+// emit_min..emit_max go.  Row r of `cells` = the vertices (v0..vd) of one cell, padded with FCM_NONE.
+struct EmitArgs { u32 emit_min, emit_max, stride; u32* cells; u64 cap; unsigned long long* ncells; };
+
+__device__ __forceinline__ void emit_cell(const EmitArgs& ea, u32 v0, const u32* verts, u64 e, u32 d) {
+  if (d < ea.emit_min || d > ea.emit_max) return;
+  const u64 row = atomicAdd(ea.ncells, 1ULL);
+  if (row >= ea.cap) return;
+  u32* out = ea.cells + row * ea.stride;
+  out[0] = v0;
+  for (u32 t = 0; t < ea.stride - 1; t++) out[1 + t] = t < d ? verts[(e >> (10 * t)) & 1023u] : FCM_NONE;
+}
+
 // P = candidates for the vertex of index `lvl` (non-empty, already counted).  Generic levels: explicit
-// stack in local memory, counts through shared atomics (rare: dimension > REG_LEVELS + 2).
-template <int WK>
+// stack in local memory, counts through shared atomics (rare: dimension > MAXIDS + 1, or a full stack).
+// EMIT: the walk also writes out the cells it meets (for_each_cell never drops a subtree): `e` = the
+// tuple of local ids (10 bits each) of the simplex P belongs to; the walk stops at dimension emit_max.
+template <int WK, bool EMIT>
 __device__ __noinline__ void deep_count(const u64 (&P0)[WK], int lvl, const u64* __restrict__ L,
-                                        unsigned long long* s_cnt, u32* ctrl) {
+                                        unsigned long long* s_cnt, u32* ctrl, const EmitArgs& ea, u32 v0,
+                                        const u32* verts, u64 e) {
   constexpr int LS = LocalCfg<WK>::LS;
   u64 P[FCM_MAXD][WK];
   int cw[FCM_MAXD];
@@ -161,6 +177,13 @@ __device__ __noinline__ void deep_count(const u64 (&P0)[WK], int lvl, const u64*
     const u64* Lj = L + (size_t)j * LS;
     u32 cpc = 0;
     const int d = lvl + l + 1;                          // flag_count index the children of this node close
+    if constexpr (EMIT) {
+      // the simplex (v0, tuple.., j) has dimension d - 1 = lvl + l; its ids sit at positions 0 .. lvl + l - 1
+      const u32 npos = (u32)(lvl + l - 1);              // position of j in the tuple
+      e = (e & ((1ULL << (10 * npos)) - 1ULL)) | ((u64)j << (10 * npos));
+      emit_cell(ea, v0, verts, e, (u32)(lvl + l));
+      if ((u32)(lvl + l) >= ea.emit_max) continue;      // nothing deeper is asked for (MAXIDS bounds emit_max)
+    }
     if (d < FCM_MAXD) {
 #pragma unroll
       for (int x = 0; x < WK; x++) { u64 q = P[l][x] & Lj[x]; P[l + 1][x] = q; cpc += __popcll(q); }
@@ -174,19 +197,6 @@ __device__ __noinline__ void deep_count(const u64 (&P0)[WK], int lvl, const u64*
       if (cpc) atomicExch(&ctrl[CT_ERR], 2u);           // a simplex of dimension >= FCM_MAXD
     }
   }
-}
-
-// for_each_cell (flag_complex::for_each_cell, src/bin/all_cxs.rs:60-64): where the cells of dimension
-// emit_min..emit_max go.  Row r of `cells` = the vertices (v0..vd) of one cell, padded with FCM_NONE.
-struct EmitArgs { u32 emit_min, emit_max, stride; u32* cells; u64 cap; unsigned long long* ncells; };
-
-__device__ __forceinline__ void emit_cell(const EmitArgs& ea, u32 v0, const u32* verts, u64 e, u32 d) {
-  if (d < ea.emit_min || d > ea.emit_max) return;
-  const u64 row = atomicAdd(ea.ncells, 1ULL);
-  if (row >= ea.cap) return;
-  u32* out = ea.cells + row * ea.stride;
-  out[0] = v0;
-  for (u32 t = 0; t < ea.stride - 1; t++) out[1 + t] = t < d ? verts[(e >> (10 * t)) & 1023u] : FCM_NONE;
 }
 
 template <int WK, bool EMIT>
@@ -346,9 +356,9 @@ count_local_kernel(const u64* __restrict__ adj, const u64* __restrict__ csr_off,
         const u32 total = __shfl_sync(0xffffffffu, incl, 31);
         __syncwarp();                                   // every lane has read its entry
         if (top + total > scap) {                       // stack full: this batch's subtrees by per-thread DFS
-          if (pc) deep_count<WK>(P, (int)d + 1, L, s_cnt, ctrl);
+          if (pc) deep_count<WK, EMIT>(P, (int)d + 1, L, s_cnt, ctrl, ea, v0, verts, e);
         } else {
-          if (deep) deep_count<WK>(P, (int)d + 1, L, s_cnt, ctrl);
+          if (deep) deep_count<WK, EMIT>(P, (int)d + 1, L, s_cnt, ctrl, ea, v0, verts, e);
           else if (pc) {
             u32 o = top + incl - want;
             const u64 base = (e & 0x0fffffffffffffffULL) | ((u64)(d + 1) << 60);

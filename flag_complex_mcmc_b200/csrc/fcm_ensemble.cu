@@ -49,7 +49,13 @@ static int weighted_index_init(const double w[4], double cum[3], double* scale) 
 // Keep the static clique index resident in L2: the chains' own state (GBs of random rows) otherwise competes with the
 // ~50 MB index for the 126 MB L2 (measured on the C5 shard: 363.1 -> 372.6 M proposals/s, profiles/README.md).
 // FCM_L2_PERSIST=<hit ratio scale, 0 < x <= 1> tunes it, FCM_L2_PERSIST=0 turns it off; default 1.
-static void index_l2_window(fcm_ctx* ctx, void* base, size_t bytes) {
+// The window is handed to every launch of the chain kernel as a launch attribute (fcm_chain.cu), never installed on a
+// stream: a caller-owned stream (fcm_ctx_set_stream) is left as it was, and the window follows the context wherever
+// it launches.  Process-global side effect: cudaLimitPersistingL2CacheSize is raised to cover the index;
+// fcm_ensemble_destroy resets the persisting lines (cudaCtxResetPersistingL2Cache).
+static void index_l2_window(fcm_ensemble* e, void* base, size_t bytes) {
+  fcm_ctx* ctx = e->ctx;
+  memset(&e->l2_window, 0, sizeof(e->l2_window));
   const char* env = getenv("FCM_L2_PERSIST");
   const double scale = env ? atof(env) : 1.0;
   if (!(scale > 0.0) || bytes == 0) return;
@@ -59,13 +65,11 @@ static void index_l2_window(fcm_ctx* ctx, void* base, size_t bytes) {
   if (max_persist <= 0 || max_win <= 0) return;
   const size_t carve = std::min(bytes, (size_t)max_persist), win = std::min(bytes, (size_t)max_win);
   if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) != cudaSuccess) { cudaGetLastError(); return; }
-  cudaStreamAttrValue v{};
-  v.accessPolicyWindow.base_ptr = base;
-  v.accessPolicyWindow.num_bytes = win;
-  v.accessPolicyWindow.hitRatio = (float)std::min(1.0, scale * (double)carve / (double)win);
-  v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-  v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-  if (cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &v) != cudaSuccess) cudaGetLastError();
+  e->l2_window.base_ptr = base;
+  e->l2_window.num_bytes = win;
+  e->l2_window.hitRatio = (float)std::min(1.0, scale * (double)carve / (double)win);
+  e->l2_window.hitProp = cudaAccessPropertyPersisting;
+  e->l2_window.missProp = cudaAccessPropertyStreaming;
 }
 
 template <typename T>
@@ -320,6 +324,7 @@ extern "C" int fcm_ensemble_destroy(fcm_ensemble* e) {
   if (!e) return FCM_OK;
   if (e->ctx) { cudaSetDevice(e->ctx->device); cudaStreamSynchronize(e->ctx->stream); }
   for (void* q : e->dev_allocs) cudaFree(q);
+  if (e->l2_window.num_bytes) cudaCtxResetPersistingL2Cache();   // the index's persisting lines go back to normal
   if (e->trace_dev) cudaFree(e->trace_dev);
   if (e->eb_out_dev) cudaFree(e->eb_out_dev);
   delete e;
@@ -576,7 +581,7 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     unsigned char* slab = nullptr;
     if ((rc = dev_alloc(e, &slab, o_k4 + b_k4))) return fail(rc);
     uint4* d_pinfo = (uint4*)slab; uint2* d_tri = (uint2*)(slab + o_tri); u32* d_k4 = (u32*)(slab + o_k4);
-    index_l2_window(ctx, slab, o_k4 + b_k4);
+    index_l2_window(e, slab, o_k4 + b_k4);
     cudaError_t ce = cudaMemcpyAsync(d_pinfo, pinfo.data(), pinfo.size() * sizeof(uint4), cudaMemcpyHostToDevice, ctx->stream);
     if (ce == cudaSuccess) ce = cudaMemcpyAsync(d_tri, tri.data(), tri.size() * sizeof(uint2), cudaMemcpyHostToDevice, ctx->stream);
     if (ce == cudaSuccess && !k4.empty()) ce = cudaMemcpyAsync(d_k4, k4.data(), k4.size() * 4, cudaMemcpyHostToDevice, ctx->stream);

@@ -226,6 +226,7 @@ struct fcm_ensemble {
   int cliques = 0;                        // clique moves enabled (bigger per-warp shared memory)
   int stats = 1;                          // 1: the kernels keep the neighbourhood-size statistic (sumK / nonempty)
   u64 index_bytes = 0;
+  cudaAccessPolicyWindow l2_window = {};    // the clique index slab, given to every chain-kernel launch (num_bytes = 0: none)
   fcm_trace_rec* trace_dev = nullptr;
   u64 trace_cap = 0;
   u32* edit_dev = nullptr;                // FCM_MAXEDIT * 2 (slot, add)

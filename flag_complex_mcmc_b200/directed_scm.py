@@ -94,16 +94,29 @@ def calc_relax_de(sc):
 
 
 # ---- io.rs ---------------------------------------------------------------------------------------
+def _parse_node(tok):
+    """Rust `u32::from_str` (src/io.rs:31 `i.parse().unwrap()`): optional '+', then decimal digits only."""
+    t = tok[1:] if tok.startswith("+") else tok
+    if not t or not all("0" <= ch <= "9" for ch in t) or int(t) > 0xFFFFFFFF:
+        raise ValueError("not a vertex id: %r" % tok)
+    return int(t)
+
+
 def read_flag_file(fname):
-    """src/io.rs:18-35 -> (n, edges uint32 (E,2) in file order)."""
-    with open(fname) as f:
-        lines = f.read().splitlines()
+    """src/io.rs:18-35 -> (n, edges uint32 (E,2) in file order).  Lines as str::lines() yields them, tokens split
+    on ' ' only; a token that is not a u32 raises ValueError where the reference panics."""
+    with open(fname, "rb") as f:
+        text = f.read().decode("utf-8")
+    lines = text.split("\n")
+    if lines and lines[-1] == "":
+        lines.pop()                                                  # str::lines(): no empty last line after a final '\n'
+    lines = [ln[:-1] if ln.endswith("\r") else ln for ln in lines]
     n = len([t for t in lines[1].split(" ") if t != ""])
     edges = []
     for ln in lines[3:]:
         t = [x for x in ln.split(" ") if x != ""]
         if len(t) >= 2:
-            edges.append((int(t[0]), int(t[1])))
+            edges.append((_parse_node(t[0]), _parse_node(t[1])))
     return n, np.array(edges, dtype=np.uint32).reshape(-1, 2)
 
 
@@ -403,6 +416,7 @@ class MCMCSampler:
         mw = np.asarray(move_weights, dtype=np.float64)
         if mw.size != 4:
             raise ValueError("move_weights must have 4 entries")
+        self.move_weights = [float(x) for x in mw]
         self.h = C.c_void_p()
         check(lib().fcm_ensemble_create(ctx.h, self.n, int(e.shape[0]), ptr(e), self.nchains, ptr(self.seeds),
                                         ptr(fc0), int(fc0.size), ptr(mn), int(mn.size), ptr(mx), int(mx.size),
@@ -612,8 +626,20 @@ class BitOutput:
             self.current_file.flush()
 
 
+def _undirected_hash(edges):
+    """FNV-1a over the sorted list of adjacent pairs: identifies the underlying undirected graph, which no move changes."""
+    e = np.asarray(edges, dtype=np.uint64).reshape(-1, 2)
+    key = np.unique(np.maximum(e[:, 0], e[:, 1]) << np.uint64(32) | np.minimum(e[:, 0], e[:, 1]))
+    h = 1469598103934665603
+    for x in key.tolist():
+        h = ((h ^ x) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
 def save_state(fname, sample_number, sampler, chain=0):
-    """io::save_state (src/io.rs:51-56): (sample_number, chain state) to `fname` via a temp file + rename."""
+    """io::save_state (src/io.rs:51-56): (sample_number, chain state) to `fname` via a temp file + rename.
+    Beside the chain (edge containers in order, RNG, counters) the file holds what the reference's MCMCSampler
+    carries (src/lib.rs:164-178): bounds, move distribution, sample_distance - and a hash of the undirected graph."""
     import os
     ck = sampler.checkpoint(chain)
     tmp = fname + ".tmp"
@@ -621,15 +647,38 @@ def save_state(fname, sample_number, sampler, chain=0):
         np.savez(f, sample_number=np.int64(sample_number), sample_distance=np.int64(sampler.sample_distance),
                  bounds_min=np.asarray(sampler.bounds.flag_count_min, dtype=np.uint64),
                  bounds_max=np.asarray(sampler.bounds.flag_count_max, dtype=np.uint64),
+                 move_weights=np.asarray(sampler.move_weights, dtype=np.float64),
+                 undirected_hash=np.uint64(_undirected_hash(ck["edges"])),
                  sampled=np.uint64(ck["sampled"]), accepted=np.uint64(ck["accepted"]),
                  **{k: ck[k] for k in ("edges", "doubles", "rng", "flag_count")})
     os.replace(tmp, fname)
 
 
-def load_state(fname, sampler, chain=0):
-    """io::load_state (src/io.rs:58-62) into chain `chain` of `sampler` -> sample_number."""
+def load_state(fname, sampler, chain=0, adopt_settings=False):
+    """io::load_state (src/io.rs:58-62) into chain `chain` of `sampler` -> sample_number.
+
+    The reference rebuilds a whole one-chain MCMCSampler from the file.  Here the target is one chain of an
+    ensemble whose bounds, move distribution and sample_distance are shared by all chains, so a checkpoint taken
+    under different settings is REFUSED (ValueError) rather than silently changing the other chains - unless
+    adopt_settings=True, which takes bounds and sample_distance from the file for the whole ensemble (what the
+    reference does for its single chain).  The underlying undirected graph must be the ensemble's."""
     z = np.load(fname)
+    mn, mx = [int(x) for x in z["bounds_min"]], [int(x) for x in z["bounds_max"]]
+    sd = int(z["sample_distance"])
+    mw = [float(x) for x in z["move_weights"]] if "move_weights" in z.files else None
+    if mw is not None and list(mw) != [float(x) for x in sampler.move_weights]:
+        raise ValueError("checkpoint was taken with move distribution %s, the ensemble runs %s" % (mw, list(sampler.move_weights)))
+    same = (mn == list(sampler.bounds.flag_count_min) and mx == list(sampler.bounds.flag_count_max) and sd == sampler.sample_distance)
+    if not same and not adopt_settings:
+        raise ValueError("checkpoint bounds / sample_distance differ from the ensemble's (pass adopt_settings=True to "
+                         "take them over for every chain)")
+    if "undirected_hash" in z.files and sampler.nchains:
+        here = _undirected_hash(sampler.read(0)["edges"])
+        if int(z["undirected_hash"]) != here:
+            raise ValueError("checkpoint belongs to a different underlying undirected graph")
     sampler.restore(chain, {k: z[k] for k in ("edges", "doubles", "rng", "flag_count")} |
                     {"sampled": int(z["sampled"]), "accepted": int(z["accepted"])})
-    sampler.set_bounds(Bounds([int(x) for x in z["bounds_min"]], [int(x) for x in z["bounds_max"]]))
+    if not same:
+        sampler.set_bounds(Bounds(mn, mx))
+        sampler.sample_distance = sd
     return int(z["sample_number"])

@@ -39,24 +39,47 @@ inline void check(int rc) {
 
 // ---- io.rs ------------------------------------------------------------------------------------------
 // line 1 skipped, the token count of line 2 is the number of vertices, line 3 skipped, then "i j [w]"
+// Tokens are split on ' ' ONLY, empty tokens dropped (src/io.rs:25,29: `split(' ').filter(|s| *s != "")`), lines as
+// Rust's str::lines() yields them (split on '\n', one trailing '\r' removed).  A token that is not a u32 - e.g. two
+// numbers joined by a tab - throws where the reference's `parse().unwrap()` panics (:31).
 inline std::pair<uint32_t, std::vector<Edge>> read_flag_file(const std::string& fname) {
-  std::ifstream f(fname);
+  std::ifstream f(fname, std::ios::binary);
   if (!f) throw Error(FCM_EINVAL, "cannot open " + fname);
   std::string line;
+  auto next_line = [&](std::string& out) {
+    if (!std::getline(f, out, '\n')) return false;
+    if (!out.empty() && out.back() == '\r') out.pop_back();
+    return true;
+  };
   auto tokens = [](const std::string& s) {
     std::vector<std::string> t;
-    std::istringstream is(s);
-    for (std::string w; is >> w;) t.push_back(w);
+    size_t i = 0;
+    while (i <= s.size()) {
+      const size_t j = std::min(s.find(' ', i), s.size());
+      if (j > i) t.push_back(s.substr(i, j - i));
+      i = j + 1;
+    }
     return t;
   };
-  std::getline(f, line);
-  std::getline(f, line);
+  auto parse_node = [&](const std::string& w) {             // Rust u32::from_str: optional '+', then decimal digits only
+    size_t i = (!w.empty() && w[0] == '+') ? 1 : 0;
+    if (i >= w.size()) throw Error(FCM_EINVAL, "not a vertex id: '" + w + "' in " + fname);
+    uint64_t v = 0;
+    for (; i < w.size(); i++) {
+      if (w[i] < '0' || w[i] > '9') throw Error(FCM_EINVAL, "not a vertex id: '" + w + "' in " + fname);
+      v = v * 10 + (uint64_t)(w[i] - '0');
+      if (v > 0xffffffffull) throw Error(FCM_EINVAL, "vertex id out of range: '" + w + "' in " + fname);
+    }
+    return (Node)v;
+  };
+  next_line(line);                                           // skip "dim 0:"
+  if (!next_line(line)) throw Error(FCM_EINVAL, "no vertex line in " + fname);   // reference: unwrap() on None panics
   const uint32_t n = (uint32_t)tokens(line).size();
-  std::getline(f, line);
+  next_line(line);                                           // skip "dim 1:"
   std::vector<Edge> edges;
-  while (std::getline(f, line)) {
+  while (next_line(line)) {
     const auto t = tokens(line);
-    if (t.size() >= 2) edges.push_back({(Node)std::stoul(t[0]), (Node)std::stoul(t[1])});
+    if (t.size() >= 2) edges.push_back({parse_node(t[0]), parse_node(t[1])});
   }
   return {n, edges};
 }

@@ -654,25 +654,47 @@ struct Sampler {
 };
 
 // io::read_flag_file  src/io.rs:18-35 : line 1 skipped, line 2 token count = n, line 3 skipped,
-// then "i j [w]" (weight ignored), lines with < 2 tokens ignored.
+// then "i j [w]" (weight ignored), lines with < 2 tokens ignored.  Lines as str::lines() (:23) gives them
+// ('\n' ends a line, one '\r' before it is dropped); tokens split on ' ' only (:25,:29); a token that is not a
+// u32 makes the reference panic (`parse().unwrap()`, :31) -> false here.
+static bool parse_u32_token(const std::string& w, Node& out) {
+  size_t i = (!w.empty() && w[0] == '+') ? 1 : 0;
+  if (i >= w.size()) return false;
+  u64 v = 0;
+  for (; i < w.size(); i++) {
+    if (w[i] < '0' || w[i] > '9') return false;
+    v = v * 10 + (u64)(w[i] - '0');
+    if (v > 0xffffffffULL) return false;
+  }
+  out = (Node)v;
+  return true;
+}
 static bool read_flag_file(const char* path, u32& n, std::vector<Edge>& edges) {
-  std::ifstream f(path);
+  std::ifstream f(path, std::ios::binary);
   if (!f) return false;
   std::string line;
+  auto next_line = [&](std::string& out) {
+    if (!std::getline(f, out, '\n')) return false;
+    if (!out.empty() && out.back() == '\r') out.pop_back();
+    return true;
+  };
   auto tokens = [](const std::string& s) {
     std::vector<std::string> t; std::string cur;
-    for (char c : s) { if (c == ' ' || c == '\r') { if (!cur.empty()) { t.push_back(cur); cur.clear(); } } else cur.push_back(c); }
+    for (char c : s) { if (c == ' ') { if (!cur.empty()) { t.push_back(cur); cur.clear(); } } else cur.push_back(c); }
     if (!cur.empty()) t.push_back(cur);
     return t;
   };
-  if (!std::getline(f, line)) return false;
-  if (!std::getline(f, line)) return false;
+  if (!next_line(line)) return false;
+  if (!next_line(line)) return false;
   n = (u32)tokens(line).size();
-  std::getline(f, line);
+  next_line(line);
   edges.clear();
-  while (std::getline(f, line)) {
+  while (next_line(line)) {
     auto t = tokens(line);
-    if (t.size() >= 2) edges.push_back({(Node)strtoul(t[0].c_str(), 0, 10), (Node)strtoul(t[1].c_str(), 0, 10)});
+    if (t.size() < 2) continue;
+    Edge e;
+    if (!parse_u32_token(t[0], e.a) || !parse_u32_token(t[1], e.b)) return false;
+    edges.push_back(e);
   }
   return true;
 }

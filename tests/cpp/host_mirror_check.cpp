@@ -1,6 +1,7 @@
 // Test driver of include/directed_scm.hpp: the reference's sample flow (src/bin/sample.rs:80-150) on one
 // .flag file, printed as one line of JSON for tests/test_cpp_host.py.
 //   host_mirror_check selfcheck                      host maths only (no device)
+//   host_mirror_check parse file.flag                read_flag_file only (no device): n, edge count, FNV of the edges
 //   host_mirror_check run file.flag seed nsteps simple(0|1)
 #include <cstdio>
 #include <cstring>
@@ -24,6 +25,13 @@ int main(int argc, char** argv) {
       printf(", ");
       print_vec("relax_de", calc_relax_de({279, 2200, 2743, 2431, 1839, 1054, 379, 64}));
       printf(", \"devices\": %d, \"abi\": %d}\n", fcm_device_count(), fcm_abi_version());
+      return 0;
+    }
+    if (argc >= 3 && !strcmp(argv[1], "parse")) {
+      auto ge = read_flag_file(argv[2]);
+      uint64_t h = 1469598103934665603ULL;
+      for (const Edge& e : ge.second) for (Node x : e) { h ^= x; h *= 1099511628211ULL; }
+      printf("{\"n\": %u, \"nedges\": %zu, \"edges_fnv\": %llu}\n", ge.first, ge.second.size(), (unsigned long long)h);
       return 0;
     }
     if (argc < 6 || strcmp(argv[1], "run")) { fprintf(stderr, "usage: %s selfcheck | run file.flag seed nsteps simple\n", argv[0]); return 2; }

@@ -41,6 +41,43 @@ def fnv(edges):
     return h
 
 
+FLAG_TEXTS = {
+    # name: (file bytes, parses?)  — the reference splits on ' ' only and unwraps the parse (src/io.rs:25-31)
+    "plain": (b"dim 0:\n1 1 1 1\ndim 1:\n0 1 1\n1 2 1\n3 0 1\n", True),
+    "crlf": (b"dim 0:\r\n1 1 1 1\r\ndim 1:\r\n0 1 1\r\n1 2 1\r\n3 0 1\r\n", True),        # str::lines() drops the \r
+    "blank_lines_and_runs_of_spaces": (b"dim 0:\n1  1 1   1 \ndim 1:\n\n0   1 1\n \n1 2\n3 0 0.5 junk\n", True),
+    "no_weights_no_final_newline": (b"dim 0:\n1 1 1 1\ndim 1:\n0 1\n1 2\n3 0", True),
+    "tab_separated": (b"dim 0:\n1 1 1 1\ndim 1:\n0\t1\t1\n", None),   # one token "0\t1\t1": < 2 tokens, line skipped
+    "tab_inside_token": (b"dim 0:\n1 1 1 1\ndim 1:\n0\t1 2 1\n", False),   # token "0\t1" does not parse: reference panics
+}
+
+
+@pytest.mark.parametrize("name", sorted(FLAG_TEXTS))
+def test_flag_reader_tokenises_like_the_reference(name, driver, tmp_path):
+    """include/directed_scm.hpp, the Python mirror and the oracle read a .flag file exactly as src/io.rs:18-35 does:
+    tokens split on ' ' only, a \r before the newline dropped, lines with fewer than two tokens skipped, a token that
+    is not a number is an error (the reference's parse().unwrap() panics)."""
+    data, ok = FLAG_TEXTS[name]
+    f = str(tmp_path / "g.flag")
+    with open(f, "wb") as fh:
+        fh.write(data)
+    p = subprocess.run([driver, "parse", f], capture_output=True, text=True)
+    if ok is False:
+        assert p.returncode != 0
+        with pytest.raises(ValueError):
+            ds.read_flag_file(f)
+        with pytest.raises(Exception):
+            orc.read_flag_file(f)
+        return
+    got = json.loads(p.stdout)
+    n_py, e_py = ds.read_flag_file(f)
+    n_or, e_or = orc.read_flag_file(f)
+    want_edges = [] if ok is None else [(0, 1), (1, 2), (3, 0)]
+    assert n_py == n_or == got["n"] == 4
+    assert e_py.tolist() == [list(x) for x in want_edges] and e_or.tolist() == e_py.tolist()
+    assert got["nedges"] == len(want_edges) and got["edges_fnv"] == fnv(e_py)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,seed,steps,simple", [("c2_chunglu_279", 3, 4000, 1), ("c2_chunglu_279", 4, 2500, 0),
                                                     ("counterexample_seo_greedy_5_start", 0, 3000, 1)])

@@ -405,6 +405,20 @@ def test_checkpoint_restore_resumes_exactly(simple, ctx, graphs, tmp_path):
     o0 = orc.Sampler(n, e, 99, 0.01, move_weights=mw)     # the neighbours of the restored chain are untouched
     o0.steps(500, trace=False)
     compare_chain(s2, 0, o0)
+    # a checkpoint taken under other settings is refused instead of changing the neighbours' bounds
+    s3 = fcm.initialize_new_sampler(ctx, n, e, [5, 6], target_relaxation=0.05, simple=simple)
+    b3 = (list(s3.bounds.flag_count_min), list(s3.bounds.flag_count_max))
+    with pytest.raises(ValueError):
+        fcm.load_state(f, s3, chain=0)
+    assert (list(s3.bounds.flag_count_min), list(s3.bounds.flag_count_max)) == b3
+    assert fcm.load_state(f, s3, chain=0, adopt_settings=True) == 7
+    assert list(s3.bounds.flag_count_min) == list(s.bounds.flag_count_min) and s3.sample_distance == s.sample_distance
+    s3.close()
+    if simple:
+        s4 = fcm.initialize_new_sampler(ctx, n, e, [5], simple=False)
+        with pytest.raises(ValueError):
+            fcm.load_state(f, s4, chain=0)              # other move distribution
+        s4.close()
     bad = dict(ck)
     bad["edges"] = ck["edges"].copy()
     bad["edges"][0] = [0, 0]

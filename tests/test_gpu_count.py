@@ -160,6 +160,36 @@ def test_for_each_cell_matches_oracle_rows(name, dmin, dmax, ctx, graphs):
     assert seen == [[int(x) for x in r if x != 0xFFFFFFFF] for r in orc.cells(n, e, 2, 2)]
 
 
+def bidirected_clique(m):
+    return np.array([(a, b) for a in range(m) for b in range(m) if a != b], dtype=np.uint32)
+
+
+def transitive_tournament(m):
+    return np.array([(a, b) for a in range(m) for b in range(a + 1, m)], dtype=np.uint32)
+
+
+@pytest.mark.parametrize("case", ["k9_bidirected", "tournament_40", "dense_random_48"])
+def test_for_each_cell_dense_graphs_never_drop_a_subtree(case, ctx):
+    """A popped batch whose children overflow the per-warp stack must still emit every cell below it
+    (the batch goes through the per-thread walk, which emits too).  Dense graphs: ~k children per entry."""
+    if case == "k9_bidirected":
+        n, e, dmax = 9, bidirected_clique(9), 4
+    elif case == "tournament_40":
+        n, e, dmax = 40, transitive_tournament(40), 4
+    else:
+        n, e, dmax = 48, rand_graph(48, 0.55, 11, pdouble=0.5), 4
+    g = ds.DeviceGraph(ctx, n, e)
+    got = g.cells(0, dmax)
+    want = orc.cells(n, e, 0, dmax)
+    assert got.shape == want.shape
+    assert np.array_equal(got, want)
+    fc = g.flagser_count()
+    dims = (got != 0xFFFFFFFF).sum(1) - 1
+    for d in range(dmax + 1):
+        assert int((dims == d).sum()) == (fc[d] if d < len(fc) else 0), d
+    g.close()
+
+
 def test_for_each_cell_local_subgraph_like_all_cxs(ctx):
     # the use in src/bin/all_cxs.rs:57-64: 2-cells of a small induced neighbourhood graph, as sorted sets
     e = rand_graph(24, 0.4, 5, pdouble=0.2)

@@ -102,17 +102,41 @@ def test_all_le_zero_padding():
         assert ds.all_le(a, b) == want
 
 
-def test_intersect_sorted_reference_cases():
-    # the reference's only unit test, src/util.rs:107-156
+# the reference's only unit test, `test_intersect` (src/util.rs:107-156), literally: its 8 (a, b, expected) cases in order
+REFERENCE_TEST_INTERSECT = [
+    ([1, 2, 5, 8, 9], [0, 2, 2, 2, 3, 4, 5, 9, 9, 9], [2, 5, 9]),       # :109-112
+    ([0, 2, 2, 2, 3, 4, 5, 9, 9, 9], [1, 2, 5, 8, 9], [2, 5, 9]),       # :114-117
+    ([], [0, 2, 2, 2, 3, 4, 5, 9, 9, 9], []),                           # :119-122
+    ([2], [3], []),                                                     # :124-127
+    ([2], [0, 1, 2, 3, 4, 5], [2]),                                     # :129-134
+    ([0], [0, 1, 2, 3, 4, 5], [0]),                                     # :136-141
+    ([0], [0, 1, 2, 3, 4, 5], [0]),                                     # :143-148 (the reference repeats the case)
+    ([5], [0, 1, 2, 3, 4, 5], [5]),                                     # :150-155
+]
+
+
+def oracle_intersect(x, y):
+    xa, ya = np.asarray(x, dtype=np.uint32), np.asarray(y, dtype=np.uint32)
+    out = np.zeros(16, dtype=np.uint32)
+    k = orc.lib().orc_intersect_sorted(orc._p(xa), len(x), orc._p(ya), len(y), orc._p(out))
+    return [int(v) for v in out[:k]]
+
+
+def test_intersect_sorted_reference_vectors():
+    """Golden vectors the reference itself holds (src/util.rs:107-156): the oracle's intersect_sorted gives the
+    reference's expected output on each, twice in a row where the reference calls it twice (:131-133)."""
+    assert len(REFERENCE_TEST_INTERSECT) == 8
+    for a, b, want in REFERENCE_TEST_INTERSECT:
+        assert oracle_intersect(a, b) == want
+        assert oracle_intersect(a, b) == oracle_intersect(a, b)
+
+
+def test_intersect_sorted_more_cases():
     a = [1, 2, 5, 8, 9]
     b = [0, 2, 2, 2, 3, 4, 5, 9, 9, 9]
-    cases = [(a, b, [2, 5, 9]), (b, a, [2, 5, 9]), (a, [], []), ([], a, []), ([1], a, [1]), (a, [1], [1]),
-             ([9], a, [9]), (a, [9], [9])]
+    cases = [(a, [], []), ([], a, []), ([1], a, [1]), (a, [1], [1]), ([9], a, [9]), (a, [9], [9]), ([2, 5], b, [2, 5])]
     for x, y, want in cases:
-        xa, ya = np.asarray(x, dtype=np.uint32), np.asarray(y, dtype=np.uint32)
-        out = np.zeros(16, dtype=np.uint32)
-        k = orc.lib().orc_intersect_sorted(orc._p(xa), len(x), orc._p(ya), len(y), orc._p(out))
-        assert [int(v) for v in out[:k]] == want
+        assert oracle_intersect(x, y) == want
 
 
 @pytest.mark.parametrize("name", ["counterexample_seo_greedy_5_start", "bug_calc_relax_de", "c2_chunglu_279",
