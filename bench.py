@@ -31,9 +31,51 @@ sys.path.insert(0, ROOT)
 
 METRIC = "mcmc_proposals_per_sec"
 UNIT = "proposals/s"
-CHAIN_DRAM_BYTES_PER_PROPOSAL = 4326       # measured, see roofline.traffic_source
-RECOUNT_DRAM_BYTES_C4 = 10.42e9 + 0.47e9   # ncu --set full of count_local_kernel<8> on C4, one GPU (profiles/r01_d_count_local_stack.ncu.txt)
 N_C3, W_C3 = 2000, 32                      # vertices, 64-bit words per adjacency row (ceil(n/64))
+# ncu --set full summaries of the kernels this file times (tools/ncu_summary.py output, committed); the roofline's
+# `traffic` and the issue-slot figures are read from them at run time, nothing is hard-coded here
+CHAIN_CAPTURE = os.path.join("profiles", "r02_chain_step.ncu.txt")
+COUNT_CAPTURE = os.path.join("profiles", "r02_count_local.ncu.txt")
+RANDSECTOR = os.path.join("profiles", "r02_randsector.json")
+
+
+def read_capture(relpath):
+    """-> dict of the raw ncu metrics of a committed capture summary (value in base units) + its '# key=value' header
+    fields, or None when the file is absent."""
+    path = os.path.join(ROOT, relpath)
+    if not os.path.exists(path):
+        return None
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12, "ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0}
+    out = {"file": relpath}
+    with open(path) as f:
+        for ln in f:
+            ln = ln.strip()
+            if ln.startswith("#"):
+                for tok in ln[1:].split():
+                    if "=" in tok:
+                        k, v = tok.split("=", 1)
+                        try:
+                            out[k] = float(v)
+                        except ValueError:
+                            out[k] = v
+                continue
+            parts = ln.split(",")
+            if len(parts) == 3 and parts[0] and not parts[0].startswith("=="):
+                try:
+                    out[parts[0]] = float(parts[2]) * scale.get(parts[1], 1.0)
+                except ValueError:
+                    pass
+    return out
+
+
+def random_sector_peak():
+    """measured ceiling of independent 32-byte-sector reads out of HBM (tools/randsector.cu), G sectors/s"""
+    try:
+        with open(os.path.join(ROOT, RANDSECTOR)) as f:
+            d = json.load(f)
+        return max(r["gsectors_per_s"] for r in d["rows"])
+    except Exception:
+        return None
 
 
 def env_int(k, d):
@@ -234,6 +276,29 @@ def workload_config(args, ngpu):
 # ------------------------------------------------------------------------------------------------
 # the CUDA path
 # ------------------------------------------------------------------------------------------------
+def oracle_chain_after(n, e, seed, nproposals, move_weights=(0.5, 0.5, 0.0, 0.0)):
+    """state of the oracle's chain `seed` after nproposals (checker for parity_spot_check)"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding as orc
+    o = orc.Sampler(n, e, int(seed), 0.01, move_weights=move_weights)
+    o.steps(int(nproposals), trace=False)
+    return o.read()
+
+
+def cpu_single_chain_rate(n, e, move_weights, budget_s=2.0):
+    """the oracle port's proposals/s for ONE chain on one host core (the reference runs a chain single-threaded)"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding as orc
+    o = orc.Sampler(n, e, 0, 0.01, move_weights=move_weights)
+    t0 = time.perf_counter()
+    o.steps(500, trace=False)
+    r = 500 / max(time.perf_counter() - t0, 1e-6)
+    per = max(int(r * budget_s), 500)
+    t0 = time.perf_counter()
+    o.steps(per, trace=False)
+    return per / (time.perf_counter() - t0), per
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -245,6 +310,8 @@ def main():
     ap.add_argument("--no-recount", action="store_true", help="skip the C4 recount leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-clique-mix", action="store_true", help="skip the default-move-mix leg")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C2 / C3-1024 lines")
+    ap.add_argument("--no-spot-check", action="store_true", help="skip the oracle comparison of two timed chains")
     ap.add_argument("--recount-graph", default="c4_geo_31346")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
@@ -262,6 +329,7 @@ def main():
 
     import torch
     import flag_complex_mcmc_b200 as fcm
+    from flag_complex_mcmc_b200 import directed_scm as ds
     from flag_complex_mcmc_b200 import sharding
     from tools import synth
 
@@ -290,15 +358,18 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    def sum_over_ranks(x):
+    def exchange(blob):
+        """host transport of the fcm_comm handles: all_gather over the bench's process group"""
         if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+            return [blob]
+        mine = torch.from_numpy(np.asarray(blob, dtype=np.uint8).copy()).cuda()
+        allh = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allh, mine)
+        return [t.cpu().numpy() for t in allh]
 
     ctx = fcm.Context(local)
     peak, peak_src = measured_peak()
+    rs_peak = random_sector_peak()
 
     # ---- chains --------------------------------------------------------------------------------
     n, e = synth.config("c3_er_2000")
@@ -369,8 +440,50 @@ def main():
     e2e_value = total_props / (e2e_ms * 1e-3)
     info = s.info()
     info.update(s.index_info())
+
+    # ---- parity spot check: two of the TIMED chains (state after every step above) against the oracle ----
+    spot = None
+    if rank == 0 and not args.no_spot_check and not args.no_cpu:
+        try:
+            spot = "ok"
+            which = [0, min(args.chains - 1, 1777)]
+            res = {}
+            got = {k: s.read(k) for k in which}               # the handle is read from this thread only
+
+            def chk(k):
+                r_ = got[k]
+                w_ = oracle_chain_after(n, e, int(seeds[k]), r_["sampled"])
+                res[k] = (r_["flag_count"] == w_["flag_count"] and r_["rng"] == w_["rng"] and r_["accepted"] == w_["accepted"]
+                          and np.array_equal(r_["edges"], w_["edges"]), r_["sampled"])
+            th = [threading.Thread(target=chk, args=(k,)) for k in which]
+            for t in th:
+                t.start()
+            for t in th:
+                t.join()
+            if not all(res.get(k, (False,))[0] for k in which):
+                spot = "MISMATCH on chain(s) %s" % [k for k in which if not res.get(k, (False,))[0]]
+            spot_what = "chains %s (seeds %s) after %d proposals each: flag_count, xoshiro state, accepted and the edge container in order equal the oracle's" % (
+                which, [int(seeds[k]) for k in which], res[which[0]][1])
+        except Exception as ex:                                 # noqa: BLE001
+            spot, spot_what = "error: %r" % (ex,), ""
     s.close()
 
+    cap = read_capture(CHAIN_CAPTURE)
+    traffic = None
+    traffic_src = "no capture of the timed kernel committed yet (%s)" % CHAIN_CAPTURE
+    rs = None
+    if cap and "dram__bytes_read.sum" in cap and cap.get("chains") and cap.get("proposals"):
+        bpp = (cap["dram__bytes_read.sum"] + cap["dram__bytes_write.sum"]) / (cap["chains"] * cap["proposals"])
+        traffic = bpp * float(args.chains) * P
+        traffic_src = ("%s: ncu --set full of chain_step_kernel, %d chains x %d proposals: dram read %.3f GB + write %.3f GB = %.0f B/proposal, "
+                       "scaled to this launch" % (cap["file"], cap["chains"], cap["proposals"], cap["dram__bytes_read.sum"] / 1e9,
+                                                  cap["dram__bytes_write.sum"] / 1e9, bpp))
+        if rs_peak:
+            # HBM moves 64-byte granules per missing sector pair: accesses = traffic / 64
+            acc_per_s = bpp / 64.0 * float(args.chains) * P / (kern_ms * 1e-3) / 1e9
+            rs = {"bound": "hbm random access", "achieved": acc_per_s, "peak": rs_peak, "unit": "G accesses/s", "frac": acc_per_s / rs_peak,
+                  "what": "DRAM accesses of the launch (measured bytes / 64 B) per second against the measured ceiling of independent "
+                          "random 32-byte-sector reads (tools/randsector.cu, %s): the chain's state is touched 4 bytes at a time" % RANDSECTOR}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": ngpu, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -380,18 +493,57 @@ def main():
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "chain_step_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": CHAIN_DRAM_BYTES_PER_PROPOSAL * float(args.chains) * P,
-                     "traffic_source": "ncu --set full of chain_step_kernel (profiles/r01_b_chain_step_clique_index.ncu.txt): "
-                                       "dram read 8.177 GB + write 0.682 GB for 4096 x 500 proposals = %d B/proposal, scaled to this launch" % CHAIN_DRAM_BYTES_PER_PROPOSAL,
+                     "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                      "peak_source": peak_src,
                      "model": "8*W*K + 4*(K-2) + 16 bytes per non-empty proposal (SURVEY 8d), W=%d, mean K=%.2f, "
                               "non-empty fraction %.3f (both measured over the instrumented warm-up steps of the same chains)" % (W_C3, meanK, nonempty_frac),
-                     "kernel_ms": kern_ms},
+                     "kernel_ms": kern_ms,
+                     "issue_active_pct": cap.get("smsp__issue_active.avg.pct_of_peak_sustained_active") if cap else None,
+                     "random_access": rs},
         "acceptance_ratio": accepted / (float(args.chains) * P * args.steps),
         "bytes_per_chain": info["bytes_per_chain"],
         "value_instrumented": value_instr,
         "clique_index": {"built": info["have_index"], "bytes": info["index_bytes"]},
+        "parity": "bit-exact against oracle/ (C++ restatement); the oracle's counts are pinned by known answers, its trajectory "
+                  "semantics are UNPINNED (reference not buildable here: no rustc, un-vendored crates) - DESIGN.md 4",
     }
+    if spot is not None:
+        line["parity_spot_check"] = spot
+        line["parity_spot_check_what"] = spot_what
+
+    # ---- the other BASELINE.json configs: C1 (reference fixture, 1 chain), C2 (1 chain), C3 (1024 chains) -------
+    if not args.no_configs and ngpu == 1:
+        z = np.load(os.path.join(ROOT, "tests", "golden", "fixtures.npz"))
+        cfgs = {}
+        cases = [("c1", 200, z["counterexample_seo_greedy_5_start"].reshape(-1, 2).astype(np.uint32), 1,
+                  "flag_file_examples/counterexample_seo_greedy_5_start.flag, `sample -s 0` (1 chain, step = sample_distance proposals)"),
+                 ("c2", 279, z["c2_chunglu_279"].reshape(-1, 2).astype(np.uint32), 1, "C. elegans-shaped Chung-Lu graph (279 nodes, 2200 edges), 1 chain"),
+                 ("c3_1024", n, e, 1024, "ER n=2000 p=0.05 (C3), 1024 batched chains, step = %d proposals per chain" % P)]
+        for name, cn, ce, nch, what in cases:
+            entry = {"workload": what, "chains": nch}
+            for mixname, simple in (("simple", True), ("default_mix", False)):
+                sc_ = fcm.initialize_new_sampler(ctx, cn, ce, list(range(nch)), target_relaxation=0.01, simple=simple)
+                Pc = sc_.sample_distance if nch == 1 else (P if simple else max(P // 10, 1))
+                Pc = min(Pc, 100000)
+                sc_.set_stats(False)
+                sc_.step(Pc)
+                ctx.synchronize()
+                ctx.timer_begin()
+                for _ in range(2):
+                    sc_.step(Pc)
+                cms = ctx.timer_end()
+                sc_.status()
+                v = float(nch) * Pc * 2 / (cms * 1e-3)
+                entry[mixname] = {"value": v, "unit": UNIT, "proposals_per_chain_per_step": Pc, "ms_per_step": cms / 2,
+                                  "us_per_proposal_per_chain": cms * 1e3 / (2 * Pc)}
+                if rank == 0 and not args.no_cpu:
+                    mw = ds.MOVE_DISTRIBUTION_SIMPLE if simple else ds.MOVE_DISTRIBUTION
+                    cv, cnt = cpu_single_chain_rate(cn, ce, mw, 1.5)
+                    entry[mixname]["cpu_baseline"] = {"value": cv, "unit": UNIT, "cores": 1, "kind": "port",
+                                                      "sample": "one chain x %d proposals on one host core (oracle/), per-chain rate" % cnt}
+                sc_.close()
+            cfgs[name] = entry
+        line["configs"] = cfgs
 
     # ---- default move mix [0.1,0.1,0.6,0.2] (clique_permute / clique_swap included, src/bin/sample.rs:17) ----
     if not args.no_clique_mix:
@@ -418,55 +570,89 @@ def main():
                                "what": "same graph and chains with the CLI's default move mix; clique moves run on the cold path"}
         sc.close()
 
-    # ---- full recount (C4), sharded by source vertex + allreduce --------------------------------
+    # ---- full recount (C4), sharded by source vertex; the all-reduce is part of the library call and of the timed region ----
     if not args.no_recount:
         n4, e4 = synth.config(args.recount_graph)
         g = fcm.DeviceGraph(ctx, n4, e4)
         W4 = (n4 + 63) // 64
-        for _ in range(max(args.warmup, 1)):
-            g.count_shard(rank, ngpu)
-        barrier()
+        NC = max(args.steps, 50)                               # >= 50 counts: long enough for the clock sampler
+
+        def time_counts(fn):
+            for _ in range(max(args.warmup, 1)):
+                fn()
+            g.status()
+            barrier()
+            ctx.timer_begin()
+            for _ in range(NC):
+                fn()
+            t = ctx.timer_end()
+            g.status()
+            barrier()
+            return max_over_ranks(t) / NC
+
+        ms_kernel_only = time_counts(lambda: g.count_async(rank, ngpu))      # this rank's shard, no collective
+        comm = fcm.Comm(ctx, rank, ngpu, fcm.COMM_PEER, exchange=exchange if ngpu > 1 else None)
         l0 = ctx.launches
         rclk = Clocks(local)
         rclk.start()
-        ctx.timer_begin()
-        for _ in range(max(args.steps, 50)):                   # >= 50 counts: long enough for the clock sampler
-            g.count_async(rank, ngpu)
-        rms = ctx.timer_end() * args.steps / max(args.steps, 50)
-        rl = (ctx.launches - l0) * args.steps // max(args.steps, 50)
+        ms_fused = time_counts(lambda: g.count_allreduce_async(comm))       # count + all-reduce in ONE launch (last-CTA epilogue over NVLink)
+        rl = (ctx.launches - l0) // (NC + max(args.warmup, 1))
         rclocks = rclk.stop()
-        barrier()
-        part = g.count_shard(rank, ngpu)
-        tot = torch.from_numpy(part.astype(np.int64)).cuda()
-        if dist is not None:
-            dist.all_reduce(tot)                               # int64 per-dimension counts over NCCL/NVLink
-        counts = [int(x) for x in tot.cpu().numpy()]
+        ms_nccl, nccl_err = None, None
+        if ngpu > 1:
+            try:
+                ncomm = fcm.Comm(ctx, rank, ngpu, fcm.COMM_NCCL, exchange=exchange)
+                ms_nccl = time_counts(lambda: g.count_allreduce_async(ncomm))   # count kernel, then ncclAllReduce on the same stream
+                ncomm.close()
+            except Exception as ex:                                 # noqa: BLE001
+                nccl_err = repr(ex)
+        tot = g.count_allreduce(comm)                          # every rank holds the whole graph's vector
+        counts = [int(x) for x in tot]
         while counts and counts[-1] == 0:
             counts.pop()
         simplices = sum(counts)
-        rms_max = max_over_ranks(rms)
-        rvalue = simplices * args.steps / (rms_max * 1e-3)
+        rvalue = simplices / (ms_fused * 1e-3)
         rbytes = 8 * W4 * simplices                            # dense-row model, whole graph
-        # e2e: the precedent C ABI fcm_count_unweighted with the host edge list (H2D + build + count + D2H)
+        # e2e through the library's sharded call with HOST buffers: every rank uploads the edge list, builds its rows +
+        # CSR, counts its shard, all-reduces inside the kernel and reads the vector back
+        barrier()
         t0 = time.perf_counter()
-        if rank == 0:
-            c2 = fcm.flagser_count(n4, e4)
-            assert c2 == counts, (c2, counts)
-        re2e = time.perf_counter() - t0
+        g2 = fcm.DeviceGraph(ctx, n4, e4)
+        c2 = ds.trim(g2.count_allreduce(comm))
+        re2e = max_over_ranks(time.perf_counter() - t0)
+        g2.close()
+        assert c2 == counts, (c2, counts)
+        ccap = read_capture(COUNT_CAPTURE)
+        rtraffic, issue, winst = None, None, None
+        if ccap and ngpu == 1 and args.recount_graph == ccap.get("graph", "c4_geo_31346"):
+            rtraffic = ccap.get("dram__bytes_read.sum", 0.0) + ccap.get("dram__bytes_write.sum", 0.0)
+            issue = ccap.get("smsp__issue_active.avg.pct_of_peak_sustained_active")
+            winst = ccap.get("smsp__inst_executed.sum")
         line["recount"] = {
             "metric": "full_recount_simplices_per_sec", "value": rvalue, "unit": "simplices/s", "graph": args.recount_graph,
-            "n": n4, "nedges": int(e4.shape[0]), "flag_count": counts, "simplices": simplices, "ms_per_count": rms_max / max(args.steps, 1),
-            "gpu_launches": int(rl), "clocks": rclocks, "sharding": "source vertices, degree-descending round-robin over %d rank(s) + allreduce(sum) of uint64[32]" % ngpu,
-            "e2e": {"value": simplices / re2e if rank == 0 else None, "unit": "simplices/s", "h2d_bytes_per_step": int(e4.nbytes),
-                    "d2h_bytes_per_step": 8 * len(counts), "what": "fcm_count_unweighted(host edge list) on one GPU: upload, build bit rows + CSR, count, download"},
-            "roofline": {"bound": "hbm", "kernel": "count_local_kernel", "achieved": rbytes * args.steps / (rms_max * 1e-3) / 1e9 / ngpu,
-                         "peak": peak, "unit": "GB/s", "frac": rbytes * args.steps / (rms_max * 1e-3) / 1e9 / ngpu / peak,
-                         "traffic": RECOUNT_DRAM_BYTES_C4 if (ngpu == 1 and args.recount_graph == "c4_geo_31346") else None,
-                         "peak_source": peak_src,
-                         "model": "8*ceil(n/64) bytes per enumerated simplex (dense-row model, SURVEY 8d). The tile kernel gathers each "
-                                  "source's k x k bits once and intersects in shared memory, so the fraction exceeds 1 by design: "
-                                  "measured DRAM traffic is ~1 % of the model (traffic key); the kernel is issue-bound (DESIGN.md 3.2)"},
+            "n": n4, "nedges": int(e4.shape[0]), "flag_count": counts, "simplices": simplices,
+            "ms_per_count": ms_fused, "ms_per_count_kernel_only": ms_kernel_only, "ms_per_count_nccl": ms_nccl, "nccl_error": nccl_err,
+            "allreduce": "inside libfcm.so and inside the timed region: fcm_graph_count_allreduce_async - the count kernel's last CTA adds the "
+                         "rank's u64[33] into every rank's window with system-scope atomics over NVLink and waits for the others (one launch per "
+                         "count); ms_per_count_nccl = same count followed by ncclAllReduce(u64[33]) on the stream; ms_per_count_kernel_only = no collective",
+            "gpu_launches": int(rl), "clocks": rclocks,
+            "sharding": "source vertices, degree-descending round-robin over %d rank(s)" % ngpu,
+            "e2e": {"value": simplices / re2e, "unit": "simplices/s", "h2d_bytes_per_step": int(e4.nbytes),
+                    "d2h_bytes_per_step": 8 * 33, "seconds": re2e,
+                    "what": "DeviceGraph(host edge list) + count_allreduce on every rank: upload, build bit rows + CSR, count the shard, all-reduce, download"},
+            "roofline": {"bound": "issue", "kernel": "count_local_kernel",
+                         "dense_row_model": {"achieved": rbytes / (ms_fused * 1e-3) / 1e9 / ngpu, "peak": peak, "unit": "GB/s",
+                                             "frac": rbytes / (ms_fused * 1e-3) / 1e9 / ngpu / peak,
+                                             "note": "8*ceil(n/64) bytes per enumerated simplex (SURVEY 8d). NOT a bound for this kernel: it gathers each "
+                                                     "source's k x k bits once and intersects in shared memory, so this exceeds 1 by design"},
+                         "dram": {"traffic": rtraffic, "achieved": (rtraffic / (ms_fused * 1e-3) / 1e9) if rtraffic else None, "peak": peak, "unit": "GB/s",
+                                  "frac": (rtraffic / (ms_fused * 1e-3) / 1e9 / peak) if rtraffic else None,
+                                  "compulsory_bytes": 8 * (W4 + (W4 & 1)) * n4 + 4 * int(e4.shape[0])},
+                         "issue": {"warp_instructions": winst, "issue_active_pct": issue,
+                                   "warp_instructions_per_simplex": (winst / simplices) if winst else None},
+                         "source": ccap["file"] if ccap else None, "peak_source": peak_src},
         }
+        comm.close()
         g.close()
 
     # ---- CPU baseline beside it (rank 0, N=1 only) ---------------------------------------------
@@ -480,10 +666,10 @@ def main():
                                 "sample": "%d chains (one per host thread) x %d proposals on the C3 graph, %.1f s; C++ restatement "
                                           "of the reference CPU path (oracle/), the Rust crate cannot be built here" % (cores, cnt // cores, dt)}
         if not args.no_recount:
-            rv, rs, rdt = cpu_recount(n4, e4, cores, 4)
+            rv, rs_, rdt = cpu_recount(n4, e4, cores, 4)
             line["recount"]["cpu_baseline"] = {"value": rv, "unit": "simplices/s", "cores": cores, "kind": "port",
                                                "sample": "every 4th source vertex (degree-descending order) of %s: %d simplices "
-                                                         "in %.2f s incl. bit-matrix build" % (args.recount_graph, rs, rdt)}
+                                                         "in %.2f s incl. bit-matrix build" % (args.recount_graph, rs_, rdt)}
     ctx.close()
     if rank == 0:
         emit(line)

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Summarise an .ncu-rep (read here, no GPU): key raw metrics + top source lines by stall samples.
-usage: python tools/ncu_summary.py gpurun_out/prof.ncu-rep [nlines]"""
+usage: python tools/ncu_summary.py gpurun_out/prof.ncu-rep [nlines] [key=value ...]
+key=value pairs are written as a '# key=value ...' header line (bench.py reads e.g. chains=4096 proposals=500 from it)."""
 import csv
 import io
 import subprocess
@@ -20,7 +21,10 @@ WANT = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
 
 def main():
     rep = sys.argv[1]
-    nl = int(sys.argv[2]) if len(sys.argv) > 2 else 25
+    nl = int(sys.argv[2]) if len(sys.argv) > 2 and "=" not in sys.argv[2] else 25
+    kv = [a for a in sys.argv[2:] if "=" in a]
+    if kv:
+        print("# " + " ".join(kv))
     raw = subprocess.run(['ncu', '-i', rep, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units = rows[0], rows[1]
