@@ -33,6 +33,9 @@
 
 #include <algorithm>
 
+#ifndef FCM_CHAIN_MINBLOCKS
+#define FCM_CHAIN_MINBLOCKS 7              // 7 blocks x 4 warps = 28 chains per SM: 4096 chains fill 148 SMs in one wave (72 registers per thread)
+#endif
 #define FULL 0xffffffffu
 #define MAXL_CHAIN (FCM_MAXD - 1)     // level l holds candidates for vertex index l+1
 static_assert(FCM_MAXD == 32, "flag_count is held one entry per lane");
@@ -1296,11 +1299,435 @@ __device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned ch
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Index hot path, one proposal (flip or double-edge move on lists of <= 32 common neighbours).
+//
+// Built for the 72 registers a thread has when 28 chains share an SM:
+//   * the two move kinds are separate code (a flip never carries the second pair's state);
+//   * the orientation words a pair's triangles / 4-cliques name are copied global -> shared with cp.async
+//     (LDGSTS: the data never sits in registers while the warp waits); between issue and finish a lane keeps
+//     two packed words per pair (the bit positions of its entries), nothing else;
+//   * LOOK-AHEAD.  Simple moves keep |E| and the number of double pairs, so once proposal t has made its last
+//     draw, the first draws of proposal t+1 (move kind, container index) are known.  They are made right
+//     there and the container entries they name are fetched with cp.async while t is being counted (level 1);
+//     when those have landed, the pair records and the orientation word of the sampled slot follow (level 2).
+//     t's own container / orientation updates are patched into the staged values by the update stage (or the
+//     stage is dropped when a patched entry invalidates level 2), so the look-ahead is exact, never a guess.
+//     The RNG state with the look-ahead draws lives beside the committed one; leaving the hot stretch (end of
+//     launch, cold proposal) drops the look-ahead and keeps the committed state.
+// Returns 0 (proposal done), 1 (parked for cold_step) or an FCM_E* code.
+// ---------------------------------------------------------------------------------------------------
+enum { LA_VALID = 0, LA_L2 = 1, LA_SLOT = 2, LA_DPAIR = 3, LA_KIND = 4, LA_IDX = 5, LA_DIDX = 6, LA_ORIA = 8, LA_ORID = 9, LA_WORDS = 16 };   // [LA_KIND..+3] is written as one uint4
+#define ST_STAGE 0                     // u32[2][4][32]  staged orientation words: pair A, pair D; rows wu, wv, w0, w1
+#define ST_LA 1024                     // u32[LA_WORDS]  the look-ahead of the next proposal
+#define ST_RNGLA 1088                  // u64[4]         RNG state behind the look-ahead draws
+#define ST_PINFO 1120                  // uint4[4]       records of the next proposal's pairs: A (2), D (2)
+#define ST_BYTES 1184
+static_assert(ST_BYTES <= 8 * 8 + 3 * FCM_MAXD * 8 + 8 * 4 + FCM_MAXEDIT * 2 * 4, "the staging block overlays the full path's arrays");
+
+__device__ __forceinline__ void cp_async16(u32 saddr, const void* g) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
+}
+// move kind of a proposal from one draw: WeightedIndex<f64>::sample (src/lib.rs:210)
+__device__ __forceinline__ int draw_kind(const EnsParams& p, Rng& g) {
+  const u64 r = g.next();
+  const double v = __longlong_as_double((long long)((r >> 12) | 0x3ff0000000000000ULL)) - 1.0;
+  const double chosen = __dadd_rn(__dmul_rn(v, p.scale), 0.0);
+  return (p.cum[0] <= chosen) + (p.cum[1] <= chosen) + (p.cum[2] <= chosen);
+}
+// every load of a pair: static entries into registers (kept packed: bit positions only), the orientation words
+// they name straight into shared memory.  pk0 = (sU & 31) | (sV & 31) << 5, pk1 = low 15 bits of e0 | of e1 << 15.
+__device__ __forceinline__ void stage_issue(const EnsParams& p, const u32* ori, u32 o, int c, u32 k4o, int m, bool uBig,
+                                            int lane, u32* stage, u32& pk0, u32& pk1) {
+  pk0 = 0; pk1 = 0;
+  const u32 sbase = (u32)__cvta_generic_to_shared(stage + lane);
+  if (lane < c) {
+    const uint2 t = __ldg(&p.tri[o + lane]);
+    const u32 sU = uBig ? t.x : t.y, sV = uBig ? t.y : t.x;
+    cp_async4(sbase, &ori[sU >> 5]);
+    cp_async4(sbase + 128, &ori[sV >> 5]);
+    pk0 = (sU & 31u) | ((sV & 31u) << 5);
+  }
+  if (lane < m) {
+    const u32 e0 = __ldg(&p.k4[k4o + lane]);
+    cp_async4(sbase + 256, &ori[e0 >> 15]);
+    pk1 = e0 & 0x7fffu;
+  }
+  if (lane + 32 < m) {
+    const u32 e1 = __ldg(&p.k4[k4o + 32 + lane]);
+    cp_async4(sbase + 384, &ori[e1 >> 15]);
+    pk1 |= (e1 & 0x7fffu) << 15;
+  }
+}
+// packed entry pe = (slot & 31) << 10 | j << 5 | i, w = the orientation word of that slot
+__device__ __forceinline__ void k4_scatter_packed(u32 pe, u32 w, u32* A32) {
+  const u32 sb = pe >> 10, i = pe & 31, j = (pe >> 5) & 31;
+  const u32 two = w >> (sb & 30), d = sb & 1;
+  if ((two >> d) & 1u) atomicOr(&A32[i], 1u << j);
+  if ((two >> (d ^ 1)) & 1u) atomicOr(&A32[j], 1u << i);
+}
+// staged words -> A32[i] = { j : C[i] -> C[j] } and the four relation masks.  dropslot: a directed slot the view
+// must not contain (the double move's leaving edge while the coming edge is counted), FCM_NONE for none.
+__device__ __forceinline__ G32 stage_finish(const EnsParams& p, const u32* ori, int c, u32 k4o, int m, const u32* stage, u32 pk0,
+                                            u32 pk1, u32 dropslot, u32 o, bool uBig, u32* A32, int lane) {
+  A32[lane] = 0;
+  __syncwarp();
+  // the staged words do not say which word they are: a lane finds out from its entries only when a drop is asked for
+  u32 wu = 0, wv = 0;
+  if (lane < c) { wu = stage[lane]; wv = stage[32 + lane]; }
+  u32 w0 = lane < m ? stage[64 + lane] : 0u, w1 = lane + 32 < m ? stage[96 + lane] : 0u;
+  if (dropslot != FCM_NONE) {
+    const u32 dw = dropslot >> 5, dm = ~(1u << (dropslot & 31));
+    if (lane < c) {
+      const uint2 t = __ldg(&p.tri[o + lane]);
+      const u32 sU = uBig ? t.x : t.y, sV = uBig ? t.y : t.x;
+      if ((sU >> 5) == dw) wu &= dm;
+      if ((sV >> 5) == dw) wv &= dm;
+    }
+    if (lane < m && (__ldg(&p.k4[k4o + lane]) >> 15) == dw) w0 &= dm;
+    if (lane + 32 < m && (__ldg(&p.k4[k4o + 32 + lane]) >> 15) == dw) w1 &= dm;
+  }
+  if (lane < m) k4_scatter_packed(pk1 & 0x7fffu, w0, A32);
+  if (lane + 32 < m) k4_scatter_packed(pk1 >> 15, w1, A32);
+  for (int t = 64 + lane; t < m; t += 32) {
+    const u32 e = __ldg(&p.k4[k4o + t]);
+    u32 w = __ldcg(&ori[e >> 15]);
+    if (dropslot != FCM_NONE && (e >> 15) == (dropslot >> 5)) w &= ~(1u << (dropslot & 31));
+    k4_scatter(e, w, A32);
+  }
+  const u32 bu = pk0 & 31u, bv = pk0 >> 5;
+  const u32 tu = wu >> (bu & 30), tv = wv >> (bv & 30);               // lanes past c hold 0: never vote
+  const u32 du = bu & 1, dv = bv & 1;
+  G32 g;
+  g.inU = __ballot_sync(FULL, (tu >> du) & 1u);
+  g.outU = __ballot_sync(FULL, (tu >> (du ^ 1)) & 1u);
+  g.inV = __ballot_sync(FULL, (tv >> dv) & 1u);
+  g.outV = __ballot_sync(FULL, (tv >> (dv ^ 1)) & 1u);
+  __syncwarp();
+  return g;
+}
+
+template <bool INSTR>
+__device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, unsigned char* const wb, const int lane,
+                                            const u32 step, const u32 nsteps, fcm_trace_rec* trace, int force_full,
+                                            u32& sumK, u32& nonempty) {
+  u32* const sA32 = (u32*)(wb + SM_A);
+  u32* const scv = (u32*)(wb + SM_CV);
+  u32* const scv2 = (u32*)(wb + SM_CV2);
+  int* const sflag = (int*)(wb + SM_FLAG);
+  u32* const sAT = (u32*)(wb + SM_AT);
+  u32* const ssrc = (u32*)(wb + SM_SRC);
+  u32* const spark = (u32*)(wb + SM_PARK);
+  u64* const srng = (u64*)(wb + SM_RNG);
+  u64* const sfc = (u64*)(wb + SM_FC);
+  u32* const stage = (u32*)(wb + SM_TILE + ST_STAGE);
+  u32* const sla = (u32*)(wb + SM_TILE + ST_LA);
+  u64* const srngla = (u64*)(wb + SM_TILE + ST_RNGLA);
+  const uint4* const spinfo = (const uint4*)(wb + SM_TILE + ST_PINFO);
+  u32* const ori = cb + p.off_ori;
+  const u32 E = (u32)sflag[FL_E], ND = (u32)sflag[FL_ND];
+#define ITEMS(i) cb[p.off_items + (i)]
+#define POS(i) cb[p.off_pos + (i)]
+#define DBL(i) cb[p.off_dbl + (i)]
+
+  // ---- the draws (Transition::random_move, src/lib.rs:207-212) and the sampled container entries ----
+  Rng g;
+  int kind;
+  u32 idx = 0, didx = 0, slot = 0, dpair = 0;
+  const bool la = sla[LA_VALID] != 0;
+  const bool la2 = la && sla[LA_L2] != 0;
+  if (la) {
+    cp_async_wait<0>();
+    __syncwarp();
+    { const ulonglong2 a = *(const ulonglong2*)&srngla[0], b = *(const ulonglong2*)&srngla[2]; g.s0 = a.x; g.s1 = a.y; g.s2 = b.x; g.s3 = b.y; }
+    kind = (int)sla[LA_KIND]; idx = sla[LA_IDX]; didx = sla[LA_DIDX]; slot = sla[LA_SLOT]; dpair = sla[LA_DPAIR];
+  } else {
+    { const ulonglong2 a = *(const ulonglong2*)&srng[0], b = *(const ulonglong2*)&srng[2]; g.s0 = a.x; g.s1 = a.y; g.s2 = b.x; g.s3 = b.y; }
+    kind = draw_kind(p, g);
+    if (kind > 1) {
+      // clique move: the general code takes it from here (the kind draw is consumed)
+      if (p.cq_norders == 0) return FCM_EUNSUPPORTED;
+      if (lane == 0) {
+        *(ulonglong2*)&srng[0] = make_ulonglong2(g.s0, g.s1); *(ulonglong2*)&srng[2] = make_ulonglong2(g.s2, g.s3);
+        spark[PK_KIND] = (u32)kind;
+      }
+      __syncwarp();
+      return 1;
+    }
+    if (kind == 0) {
+      if (E) { idx = (u32)gen_range(g, E); slot = ITEMS(idx); }
+    } else if (ND) {
+      if (2ULL * ND >= E) return FCM_EINVAL;              // reference spins forever (FIXME :307)
+      didx = (u32)gen_range(g, ND);
+      idx = (u32)gen_range(g, E);                         // the next draw does not depend on the loaded pair
+      dpair = DBL(didx);
+      slot = ITEMS(idx);
+    }
+  }
+  bool live = false, sampled_edge = false;
+  u32 delme = 0, last = 0, qpos = 0;
+  u32 oA = 0, oD = 0, kA = 0, kD = 0, oriA = 0, oriD = 0;
+  int cA = 0, cD = 0, mA = 0, mD = 0;
+  uint2 abA = make_uint2(0, 0), abD = make_uint2(0, 0);
+  if (kind == 0) {
+    if (E) {
+      // single_edge_flip (src/lib.rs:292-299)
+      last = ITEMS(E - 1);
+      uint4 i0, i1;
+      if (la2) { i0 = spinfo[0]; i1 = spinfo[1]; oriA = sla[LA_ORIA]; }
+      else { oriA = __ldcg(&ori[slot >> 5]); i0 = __ldg(&p.pinfo[2 * (slot >> 1)]); i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]); }
+      abA = make_uint2(i0.x, i0.y); oA = i0.z; kA = i0.w; cA = (int)i1.x; mA = (int)i1.y;
+      live = !((oriA >> ((slot ^ 1) & 31)) & 1u);         // the reverse edge exists: empty transition
+      sampled_edge = true;
+    }
+  } else if (ND) {
+    // double_edge_move (src/lib.rs:304-325)
+    {
+      uint4 i0, i1;
+      if (la2) { i0 = spinfo[2]; i1 = spinfo[3]; oriD = sla[LA_ORID]; }
+      else { oriD = __ldcg(&ori[dpair >> 4]); i0 = __ldg(&p.pinfo[2 * dpair]); i1 = __ldg(&p.pinfo[2 * dpair + 1]); }
+      abD = make_uint2(i0.x, i0.y); oD = i0.z; kD = i0.w; cD = (int)i1.x; mD = (int)i1.y;
+    }
+    bool first_try = true;
+    for (;;) {
+      uint4 i0, i1;
+      if (la2 && first_try) { i0 = spinfo[0]; i1 = spinfo[1]; oriA = sla[LA_ORIA]; }
+      else { oriA = __ldcg(&ori[slot >> 5]); i0 = __ldg(&p.pinfo[2 * (slot >> 1)]); i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]); }
+      abA = make_uint2(i0.x, i0.y); oA = i0.z; kA = i0.w; cA = (int)i1.x; mA = (int)i1.y;
+      if (!((oriA >> ((slot ^ 1) & 31)) & 1u)) break;     // a single edge
+      first_try = false;
+      idx = (u32)gen_range(g, E);
+      slot = ITEMS(idx);
+    }
+    const bool first = g.next() < 0x8000000000000000ULL;  // gen_bool(0.5)
+    delme = 2 * dpair + (first ? 1u : 0u);                // first: [min,max] = small -> big
+    qpos = POS(delme);                                    // needed when the containers are updated
+    live = true;
+    sampled_edge = true;
+  }
+  // (ta,tb) = the sampled single edge, (tdm0,tdm1) = delme; dir 0 of a slot = big -> small
+  u32 ta = 0, tb = 0, tdm0 = 0, tdm1 = 0;
+  if (sampled_edge) { ta = (slot & 1) ? abA.y : abA.x; tb = (slot & 1) ? abA.x : abA.y; }
+  if (kind == 1 && live) { tdm0 = (delme & 1) ? abD.y : abD.x; tdm1 = (delme & 1) ? abD.x : abD.y; }
+  // this proposal has made its last draw: commit the RNG
+  if (lane == 0) { *(ulonglong2*)&srng[0] = make_ulonglong2(g.s0, g.s1); *(ulonglong2*)&srng[2] = make_ulonglong2(g.s2, g.s3); }
+  const bool cold = live && (force_full || cA > NARROW_C || (kind == 1 && cD > NARROW_C));
+  // the proposal is parked in shared memory: the update stage (lane 0) and cold_step read it back, so
+  // that its scalars do not occupy registers while the simplices are counted
+  if (live && lane == 0) {
+    *(uint4*)&spark[PK_KIND] = make_uint4((u32)kind, slot, delme, idx);
+    *(uint4*)&spark[PK_DIDX] = make_uint4(didx, dpair, last, qpos);
+    *(uint4*)&spark[PK_TA] = make_uint4(ta, tb, tdm0, tdm1);
+    *(uint4*)&spark[PK_CA] = make_uint4((u32)cA, (u32)cD, oA, oD);
+    *(uint2*)&spark[PK_ORIA] = make_uint2(oriA, oriD);
+  }
+  if (cold) {
+    if (lane == 0) sla[LA_VALID] = 0;
+    __syncwarp();
+    return 1;
+  }
+  // ---- look-ahead, level 1: the next proposal's kind and container indices; its entries start travelling ----
+  {
+    bool nla = false;
+    if (step + 1 < nsteps) {
+      Rng h = g;
+      const int k2 = draw_kind(p, h);
+      if (k2 == 0 ? E != 0 : (k2 == 1 && ND != 0 && 2ULL * ND < E)) {
+        u32 d2 = 0;
+        if (k2 == 1) d2 = (u32)gen_range(h, ND);
+        const u32 i2 = (u32)gen_range(h, E);
+        if (lane == 0) {
+          *(ulonglong2*)&srngla[0] = make_ulonglong2(h.s0, h.s1); *(ulonglong2*)&srngla[2] = make_ulonglong2(h.s2, h.s3);
+          *(uint4*)&sla[LA_KIND] = make_uint4((u32)k2, i2, d2, 0u);
+          cp_async4((u32)__cvta_generic_to_shared(&sla[LA_SLOT]), &ITEMS(i2));
+          if (k2 == 1) cp_async4((u32)__cvta_generic_to_shared(&sla[LA_DPAIR]), &DBL(d2));
+        }
+        nla = true;
+      }
+    }
+    if (lane == 0) { sla[LA_VALID] = nla ? 1u : 0u; sla[LA_L2] = 0u; }
+    cp_async_commit();
+  }
+
+  // ---- State::apply_transition  src/lib.rs:61-79: flag_count += post - pre ----
+  int K = 0;
+  u64 fnew;
+  if (live) {
+    int cnt[DELTA_SD];
+#pragma unroll
+    for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
+    int tri = 0, top = 1;
+    bool overflow = false;
+    Tagged t;
+    u32 pkA0, pkA1;
+    if (kind == 0) {
+      // ---- flip: one pair, two counts on one gather (coming edge tb -> ta, going edge ta -> tb) ----
+      const bool uBig = tb == abA.x;
+      stage_issue(p, ori, oA, cA, kA, mA, uBig, lane, stage, pkA0, pkA1);
+      cp_async_commit();
+      cp_async_wait<0>();
+      __syncwarp();
+      G32 ga = stage_finish(p, ori, cA, kA, mA, stage, pkA0, pkA1, FCM_NONE, oA, uBig, sA32, lane);
+      if (!hot_tag(ga, cA, true, sA32, sAT, ssrc, lane, t)) overflow = true;
+      else {
+        tri = __popc(t.come) - __popc(t.go);
+        hot_count(t.come, t.row, sAT, lane, 1, cnt, &sflag[FL_OVF]);
+        const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : t.come ? 2 : 1;
+        top = __reduce_max_sync(FULL, mytop);
+        hot_count(t.go, t.row, sAT, lane, -1, cnt, &sflag[FL_OVF]);
+      }
+      if constexpr (INSTR) K = cA + 2;
+    } else {
+      // ---- double-edge move: the coming edge tb -> ta in the graph without delme, then delme's own count ----
+      const bool uBigA = tb == abA.x, uBigD = tdm0 == abD.x;
+      u32 pkD0, pkD1;
+      stage_issue(p, ori, oA, cA, kA, mA, uBigA, lane, stage, pkA0, pkA1);
+      stage_issue(p, ori, oD, cD, kD, mD, uBigD, lane, stage + 128, pkD0, pkD1);
+      if constexpr (INSTR) {
+        scv[lane] = lane < cA ? __ldg(&p.nb_list[oA + lane]) : 0u;
+        scv2[lane] = lane < cD ? __ldg(&p.nb_list[oD + lane]) : 0u;
+      }
+      cp_async_commit();
+      cp_async_wait<0>();
+      __syncwarp();
+      {
+        G32 ga = stage_finish(p, ori, cA, kA, mA, stage, pkA0, pkA1, delme, oA, uBigA, sA32, lane);
+        if (!hot_tag(ga, cA, false, sA32, sAT, ssrc, lane, t)) overflow = true;
+      }
+      if (!overflow) {
+        tri = __popc(t.come);
+        hot_count(t.come, t.row, sAT, lane, 1, cnt, &sflag[FL_OVF]);
+        const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : t.come ? 2 : 1;
+        top = __reduce_max_sync(FULL, mytop);
+        __syncwarp();
+        G32 gd = stage_finish(p, ori, cD, kD, mD, stage + 128, pkD0, pkD1, FCM_NONE, oD, uBigD, sA32, lane);
+        if (!hot_tag(gd, cD, false, sA32, sAT, ssrc, lane, t)) overflow = true;
+        else {
+          tri -= __popc(t.come);
+          hot_count(t.come, t.row, sAT, lane, -1, cnt, &sflag[FL_OVF]);
+        }
+      }
+      if constexpr (INSTR) K = union_size(scv, cA, scv2, cD, ta, tb, tdm0, tdm1, lane);
+    }
+    __syncwarp();
+    if (sflag[FL_OVF]) { overflow = true; __syncwarp(); if (lane == 0) sflag[FL_OVF] = 0; }
+    if (overflow) {
+      // the parked proposal goes to the general code (nothing of the chain was modified yet)
+      cp_async_wait<0>();
+      if (lane == 0) sla[LA_VALID] = 0;
+      __syncwarp();
+      return 1;
+    }
+    long long delta = 0;
+#pragma unroll
+    for (int k = 0; k < DELTA_SD; k++) {
+      const int tot = __reduce_add_sync(FULL, cnt[k]);
+      if (lane == k + 3) delta = tot;
+    }
+    if (lane == 2) delta = tri;
+    fnew = sfc[lane] + (u64)delta;
+    if (__any_sync(FULL, (long long)fnew < 0)) return FCM_EASSERT;
+    if (lane == 0) sflag[FL_FCLEN] = max(sflag[FL_FCLEN], top + 1);
+    if constexpr (INSTR) { sumK += K; nonempty++; }
+  } else fnew = sfc[lane];
+
+  // ---- look-ahead, level 2: the entries have landed - the next proposal's pair records and orientation words ----
+  cp_async_wait<0>();
+  __syncwarp();
+  if (sla[LA_VALID]) {
+    if (lane < 2) {
+      const u32 s2 = sla[LA_SLOT];
+      cp_async16((u32)__cvta_generic_to_shared(&spinfo[lane]), &p.pinfo[2 * (s2 >> 1) + lane]);
+      if (lane == 0) cp_async4((u32)__cvta_generic_to_shared(&sla[LA_ORIA]), &ori[s2 >> 5]);
+    } else if (lane < 4 && sla[LA_KIND] == 1u) {
+      const u32 d2 = sla[LA_DPAIR];
+      cp_async16((u32)__cvta_generic_to_shared(&spinfo[lane]), &p.pinfo[2 * d2 + (lane - 2)]);
+      if (lane == 2) cp_async4((u32)__cvta_generic_to_shared(&sla[LA_ORID]), &ori[d2 >> 4]);
+    }
+  }
+  cp_async_commit();
+
+  // ---- Bounds::check, then keep or revert_transition (src/lib.rs:186-191, 81-95) ----
+  const bool ok = bounds_ok(p, fnew, lane);
+  if (lane == 0) sflag[FL_ACC] += ok;
+  if (live) {
+    if (lane == 0) {                                      // the parked proposal, read back
+      const uint4 q0 = *(const uint4*)&spark[PK_KIND], q1 = *(const uint4*)&spark[PK_DIDX];
+      const u32 uslot = q0.y, udelme = q0.z, uidx = q0.w, udidx = q1.x, udpair = q1.y, ulast = q1.z, uqpos = q1.w;
+      // what this update writes into the containers, mirrored into the look-ahead's staged entries (exact look-ahead)
+      const bool nla = sla[LA_VALID] != 0;
+      const u32 nidx = sla[LA_IDX], ndidx = sla[LA_DIDX];
+      const bool nmove = sla[LA_KIND] == 1u;
+      u32 nslot = sla[LA_SLOT], ndp = sla[LA_DPAIR];
+      if (nla) {
+        if (kind == 0) {
+          const u32 fin = ok ? uslot ^ 1 : uslot;
+          if (nidx == uidx) nslot = ulast;
+          if (nidx == E - 1) nslot = fin;
+        } else if (ok) {
+          if (nidx == uqpos) nslot = uslot ^ 1;
+          if (nmove && ndidx == udidx) ndp = uslot >> 1;
+        } else {
+          const u32 last0 = ITEMS(E - 1), lastd0 = DBL(ND - 1);
+          if (nidx == uqpos) nslot = last0;
+          if (nidx == E - 1) nslot = udelme;
+          if (nmove) { if (ndidx == udidx) ndp = lastd0; if (ndidx == ND - 1) ndp = udpair; }
+        }
+      }
+      update_containers(p, cb, kind, ok, uslot, udelme, uidx, udidx, udpair, ulast, uqpos, E, ND, 0);
+      u32 wa = FCM_NONE, wd = FCM_NONE;                   // orientation words this update rewrites
+      if (ok) {
+        // adjacency bits: gu->gv leaves, tb->ta comes
+        const uint4 q2 = *(const uint4*)&spark[PK_TA];
+        const u32 gu = kind == 0 ? q2.x : q2.z, gv = kind == 0 ? q2.y : q2.w;
+        const u32 W32 = 2 * p.W;
+        const u32 igo = gu * W32 + (gv >> 5), icome = q2.y * W32 + (q2.x >> 5);
+        const u32 mgo = 1u << (gv & 31), mcome = 1u << (q2.x & 31);
+        // rows: fire-and-forget L2 atomics (only the cold path reads them, with ld.cg); orientation
+        // bits: plain stores of the words read while sampling
+        const uint2 q4 = *(const uint2*)&spark[PK_ORIA];
+        atomicAnd(&cb[igo], ~mgo); atomicOr(&cb[icome], mcome);
+        wa = uslot >> 5;
+        if (kind == 0) ori[wa] = q4.x ^ (3u << (uslot & 30));
+        else {
+          wd = udelme >> 5;
+          const u32 ma = 1u << ((uslot ^ 1) & 31), md = 1u << (udelme & 31);
+          if (wa == wd) ori[wa] = (q4.x | ma) & ~md;
+          else { ori[wa] = q4.x | ma; ori[wd] = q4.y & ~md; }
+        }
+      }
+      if (nla) {
+        // level 2 was fetched for the entries as they stood: drop it when an entry changed under it or when one of
+        // its orientation words was just rewritten (the next proposal then loads them itself)
+        const bool changed = nslot != sla[LA_SLOT] || ndp != sla[LA_DPAIR];
+        const bool oriclash = (nslot >> 5) == wa || (nslot >> 5) == wd || (nmove && ((ndp >> 4) == wa || (ndp >> 4) == wd));
+        sla[LA_SLOT] = nslot; sla[LA_DPAIR] = ndp;
+        sla[LA_L2] = (changed || oriclash) ? 0u : 1u;
+      }
+    }
+    if (ok) sfc[lane] = fnew;
+    __syncwarp();
+  } else if (lane == 0 && sla[LA_VALID]) sla[LA_L2] = 1u;
+  if constexpr (INSTR) {
+    if (trace != nullptr && lane == 0) {
+      fcm_trace_rec tr;
+      tr.flags = (u32)kind | (ok ? FCM_TR_ACCEPT : 0u) | (live ? 0u : FCM_TR_EMPTY);
+      tr.a = ta; tr.b = tb; tr.dm0 = tdm0; tr.dm1 = tdm1; tr.K = (u32)K; tr.draws = 0; tr.pad = 0;
+      trace[step] = tr;
+    }
+  }
+  __syncwarp();
+  return 0;
+#undef ITEMS
+#undef POS
+#undef DBL
+}
+
 // IDX = true: the hot path reads the static clique index + the chain's orientation bits;
 // IDX = false: it gathers from the chain's adjacency rows (graphs too large for the index).
 // INSTR = true: per-proposal trace and the neighbourhood-size statistic (sumK / nonempty) are produced.
 template <bool IDX, bool INSTR>
-__global__ void __launch_bounds__(128, 7)
+__global__ void __launch_bounds__(128, FCM_CHAIN_MINBLOCKS)
 chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ trace, u32 trace_chain,
                   u32 smem_per_warp, int force_full) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1345,7 +1772,14 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
     const u32 step0 = step;
     int err = 0;
     bool cold = false;
+    if constexpr (IDX) { if (lane == 0) ((u32*)(wb + SM_TILE + ST_LA))[LA_VALID] = 0; __syncwarp(); }
     for (; step < nsteps; step++) {
+      if constexpr (IDX) {
+        const int rc = idx_proposal<INSTR>(p, cb, wb, lane, step, nsteps, trace, force_full, sumK, nonempty);
+        if (rc == 1) { cold = true; break; }
+        if (rc) { err = rc; break; }
+        continue;
+      }
       const u32 E = (u32)sflag[FL_E], ND = (u32)sflag[FL_ND];
       Rng g;
       { const ulonglong2 a = *(const ulonglong2*)&srng[0], b = *(const ulonglong2*)&srng[2]; g.s0 = a.x; g.s1 = a.y; g.s2 = b.x; g.s3 = b.y; }
@@ -1594,6 +2028,7 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
       }
     }
     // ---- end of the stretch: the chain's state goes back to HBM ----
+    if constexpr (IDX) cp_async_wait<0>();                // a look-ahead in flight lands before its buffer is reused
     __syncwarp();
     st->flag_count[lane] = sfc[lane];
     if (lane < 4) st->rng[lane] = srng[lane];
