@@ -1318,12 +1318,20 @@ __device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned ch
 // Returns 0 (proposal done), 1 (parked for cold_step) or an FCM_E* code.
 // ---------------------------------------------------------------------------------------------------
 enum { LA_VALID = 0, LA_L2 = 1, LA_SLOT = 2, LA_DPAIR = 3, LA_KIND = 4, LA_IDX = 5, LA_DIDX = 6, LA_ORIA = 8, LA_ORID = 9, LA_WORDS = 16 };   // [LA_KIND..+3] is written as one uint4
-#define ST_STAGE 0                     // u32[2][4][32]  staged orientation words: pair A, pair D; rows wu, wv, w0, w1
-#define ST_LA 1024                     // u32[LA_WORDS]  the look-ahead of the next proposal
-#define ST_RNGLA 1088                  // u64[4]         RNG state behind the look-ahead draws
-#define ST_PINFO 1120                  // uint4[4]       records of the next proposal's pairs: A (2), D (2)
-#define ST_BYTES 1184
-static_assert(ST_BYTES <= 8 * 8 + 3 * FCM_MAXD * 8 + 8 * 4 + FCM_MAXEDIT * 2 * 4, "the staging block overlays the full path's arrays");
+#ifndef FCM_LA
+#define FCM_LA 0                       // look-ahead: measured no gain on B200 (profiles/README.md r02_h), off; -DFCM_LA=1 builds it
+#endif
+#ifndef FCM_LA2
+#define FCM_LA2 1
+#endif
+#define ST_STAGE 0                     // u32[2][6][32]  per pair (A, D): staged orientation words wu, wv, w0, w1, then the lanes' packed entries
+#define ST_ROWS 6
+#define ST_PP 1536                     // u32[2][4]      per pair: list offset, c, k4 offset, m | uBig << 16
+#define ST_LA 1568                     // u32[LA_WORDS]  the look-ahead of the next proposal
+#define ST_RNGLA 1632                  // u64[4]         RNG state behind the look-ahead draws
+#define ST_PINFO 1664                  // uint4[4]       records of the next proposal's pairs: A (2), D (2)
+#define ST_BYTES 1728
+static_assert(ST_BYTES <= 8 * 8 + 3 * FCM_MAXD * 8 + 8 * 4 + FCM_MAXEDIT * 2 * 4 && (SM_TILE + ST_PP) % 16 == 0 && (SM_TILE + ST_PINFO) % 16 == 0, "the staging block overlays the full path's arrays");
 
 __device__ __forceinline__ void cp_async16(u32 saddr, const void* g) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
@@ -1335,11 +1343,12 @@ __device__ __forceinline__ int draw_kind(const EnsParams& p, Rng& g) {
   const double chosen = __dadd_rn(__dmul_rn(v, p.scale), 0.0);
   return (p.cum[0] <= chosen) + (p.cum[1] <= chosen) + (p.cum[2] <= chosen);
 }
-// every load of a pair: static entries into registers (kept packed: bit positions only), the orientation words
-// they name straight into shared memory.  pk0 = (sU & 31) | (sV & 31) << 5, pk1 = low 15 bits of e0 | of e1 << 15.
+// every load of a pair: the static entries pass through registers, the orientation words they name go straight into
+// shared memory; what the finish stage needs of the entries (bit positions only) is left beside them, packed:
+// pk0 = (sU & 31) | (sV & 31) << 5, pk1 = low 15 bits of e0 | of e1 << 15.
 __device__ __forceinline__ void stage_issue(const EnsParams& p, const u32* ori, u32 o, int c, u32 k4o, int m, bool uBig,
-                                            int lane, u32* stage, u32& pk0, u32& pk1) {
-  pk0 = 0; pk1 = 0;
+                                            int lane, u32* stage) {
+  u32 pk0 = 0, pk1 = 0;
   const u32 sbase = (u32)__cvta_generic_to_shared(stage + lane);
   if (lane < c) {
     const uint2 t = __ldg(&p.tri[o + lane]);
@@ -1358,6 +1367,8 @@ __device__ __forceinline__ void stage_issue(const EnsParams& p, const u32* ori, 
     cp_async4(sbase + 384, &ori[e1 >> 15]);
     pk1 |= (e1 & 0x7fffu) << 15;
   }
+  stage[128 + lane] = pk0;
+  stage[160 + lane] = pk1;
 }
 // packed entry pe = (slot & 31) << 10 | j << 5 | i, w = the orientation word of that slot
 __device__ __forceinline__ void k4_scatter_packed(u32 pe, u32 w, u32* A32) {
@@ -1368,9 +1379,10 @@ __device__ __forceinline__ void k4_scatter_packed(u32 pe, u32 w, u32* A32) {
 }
 // staged words -> A32[i] = { j : C[i] -> C[j] } and the four relation masks.  dropslot: a directed slot the view
 // must not contain (the double move's leaving edge while the coming edge is counted), FCM_NONE for none.
-__device__ __forceinline__ G32 stage_finish(const EnsParams& p, const u32* ori, int c, u32 k4o, int m, const u32* stage, u32 pk0,
-                                            u32 pk1, u32 dropslot, u32 o, bool uBig, u32* A32, int lane) {
+__device__ __forceinline__ G32 stage_finish(const EnsParams& p, const u32* ori, int c, u32 k4o, int m, const u32* stage,
+                                            u32 dropslot, u32 o, bool uBig, u32* A32, int lane) {
   A32[lane] = 0;
+  const u32 pk0 = stage[128 + lane], pk1 = stage[160 + lane];
   __syncwarp();
   // the staged words do not say which word they are: a lane finds out from its entries only when a drop is asked for
   u32 wu = 0, wv = 0;
@@ -1529,7 +1541,7 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
   // ---- look-ahead, level 1: the next proposal's kind and container indices; its entries start travelling ----
   {
     bool nla = false;
-    if (step + 1 < nsteps) {
+    if (FCM_LA && step + 1 < nsteps) {
       Rng h = g;
       const int k2 = draw_kind(p, h);
       if (k2 == 0 ? E != 0 : (k2 == 1 && ND != 0 && 2ULL * ND < E)) {
@@ -1559,56 +1571,46 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
     int tri = 0, top = 1;
     bool overflow = false;
     Tagged t;
-    u32 pkA0, pkA1;
-    if (kind == 0) {
-      // ---- flip: one pair, two counts on one gather (coming edge tb -> ta, going edge ta -> tb) ----
-      const bool uBig = tb == abA.x;
-      stage_issue(p, ori, oA, cA, kA, mA, uBig, lane, stage, pkA0, pkA1);
-      cp_async_commit();
-      cp_async_wait<0>();
-      __syncwarp();
-      G32 ga = stage_finish(p, ori, cA, kA, mA, stage, pkA0, pkA1, FCM_NONE, oA, uBig, sA32, lane);
-      if (!hot_tag(ga, cA, true, sA32, sAT, ssrc, lane, t)) overflow = true;
-      else {
-        tri = __popc(t.come) - __popc(t.go);
-        hot_count(t.come, t.row, sAT, lane, 1, cnt, &sflag[FL_OVF]);
-        const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : t.come ? 2 : 1;
-        top = __reduce_max_sync(FULL, mytop);
-        hot_count(t.go, t.row, sAT, lane, -1, cnt, &sflag[FL_OVF]);
-      }
-      if constexpr (INSTR) K = cA + 2;
-    } else {
-      // ---- double-edge move: the coming edge tb -> ta in the graph without delme, then delme's own count ----
-      const bool uBigA = tb == abA.x, uBigD = tdm0 == abD.x;
-      u32 pkD0, pkD1;
-      stage_issue(p, ori, oA, cA, kA, mA, uBigA, lane, stage, pkA0, pkA1);
-      stage_issue(p, ori, oD, cD, kD, mD, uBigD, lane, stage + 128, pkD0, pkD1);
+    // one copy of every stage, walked by a loop (the hot loop has to stay inside the 32 KB instruction cache; the
+    // second pair's parameters wait in shared memory, not in registers): a flip is one pair and two counts on one
+    // gather (coming edge tb -> ta, going edge ta -> tb); a double-edge move is the coming edge tb -> ta counted in
+    // the graph without delme, then delme's own count
+    u32* const spp = (u32*)(wb + SM_TILE + ST_PP);
+    if (lane == 0) {
+      *(uint4*)&spp[0] = make_uint4(oA, (u32)cA, kA, (u32)mA | (tb == abA.x ? 1u << 16 : 0u));
+      *(uint4*)&spp[4] = make_uint4(oD, (u32)cD, kD, (u32)mD | (tdm0 == abD.x ? 1u << 16 : 0u));
+    }
+    stage_issue(p, ori, oA, cA, kA, mA, tb == abA.x, lane, stage);
+    if (kind == 1) {
+      stage_issue(p, ori, oD, cD, kD, mD, tdm0 == abD.x, lane, stage + ST_ROWS * 32);
       if constexpr (INSTR) {
         scv[lane] = lane < cA ? __ldg(&p.nb_list[oA + lane]) : 0u;
         scv2[lane] = lane < cD ? __ldg(&p.nb_list[oD + lane]) : 0u;
       }
-      cp_async_commit();
-      cp_async_wait<0>();
-      __syncwarp();
-      {
-        G32 ga = stage_finish(p, ori, cA, kA, mA, stage, pkA0, pkA1, delme, oA, uBigA, sA32, lane);
-        if (!hot_tag(ga, cA, false, sA32, sAT, ssrc, lane, t)) overflow = true;
-      }
-      if (!overflow) {
-        tri = __popc(t.come);
-        hot_count(t.come, t.row, sAT, lane, 1, cnt, &sflag[FL_OVF]);
-        const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : t.come ? 2 : 1;
-        top = __reduce_max_sync(FULL, mytop);
-        __syncwarp();
-        G32 gd = stage_finish(p, ori, cD, kD, mD, stage + 128, pkD0, pkD1, FCM_NONE, oD, uBigD, sA32, lane);
-        if (!hot_tag(gd, cD, false, sA32, sAT, ssrc, lane, t)) overflow = true;
-        else {
-          tri -= __popc(t.come);
-          hot_count(t.come, t.row, sAT, lane, -1, cnt, &sflag[FL_OVF]);
-        }
-      }
-      if constexpr (INSTR) K = union_size(scv, cA, scv2, cD, ta, tb, tdm0, tdm1, lane);
     }
+    cp_async_commit();
+    cp_async_wait<0>();
+    __syncwarp();
+    const u32 dropA = kind == 1 ? delme : FCM_NONE;
+#pragma unroll 1
+    for (int ph = 0; ph < 2; ph++) {
+      if (ph == 0 || kind == 1) {
+        const uint4 q = *(const uint4*)&spp[4 * ph];      // this pair's parameters, back from shared memory
+        const G32 gq = stage_finish(p, ori, (int)q.y, q.z, (int)(q.w & 0xffffu), stage + ph * (ST_ROWS * 32), ph ? FCM_NONE : dropA,
+                                    q.x, (q.w >> 16) != 0, sA32, lane);
+        if (!hot_tag(gq, (int)q.y, kind == 0, sA32, sAT, ssrc, lane, t)) { overflow = true; break; }
+      }
+      const u32 roots = (ph == 1 && kind == 0) ? t.go : t.come;
+      const int sign = ph ? -1 : 1;
+      tri += sign * __popc(roots);
+      hot_count(roots, t.row, sAT, lane, sign, cnt, &sflag[FL_OVF]);
+      if (ph == 0) {
+        const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : roots ? 2 : 1;
+        top = __reduce_max_sync(FULL, mytop);
+      }
+      __syncwarp();
+    }
+    if constexpr (INSTR) K = kind == 0 ? cA + 2 : union_size(scv, cA, scv2, cD, ta, tb, tdm0, tdm1, lane);
     __syncwarp();
     if (sflag[FL_OVF]) { overflow = true; __syncwarp(); if (lane == 0) sflag[FL_OVF] = 0; }
     if (overflow) {
@@ -1634,7 +1636,7 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
   // ---- look-ahead, level 2: the entries have landed - the next proposal's pair records and orientation words ----
   cp_async_wait<0>();
   __syncwarp();
-  if (sla[LA_VALID]) {
+  if (FCM_LA2 && sla[LA_VALID]) {
     if (lane < 2) {
       const u32 s2 = sla[LA_SLOT];
       cp_async16((u32)__cvta_generic_to_shared(&spinfo[lane]), &p.pinfo[2 * (s2 >> 1) + lane]);
@@ -1702,12 +1704,12 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
         const bool changed = nslot != sla[LA_SLOT] || ndp != sla[LA_DPAIR];
         const bool oriclash = (nslot >> 5) == wa || (nslot >> 5) == wd || (nmove && ((ndp >> 4) == wa || (ndp >> 4) == wd));
         sla[LA_SLOT] = nslot; sla[LA_DPAIR] = ndp;
-        sla[LA_L2] = (changed || oriclash) ? 0u : 1u;
+        sla[LA_L2] = (!FCM_LA2 || changed || oriclash) ? 0u : 1u;
       }
     }
     if (ok) sfc[lane] = fnew;
     __syncwarp();
-  } else if (lane == 0 && sla[LA_VALID]) sla[LA_L2] = 1u;
+  } else if (FCM_LA2 && lane == 0 && sla[LA_VALID]) sla[LA_L2] = 1u;
   if constexpr (INSTR) {
     if (trace != nullptr && lane == 0) {
       fcm_trace_rec tr;
