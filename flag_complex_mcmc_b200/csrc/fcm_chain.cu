@@ -32,6 +32,7 @@
 #include "fcm_internal.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 
 #ifndef FCM_CHAIN_MINBLOCKS
 #define FCM_CHAIN_MINBLOCKS 7              // 7 blocks x 4 warps = 28 chains per SM: 4096 chains fill 148 SMs in one wave (72 registers per thread)
@@ -283,6 +284,20 @@ enum { PK_KIND = 0, PK_SLOT, PK_DELME, PK_IDX, PK_DIDX, PK_DPAIR, PK_LAST, PK_QP
        PK_CA, PK_CD, PK_OA, PK_OD, PK_ORIA, PK_ORID };
 #define CQ_SCRATCH 160                  // u32 words behind the header: clique_swap's rank / row tables (128) + perm_a while it is drawn (32)
 #define CQ_BYTES (3 * FCM_MAXCQ * 4 + 64 + CQ_SCRATCH * 4)
+// staging block of the index hot path (idx_proposal), laid over the full path's arrays behind SM_TILE
+#ifndef FCM_LA
+#define FCM_LA 0                       // look-ahead: measured no gain on B200 (profiles/README.md r02_h), off; -DFCM_LA=1 builds it
+#endif
+#ifndef FCM_LA2
+#define FCM_LA2 1
+#endif
+#define ST_STAGE 0                     // u32[2][6][32]  per pair (A, D): staged orientation words wu, wv, w0, w1, then the lanes' packed entries
+#define ST_ROWS 6
+#define ST_PP 1536                     // u32[16]        per pair: list offset, c, k4 offset, m | uBig << 16; [8] [9] root sets of the tagged graph
+#define ST_LA 1600                     // u32[LA_WORDS]  the look-ahead of the next proposal
+#define ST_RNGLA 1664                  // u64[4]         RNG state behind the look-ahead draws
+#define ST_PINFO 1696                  // uint4[4]       records of the next proposal's pairs: A (2), D (2)
+#define ST_BYTES 1760
 struct WarpSmem {
   u64 *M, *fc, *pre, *post;
   u32 *verts, *edits, *cq;
@@ -294,6 +309,7 @@ struct WarpSmem {
 // tile = false: the hot path reads the clique index, no staging tile is needed
 __host__ __device__ inline size_t warp_smem_bytes(u32 Kcap, u32 KWcap, bool tile, bool cq) {
   size_t full = (size_t)Kcap * KWcap * 8 + 3 * FCM_MAXD * 8 + (size_t)(Kcap + (Kcap & 1)) * 4 + FCM_MAXEDIT * 2 * 4 + (cq ? CQ_BYTES : 0);
+  if (full < ST_BYTES) full = ST_BYTES;                 // the index hot path's staging block overlays these arrays
   if (tile && full < TILE_WORDS * 4) full = TILE_WORDS * 4;
   return SM_TILE + full;
 }
@@ -1318,20 +1334,7 @@ __device__ __noinline__ int cold_step(const EnsParams& p, u32 chain, unsigned ch
 // Returns 0 (proposal done), 1 (parked for cold_step) or an FCM_E* code.
 // ---------------------------------------------------------------------------------------------------
 enum { LA_VALID = 0, LA_L2 = 1, LA_SLOT = 2, LA_DPAIR = 3, LA_KIND = 4, LA_IDX = 5, LA_DIDX = 6, LA_ORIA = 8, LA_ORID = 9, LA_WORDS = 16 };   // [LA_KIND..+3] is written as one uint4
-#ifndef FCM_LA
-#define FCM_LA 0                       // look-ahead: measured no gain on B200 (profiles/README.md r02_h), off; -DFCM_LA=1 builds it
-#endif
-#ifndef FCM_LA2
-#define FCM_LA2 1
-#endif
-#define ST_STAGE 0                     // u32[2][6][32]  per pair (A, D): staged orientation words wu, wv, w0, w1, then the lanes' packed entries
-#define ST_ROWS 6
-#define ST_PP 1536                     // u32[2][4]      per pair: list offset, c, k4 offset, m | uBig << 16
-#define ST_LA 1568                     // u32[LA_WORDS]  the look-ahead of the next proposal
-#define ST_RNGLA 1632                  // u64[4]         RNG state behind the look-ahead draws
-#define ST_PINFO 1664                  // uint4[4]       records of the next proposal's pairs: A (2), D (2)
-#define ST_BYTES 1728
-static_assert(ST_BYTES <= 8 * 8 + 3 * FCM_MAXD * 8 + 8 * 4 + FCM_MAXEDIT * 2 * 4 && (SM_TILE + ST_PP) % 16 == 0 && (SM_TILE + ST_PINFO) % 16 == 0, "the staging block overlays the full path's arrays");
+static_assert((SM_TILE + ST_PP) % 16 == 0 && (SM_TILE + ST_PINFO) % 16 == 0 && (SM_TILE + ST_RNGLA) % 16 == 0, "staging block alignment");
 
 __device__ __forceinline__ void cp_async16(u32 saddr, const void* g) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
@@ -1570,7 +1573,6 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
     for (int k = 0; k < DELTA_SD; k++) cnt[k] = 0;
     int tri = 0, top = 1;
     bool overflow = false;
-    Tagged t;
     // one copy of every stage, walked by a loop (the hot loop has to stay inside the 32 KB instruction cache; the
     // second pair's parameters wait in shared memory, not in registers): a flip is one pair and two counts on one
     // gather (coming edge tb -> ta, going edge ta -> tb); a double-edge move is the coming edge tb -> ta counted in
@@ -1598,12 +1600,15 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
         const uint4 q = *(const uint4*)&spp[4 * ph];      // this pair's parameters, back from shared memory
         const G32 gq = stage_finish(p, ori, (int)q.y, q.z, (int)(q.w & 0xffffu), stage + ph * (ST_ROWS * 32), ph ? FCM_NONE : dropA,
                                     q.x, (q.w >> 16) != 0, sA32, lane);
+        Tagged t;
         if (!hot_tag(gq, (int)q.y, kind == 0, sA32, sAT, ssrc, lane, t)) { overflow = true; break; }
+        if (lane == 0) { spp[8] = t.come; spp[9] = t.go; }   // root sets and rows wait in shared memory, not in registers
+        __syncwarp();
       }
-      const u32 roots = (ph == 1 && kind == 0) ? t.go : t.come;
+      const u32 roots = spp[(ph == 1 && kind == 0) ? 9 : 8];
       const int sign = ph ? -1 : 1;
       tri += sign * __popc(roots);
-      hot_count(roots, t.row, sAT, lane, sign, cnt, &sflag[FL_OVF]);
+      hot_count(roots, sAT[lane], sAT, lane, sign, cnt, &sflag[FL_OVF]);
       if (ph == 0) {
         const int mytop = cnt[2] ? 5 : cnt[1] ? 4 : cnt[0] ? 3 : roots ? 2 : 1;
         top = __reduce_max_sync(FULL, mytop);
@@ -2168,7 +2173,15 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
   if (per_warp * wpb > e->ctx->smem_optin) { fcm_set_error("neighbourhood tile does not fit shared memory"); return FCM_ELIMIT; }
   const size_t smem = per_warp * wpb;
   FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  {
+    // shared-memory carve-out: what the resident blocks need and no more - the rest of the 256 KB stays L1 (spilled
+    // registers, the static index entries a proposal re-reads).  FCM_CARVEOUT=<percent> overrides (measurements).
+    const size_t per_sm = std::min<size_t>(28 / wpb, (size_t)(227 * 1024) / (smem + 1024));
+    int pct = (int)((per_sm * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
+    if (const char* cv = getenv("FCM_CARVEOUT")) pct = atoi(cv);
+    pct = std::max(0, std::min(100, pct));
+    FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+  }
   const u32 blocks = (p.nchains + wpb - 1) / wpb;
   const u64 chunk = 1ULL << 24;                         // the kernel's per-launch counters are 32-bit
   for (u64 done = 0; done < nsteps; done += chunk) {
