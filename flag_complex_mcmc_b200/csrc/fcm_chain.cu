@@ -307,14 +307,16 @@ struct WarpSmem {
   u32* tile;
 };
 // tile = false: the hot path reads the clique index, no staging tile is needed
-__host__ __device__ inline size_t warp_smem_bytes(u32 Kcap, u32 KWcap, bool tile, bool cq) {
-  size_t full = (size_t)Kcap * KWcap * 8 + 3 * FCM_MAXD * 8 + (size_t)(Kcap + (Kcap & 1)) * 4 + FCM_MAXEDIT * 2 * 4 + (cq ? CQ_BYTES : 0);
+// long_edits: room for FCM_MAXEDIT edits (clique moves, fcm_apply); the step kernel of an ensemble without clique
+// moves only ever holds the two edits of a simple move
+__host__ __device__ inline size_t warp_smem_bytes(u32 Kcap, u32 KWcap, bool tile, bool cq, bool long_edits = true) {
+  size_t full = (size_t)Kcap * KWcap * 8 + 3 * FCM_MAXD * 8 + (size_t)(Kcap + (Kcap & 1)) * 4 + (long_edits || cq ? FCM_MAXEDIT * 2 * 4 : 32) + (cq ? CQ_BYTES : 0);
   if (full < ST_BYTES) full = ST_BYTES;                 // the index hot path's staging block overlays these arrays
   if (tile && full < TILE_WORDS * 4) full = TILE_WORDS * 4;
   return SM_TILE + full;
 }
 size_t fcm_chain_smem_per_warp(u32 Kcap, u32 KWcap, bool cliques) { return (warp_smem_bytes(Kcap, KWcap, true, cliques) + 15) & ~(size_t)15; }
-static size_t chain_smem_per_warp_mode(u32 Kcap, u32 KWcap, bool tile, bool cq) { return (warp_smem_bytes(Kcap, KWcap, tile, cq) + 15) & ~(size_t)15; }
+static size_t chain_smem_per_warp_mode(u32 Kcap, u32 KWcap, bool tile, bool cq) { return (warp_smem_bytes(Kcap, KWcap, tile, cq, false) + 15) & ~(size_t)15; }
 
 __device__ __forceinline__ WarpSmem carve(unsigned char* base, u32 Kcap, u32 KWcap) {
   WarpSmem s;
