@@ -3,6 +3,7 @@
 #include <vector>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -67,6 +68,11 @@ extern "C" int fcm_ctx_create(int device, fcm_ctx** out) {
     unsigned long long keep = ~0ULL;                    // freed graph memory stays in the pool for the next graph
     FCM_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
   }
+  if (const char* fg = getenv("FCM_L2_FETCH")) {
+    // L2 fetch-granularity hint (32 / 64 / 128 bytes), measurements only: on B200 the DRAM sectors moved per missing sector
+    // stay at two whatever the hint says (profiles/README.md r02_m), so the library leaves the device limit alone
+    if (atoi(fg) > 0 && cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(fg)) != cudaSuccess) cudaGetLastError();
+  }
   FCM_CUDA(cudaStreamCreateWithFlags(&c->own, cudaStreamNonBlocking));
   c->stream = c->own;
   FCM_CUDA(cudaEventCreate(&c->ev0));
@@ -83,6 +89,7 @@ extern "C" int fcm_ctx_destroy(fcm_ctx* c) {
   cudaEventDestroy(c->ev1);
   cudaStreamDestroy(c->own);
   if (c->pin) cudaFreeHost(c->pin);
+  for (int i = 0; i < 2; i++) { if (c->stage_host[i]) cudaFreeHost(c->stage_host[i]); if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]); }
   delete c;
   return FCM_OK;
 }
@@ -113,6 +120,43 @@ extern "C" int fcm_ctx_timer_end(fcm_ctx* c, float* ms) {
 }
 extern "C" uint64_t fcm_ctx_launches(const fcm_ctx* c) { return c ? c->launches : 0; }
 
+// Big uploads from pageable host memory (an edge list is 8 bytes per edge: 66 MB at C4).  The driver's own pageable path
+// copies through one thread; here the list goes through two pinned 8 MB buffers, filled by several host threads while
+// the previous chunk is on the wire.  Small lists take the plain call.
+int fcm_upload_edges(fcm_ctx* c, void* dst_dev, const void* src_host, size_t bytes) {
+  cudaStream_t s = c->stream;
+  if (bytes < (4u << 20)) { FCM_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, s)); return FCM_OK; }
+  for (int i = 0; i < 2; i++)
+    if (!c->stage_host[i]) {
+      FCM_CUDA(cudaHostAlloc((void**)&c->stage_host[i], FCM_STAGE_BYTES, cudaHostAllocDefault));
+      FCM_CUDA(cudaEventCreateWithFlags(&c->stage_ev[i], cudaEventDisableTiming));
+    }
+  const int nth = (int)std::max(1u, std::min(std::thread::hardware_concurrency(), 4u));
+  size_t done = 0;
+  int buf = 0;
+  while (done < bytes) {
+    const size_t now = std::min<size_t>(FCM_STAGE_BYTES, bytes - done);
+    FCM_CUDA(cudaEventSynchronize(c->stage_ev[buf]));      // the copy that last used this buffer has left it
+    unsigned char* const d = c->stage_host[buf];
+    const unsigned char* const sp = (const unsigned char*)src_host + done;
+    if (nth == 1 || now < (1u << 20)) memcpy(d, sp, now);
+    else {
+      std::vector<std::thread> th;
+      const size_t per = (now / nth + 4095) & ~(size_t)4095;
+      for (int t = 0; t < nth; t++) {
+        const size_t a = std::min(now, per * t), b = std::min(now, per * (t + 1));
+        if (b > a) th.emplace_back([=]() { memcpy(d + a, sp + a, b - a); });
+      }
+      for (auto& t : th) t.join();
+    }
+    FCM_CUDA(cudaMemcpyAsync((unsigned char*)dst_dev + done, d, now, cudaMemcpyHostToDevice, s));
+    FCM_CUDA(cudaEventRecord(c->stage_ev[buf], s));
+    done += now;
+    buf ^= 1;
+  }
+  return FCM_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // device graph
 // ---------------------------------------------------------------------------------------------------
@@ -128,9 +172,12 @@ static int graph_create(fcm_ctx* c, u32 n, u64 ne, const uint32_t (*edges)[2], i
   if (g->W == 0) g->W = 2;
   int rc = FCM_OK;
   uint2* edges_dev = nullptr;
-  std::vector<u64> off;
   auto fail = [&](int code) { fcm_pool_free(edges_dev, c->stream); fcm_graph_destroy(g); return code; };
 #define G_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { fcm_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); return fail(FCM_ECUDA); } } while (0)
+  const bool timing = getenv("FCM_TIMING") != nullptr;
+  auto now = []() { return std::chrono::steady_clock::now(); };
+  auto ms_since = [](std::chrono::steady_clock::time_point t0) { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
+  auto t0 = now();
   G_CUDA(fcm_pool_alloc(&g->adj, std::max<size_t>((size_t)n * g->W, 2) * 8, c->stream));
   G_CUDA(fcm_pool_alloc(&g->csr_off, ((size_t)n + 1) * 8, c->stream));
   G_CUDA(fcm_pool_alloc(&g->order, std::max<u32>(n, 1) * 4, c->stream));
@@ -139,18 +186,15 @@ static int graph_create(fcm_ctx* c, u32 n, u64 ne, const uint32_t (*edges)[2], i
   G_CUDA(fcm_pool_alloc(&g->ctrl, CT_WORDS * 4, c->stream));
   if (ne) {
     G_CUDA(fcm_pool_alloc(&edges_dev, ne * 8, c->stream));
-    G_CUDA(cudaMemcpyAsync(edges_dev, edges, ne * 8, cudaMemcpyHostToDevice, c->stream));
+    if ((rc = fcm_upload_edges(c, edges_dev, edges, ne * 8))) return fail(rc);
   }
-  rc = fcm_graph_build_device(g, edges_dev, ne, normalise, off);
+  if (timing) { cudaStreamSynchronize(c->stream); fprintf(stderr, "[fcm] graph_create: alloc + upload of %.1f MB: %.2f ms\n", ne * 8 / 1e6, ms_since(t0)); t0 = now(); }
+  // rows, CSR and the source order (vertices by descending out-degree: the heavy ones start first and shards
+  // (part, nparts) taken round-robin from this order are degree-balanced) are built on the device
+  rc = fcm_graph_build_device(g, edges_dev, ne, normalise);
   if (rc) return fail(rc);
-  // source vertices by descending out-degree: the heavy ones start first and shards
-  // (part, nparts) taken round-robin from this order are degree-balanced
-  std::vector<u32> order(n);
-  for (u32 v = 0; v < n; v++) order[v] = v;
-  std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) { return off[a + 1] - off[a] > off[b + 1] - off[b]; });
-  if (n) G_CUDA(cudaMemcpyAsync(g->order, order.data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
-  G_CUDA(cudaStreamSynchronize(c->stream));
   fcm_pool_free(edges_dev, c->stream);
+  if (timing) { cudaStreamSynchronize(c->stream); fprintf(stderr, "[fcm] graph_create: device build (rows, scan, sort, csr): %.2f ms\n", ms_since(t0)); }
 #undef G_CUDA
   *out = g;
   return FCM_OK;

@@ -22,6 +22,9 @@
 #include <algorithm>
 #include <cstring>
 
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
 #define DENSE_WARPS 4
 #define MAXL_DENSE (FCM_MAXD - 1)   // level l holds candidates for vertex index l+1
 
@@ -41,15 +44,16 @@ __global__ void set_bits_kernel(const uint2* __restrict__ edges, u64 ne, u32 n, 
   }
 }
 
-// one warp per row: out-degree
-__global__ void row_degree_kernel(const u64* __restrict__ adj, u32 n, u32 W, u64* __restrict__ off) {
+// one warp per row: out-degree -> off[v + 1] (scanned in place afterwards) and the sort key of the source order
+__global__ void row_degree_kernel(const u64* __restrict__ adj, u32 n, u32 W, u64* __restrict__ off,
+                                  u32* __restrict__ key, u32* __restrict__ val) {
   u32 warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= n) return;
   const u64* row = adj + (u64)warp * W;
   u32 c = 0;
   for (u32 w = lane; w < W; w += 32) c += __popcll(row[w]);
   c = __reduce_add_sync(0xffffffffu, c);
-  if (lane == 0) off[warp + 1] = c;     // exclusive scan done afterwards (host, n values)
+  if (lane == 0) { off[warp + 1] = c; key[warp] = ~c; val[warp] = warp; }   // ascending ~degree = descending degree
 }
 
 // one warp per row: ascending out-list into csr[off[v]..]
@@ -70,40 +74,68 @@ __global__ void row_to_csr_kernel(const u64* __restrict__ adj, u32 n, u32 W,
     base += __shfl_sync(0xffffffffu, incl, 31);
   }
 }
+// [0] = number of distinct edges (last scanned offset), [1] = largest out-degree (~ smallest sort key)
+__global__ void build_summary_kernel(const u64* __restrict__ off, const u32* __restrict__ key_sorted, u32 n, u64* __restrict__ out) {
+  out[0] = off[n];
+  out[1] = n ? (u64)(~key_sorted[0]) : 0ULL;
+}
 
-int fcm_graph_build_device(fcm_graph* g, const uint2* edges_dev, u64 ne_in, int normalise,
-                           std::vector<u64>& off_host) {
+// Bit rows -> CSR offsets (device scan), out-lists, and the source order (vertices by descending out-degree, ties by
+// ascending id: a stable device radix sort) - all on the device.  One small read-back (edge count, largest out-degree,
+// the bad-edge flag) is the only host hop: the host needs them to size the CSR and to choose the tile.
+int fcm_graph_build_device(fcm_graph* g, const uint2* edges_dev, u64 ne_in, int normalise) {
   fcm_ctx* c = g->ctx;
   cudaStream_t s = c->stream;
-  size_t words = (size_t)g->n * g->W;
+  const u32 n = g->n;
+  size_t words = (size_t)n * g->W;
   FCM_CUDA(cudaMemsetAsync(g->adj, 0, words * 8, s));
   FCM_CUDA(cudaMemsetAsync(g->ctrl, 0, CT_WORDS * 4, s));
   if (ne_in) {
     int blocks = (int)std::min<u64>((ne_in + 255) / 256, 148 * 16);
-    set_bits_kernel<<<blocks, 256, 0, s>>>(edges_dev, ne_in, g->n, g->W, normalise, g->adj, g->ctrl);
+    set_bits_kernel<<<blocks, 256, 0, s>>>(edges_dev, ne_in, n, g->W, normalise, g->adj, g->ctrl);
     c->launches++;
   }
   FCM_CUDA(cudaMemsetAsync(g->csr_off, 0, 8, s));
-  if (g->n) {
-    int blocks = (g->n * 32 + 255) / 256;
-    row_degree_kernel<<<blocks, 256, 0, s>>>(g->adj, g->n, g->W, g->csr_off);
+  u32 *key = nullptr, *val = nullptr, *key2 = nullptr;
+  void* tmp = nullptr;
+  u64* summary = nullptr;
+  auto release = [&]() { fcm_pool_free(key, s); fcm_pool_free(val, s); fcm_pool_free(key2, s); fcm_pool_free(tmp, s); fcm_pool_free(summary, s); };
+#define B_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { fcm_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); release(); return FCM_ECUDA; } } while (0)
+  const u32 nn = std::max<u32>(n, 1);
+  B_CUDA(fcm_pool_alloc(&key, (size_t)nn * 4, s));
+  B_CUDA(fcm_pool_alloc(&val, (size_t)nn * 4, s));
+  B_CUDA(fcm_pool_alloc(&key2, (size_t)nn * 4, s));
+  B_CUDA(fcm_pool_alloc(&summary, 16, s));
+  if (n) {
+    int blocks = (n * 32 + 255) / 256;
+    row_degree_kernel<<<blocks, 256, 0, s>>>(g->adj, n, g->W, g->csr_off, key, val);
     c->launches++;
+    size_t t_scan = 0, t_sort = 0;
+    B_CUDA(cub::DeviceScan::InclusiveSum(nullptr, t_scan, g->csr_off + 1, g->csr_off + 1, (int)n, s));
+    B_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, t_sort, key, key2, val, g->order, (int)n, 0, 32, s));
+    const size_t tbytes = std::max(t_scan, t_sort);
+    B_CUDA(fcm_pool_alloc((unsigned char**)&tmp, std::max<size_t>(tbytes, 16), s));
+    size_t tb = tbytes;
+    B_CUDA(cub::DeviceScan::InclusiveSum(tmp, tb, g->csr_off + 1, g->csr_off + 1, (int)n, s));
+    tb = tbytes;
+    B_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, key, key2, val, g->order, (int)n, 0, 32, s));
+    c->launches += 2;
   }
-  off_host.assign(g->n + 1, 0);
-  u32 ctrl_h[CT_WORDS];
-  FCM_CUDA(cudaMemcpyAsync(off_host.data(), g->csr_off, (g->n + 1) * 8, cudaMemcpyDeviceToHost, s));
-  FCM_CUDA(cudaMemcpyAsync(ctrl_h, g->ctrl, sizeof(ctrl_h), cudaMemcpyDeviceToHost, s));
-  FCM_CUDA(cudaStreamSynchronize(s));
-  if (ctrl_h[CT_ERR]) { fcm_set_error("edge list holds a vertex id >= n or a self loop"); return FCM_EINVAL; }
-  u32 maxout = 0;
-  for (u32 v = 0; v < g->n; v++) { u64 d = off_host[v + 1]; if (d > maxout) maxout = (u32)d; off_host[v + 1] = off_host[v] + d; }
-  g->maxout = maxout;
-  g->ne = off_host[g->n];
-  FCM_CUDA(cudaMemcpyAsync(g->csr_off, off_host.data(), (g->n + 1) * 8, cudaMemcpyHostToDevice, s));
+  build_summary_kernel<<<1, 1, 0, s>>>(g->csr_off, key2, n, summary);
+  c->launches++;
+  u64* const pin = c->pin;
+  B_CUDA(cudaMemcpyAsync(pin, summary, 16, cudaMemcpyDeviceToHost, s));
+  B_CUDA(cudaMemcpyAsync(pin + 2, g->ctrl, CT_WORDS * 4, cudaMemcpyDeviceToHost, s));
+  B_CUDA(cudaStreamSynchronize(s));
+  release();
+#undef B_CUDA
+  if (((const u32*)(pin + 2))[CT_ERR]) { fcm_set_error("edge list holds a vertex id >= n or a self loop"); return FCM_EINVAL; }
+  g->ne = pin[0];
+  g->maxout = (u32)pin[1];
   FCM_CUDA(fcm_pool_alloc(&g->csr, std::max<u64>(g->ne, 1) * 4, s));
-  if (g->n) {
-    int blocks = (g->n * 32 + 255) / 256;
-    row_to_csr_kernel<<<blocks, 256, 0, s>>>(g->adj, g->n, g->W, g->csr_off, g->csr);
+  if (n) {
+    int blocks = (n * 32 + 255) / 256;
+    row_to_csr_kernel<<<blocks, 256, 0, s>>>(g->adj, n, g->W, g->csr_off, g->csr);
     c->launches++;
   }
   FCM_CUDA(cudaGetLastError());

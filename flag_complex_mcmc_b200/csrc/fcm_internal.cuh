@@ -31,10 +31,13 @@ struct fcm_ctx {
   cudaStream_t own = nullptr, stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   u64 launches = 0;
+  unsigned char* stage_host[2] = {nullptr, nullptr};   // pinned staging of big host -> device uploads (edge lists), FCM_STAGE_BYTES each
+  cudaEvent_t stage_ev[2] = {nullptr, nullptr};
   u64* pin = nullptr;               // FCM_PIN_WORDS of pinned host memory: small read-backs that must not take the
                                     // driver's pageable-copy path (it blocks the other host threads' launches)
 };
 #define FCM_PIN_WORDS 128
+#define FCM_STAGE_BYTES (8u << 20)
 
 // ---- device graph for recounts ---------------------------------------------------------------------
 struct fcm_graph {
@@ -151,8 +154,9 @@ __device__ __forceinline__ void comm_last_cta(const CommArgs& ca, u64* counts, u
 // fcm_count.cu
 int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts, const CommArgs* comm = nullptr);
 int fcm_cells_launch(fcm_graph* g, u32 dim_min, u32 dim_max, u32* cells_dev, u64 cap, unsigned long long* ncells_dev);
-int fcm_graph_build_device(fcm_graph* g, const uint2* edges_dev, u64 ne_in, int normalise,
-                           std::vector<u64>& off_host);
+int fcm_graph_build_device(fcm_graph* g, const uint2* edges_dev, u64 ne_in, int normalise);
+// host edge list -> device, through the context's pinned staging buffers (fcm_api.cu)
+int fcm_upload_edges(fcm_ctx* c, void* dst_dev, const void* src_host, size_t bytes);
 
 // ---- ensemble of chains ----------------------------------------------------------------------------
 #define FCM_MAXB (FCM_MAXD + 1)     // bounds vectors may be one longer (src/lib.rs:152 push(10))

@@ -71,6 +71,9 @@ static double run_rand(const uint32_t* buf, uint64_t nsectors, int blocks, int t
 
 int main(int argc, char** argv) {
   const double gb = argc > 1 ? atof(argv[1]) : 16.0;
+  if (argc > 2) CK(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(argv[2])));   // L2 fetch granularity hint (32 / 64 / 128)
+  size_t fetch = 0;
+  CK(cudaDeviceGetLimit(&fetch, cudaLimitMaxL2FetchGranularity));
   const uint64_t bytes = (uint64_t)(gb * (1ULL << 30)) & ~255ULL;
   const uint64_t nsectors = bytes / 32;
   uint32_t *buf, *out;
@@ -82,7 +85,7 @@ int main(int argc, char** argv) {
   cudaDeviceProp prop;
   CK(cudaGetDeviceProperties(&prop, 0));
   const int sm = prop.multiProcessorCount;
-  printf("{\"gpu\": \"%s\", \"buffer_gb\": %.1f, \"rows\": [", prop.name, gb);
+  printf("{\"gpu\": \"%s\", \"buffer_gb\": %.1f, \"l2_fetch_granularity\": %zu, \"rows\": [", prop.name, gb, fetch);
   bool first = true;
   // warps per SM x loads in flight per thread
   const int wps[] = {8, 16, 28, 32, 64};
