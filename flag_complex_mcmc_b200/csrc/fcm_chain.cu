@@ -704,7 +704,7 @@ __device__ __forceinline__ bool hot_tag(const G32& g, int c, bool flip, const u3
 }
 // Ordered cliques of the tagged graph with >= 2 vertices, rooted at this lane's tagged vertex:
 // cnt[k] += sign * (number with k + 2 vertices) (flag_count index k + 3).  Sets *ovf when a clique of
-// more than DELTA_SD + 1 vertices exists (the proposal is then redone by cold_step).
+// more than DELTA_SD + 1 vertices exists (the caller runs hot_count_deep for those, or hands the proposal to cold_step).
 __device__ __forceinline__ void hot_count(u32 roots, u32 row, const u32* AT, int lane, int sign, int (&cnt)[DELTA_SD], int* ovf) {
   if (!((roots >> lane) & 1u)) return;
   const u32 P1 = row & roots;
@@ -719,6 +719,51 @@ __device__ __forceinline__ void hot_count(u32 roots, u32 row, const u32* AT, int
       cnt[2] += sign * __popc(P3);
       for (u32 R3 = P3; R3; R3 &= R3 - 1)
         if (P3 & AT[__ffs((int)R3) - 1]) *ovf = 1;
+    }
+  }
+}
+
+// Cliques of the tagged graph beyond the register levels: P0 = candidates (non-empty) for the next vertex of a clique of
+// nv0 tagged vertices.  Generic walk with a per-lane stack; the counts go to the warp's shared deep[] (by flag_count
+// index: a clique of v tagged vertices + u + v is a simplex of dimension v + 1), the highest index met by an addition to
+// dflag[FL_TOP].  Same bookkeeping as deep_dfs, but on the single-mask tagged graph the hot path has already built.
+__device__ __noinline__ void deep32(u32 P0, int nv0, const u32* AT, int sign, u64* deep, int* dflag) {
+  u32 P[FCM_MAXD], R[FCM_MAXD];
+  dflag[FL_DEEP] = 1;
+  int l = 0;
+  P[0] = P0;
+  for (;;) {
+    const int d = nv0 + l + 2;                            // flag_count index of the cliques the candidates of level l close
+    if (d >= FCM_MAXD) { dflag[FL_ERR] = FCM_EDIM; return; }
+    atomicAdd((unsigned long long*)&deep[d], (unsigned long long)(long long)(sign * __popc(P[l])));
+    if (sign > 0) atomicMax(&dflag[FL_TOP], d);
+    R[l] = P[l];
+    for (;;) {                                            // next child of level l, or pop
+      if (R[l] == 0) {
+        if (l == 0) return;
+        --l;
+        continue;
+      }
+      const int w = __ffs((int)R[l]) - 1;
+      R[l] &= R[l] - 1;
+      const u32 c = P[l] & AT[w];
+      if (c) { ++l; P[l] = c; break; }
+    }
+  }
+}
+// hot_count's walk once more for the cliques it flagged and did not count: those of more than DELTA_SD + 1 tagged
+// vertices, through deep32 into deep[] / dflag[] (the caller folds them in).
+__device__ __noinline__ void hot_count_deep(u32 roots, u32 row, const u32* AT, int lane, int sign, u64* deep, int* dflag) {
+  if (!((roots >> lane) & 1u)) return;
+  const u32 P1 = row & roots;
+  for (u32 R1 = P1; R1; R1 &= R1 - 1) {
+    const u32 P2 = P1 & AT[__ffs((int)R1) - 1];
+    for (u32 R2 = P2; R2; R2 &= R2 - 1) {
+      const u32 P3 = P2 & AT[__ffs((int)R2) - 1];
+      for (u32 R3 = P3; R3; R3 &= R3 - 1) {
+        const u32 P4 = P3 & AT[__ffs((int)R3) - 1];
+        if (P4) deep32(P4, DELTA_SD + 1, AT, sign, deep, dflag);
+      }
     }
   }
 }
@@ -1118,19 +1163,16 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
         Tagged tg;
         bool done = false;
         if (hot_tag(g, cc, false, sA32, (u32*)(wb + SM_AT), (u32*)(wb + SM_SRC), lane, tg)) {
-          int save[DELTA_SD];
-#pragma unroll
-          for (int k = 0; k < DELTA_SD; k++) save[k] = cnt[k];
           hot_count(tg.come, tg.row, (const u32*)(wb + SM_AT), lane, sign, cnt, &sflag[FL_OVF]);
           __syncwarp();
-          if (!sflag[FL_OVF]) { tri += sign * __popc(tg.come); done = true; }
-          else {
-#pragma unroll
-            for (int k = 0; k < DELTA_SD; k++) cnt[k] = save[k];
+          tri += sign * __popc(tg.come);
+          if (sflag[FL_OVF]) {                            // cliques beyond the register levels, on the same tagged graph
+            hot_count_deep(tg.come, tg.row, (const u32*)(wb + SM_AT), lane, sign, s.deep, s.dflag);
             __syncwarp();
             if (lane == 0) sflag[FL_OVF] = 0;
             __syncwarp();
           }
+          done = true;
         }
         if (!done) {
           const u32 a32v = sA32[lane];
@@ -1424,7 +1466,7 @@ __device__ __forceinline__ G32 stage_finish(const EnsParams& p, const u32* ori, 
   return g;
 }
 
-template <bool INSTR>
+template <bool INSTR, bool DEEP>
 __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, unsigned char* const wb, const int lane,
                                             const u32 step, const u32 nsteps, fcm_trace_rec* trace, int force_full,
                                             u32& sumK, u32& nonempty) {
@@ -1616,6 +1658,16 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
         top = __reduce_max_sync(FULL, mytop);
       }
       __syncwarp();
+      if constexpr (DEEP) {
+        // the kernel of graphs with simplices beyond dimension DELTA_SD + 2 (BASELINE config 2 reaches 7): cliques
+        // beyond the register levels are counted right here, on the tagged graph that is in place
+        if (sflag[FL_OVF]) {
+          hot_count_deep(roots, sAT[lane], sAT, lane, sign, (u64*)(wb + SM_DEEP), sflag);
+          __syncwarp();
+          if (lane == 0) sflag[FL_OVF] = 0;
+          __syncwarp();
+        }
+      }
     }
     if constexpr (INSTR) K = kind == 0 ? cA + 2 : union_size(scv, cA, scv2, cD, ta, tb, tdm0, tdm1, lane);
     __syncwarp();
@@ -1634,6 +1686,19 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
       if (lane == k + 3) delta = tot;
     }
     if (lane == 2) delta = tri;
+    if constexpr (DEEP) {
+      if (sflag[FL_DEEP]) {
+        // cliques beyond the register levels were met (deep32): their counts sit in the warp's deep[] by flag_count index
+        u64* const sdeep = (u64*)(wb + SM_DEEP);
+        if (sflag[FL_ERR]) return sflag[FL_ERR];
+        delta += (long long)sdeep[lane];
+        top = max(top, sflag[FL_TOP]);
+        __syncwarp();
+        sdeep[lane] = 0;
+        if (lane < 3) sflag[lane] = 0;
+        __syncwarp();
+      }
+    }
     fnew = sfc[lane] + (u64)delta;
     if (__any_sync(FULL, (long long)fnew < 0)) return FCM_EASSERT;
     if (lane == 0) sflag[FL_FCLEN] = max(sflag[FL_FCLEN], top + 1);
@@ -1735,7 +1800,7 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
 // IDX = true: the hot path reads the static clique index + the chain's orientation bits;
 // IDX = false: it gathers from the chain's adjacency rows (graphs too large for the index).
 // INSTR = true: per-proposal trace and the neighbourhood-size statistic (sumK / nonempty) are produced.
-template <bool IDX, bool INSTR>
+template <bool IDX, bool INSTR, bool DEEP>
 __global__ void __launch_bounds__(128, FCM_CHAIN_MINBLOCKS)
 chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ trace, u32 trace_chain,
                   u32 smem_per_warp, int force_full) {
@@ -1784,7 +1849,7 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
     if constexpr (IDX) { if (lane == 0) ((u32*)(wb + SM_TILE + ST_LA))[LA_VALID] = 0; __syncwarp(); }
     for (; step < nsteps; step++) {
       if constexpr (IDX) {
-        const int rc = idx_proposal<INSTR>(p, cb, wb, lane, step, nsteps, trace, force_full, sumK, nonempty);
+        const int rc = idx_proposal<INSTR, DEEP>(p, cb, wb, lane, step, nsteps, trace, force_full, sumK, nonempty);
         if (rc == 1) { cold = true; break; }
         if (rc) { err = rc; break; }
         continue;
@@ -2149,7 +2214,7 @@ int fcm_chain_launch_replicate(fcm_ensemble* e) {
   return FCM_OK;
 }
 
-template <bool IDX, bool INSTR>
+template <bool IDX, bool INSTR, bool DEEP>
 static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
   EnsParams p = e->p;
   // ensembles with clique moves size the local matrix M for the union neighbourhood of two cliques; when
@@ -2174,7 +2239,7 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
   }
   if (per_warp * wpb > e->ctx->smem_optin) { fcm_set_error("neighbourhood tile does not fit shared memory"); return FCM_ELIMIT; }
   const size_t smem = per_warp * wpb;
-  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR, DEEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
     // shared-memory carve-out: what the resident blocks need and no more - the rest of the 256 KB stays L1 (spilled
     // registers, the static index entries a proposal re-reads).  FCM_CARVEOUT=<percent> overrides (measurements).
@@ -2182,7 +2247,7 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
     int pct = (int)((per_sm * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
     if (const char* cv = getenv("FCM_CARVEOUT")) pct = atoi(cv);
     pct = std::max(0, std::min(100, pct));
-    FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+    FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR, DEEP>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
   }
   const u32 blocks = (p.nchains + wpb - 1) / wpb;
   const u64 chunk = 1ULL << 24;                         // the kernel's per-launch counters are 32-bit
@@ -2195,7 +2260,7 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
     attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
     attr[0].val.accessPolicyWindow = e->l2_window;
     cfg.attrs = attr; cfg.numAttrs = e->l2_window.num_bytes ? 1 : 0;
-    FCM_CUDA(cudaLaunchKernelEx(&cfg, chain_step_kernel<IDX, INSTR>, p, now, trace_dev ? trace_dev + done : (fcm_trace_rec*)nullptr,
+    FCM_CUDA(cudaLaunchKernelEx(&cfg, chain_step_kernel<IDX, INSTR, DEEP>, p, now, trace_dev ? trace_dev + done : (fcm_trace_rec*)nullptr,
                                 trace_chain, (u32)per_warp, (int)e->force_full));
     e->ctx->launches++;
   }
@@ -2205,10 +2270,15 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
 
 int fcm_chain_launch_step(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
   const bool idx = e->have_index && !e->force_rows, instr = trace_dev != nullptr || e->stats;
-  if (idx) return instr ? launch_step_mode<true, true>(e, nsteps, trace_dev, trace_chain)
-                        : launch_step_mode<true, false>(e, nsteps, trace_dev, trace_chain);
-  return instr ? launch_step_mode<false, true>(e, nsteps, trace_dev, trace_chain)
-               : launch_step_mode<false, false>(e, nsteps, trace_dev, trace_chain);
+  // graphs that start with simplices beyond dimension DELTA_SD + 2 run the index kernel that counts deep cliques in
+  // place; the others keep the leaner loop (a deep clique met later sends that proposal through cold_step: same result)
+  if (idx && e->deep_hint)
+    return instr ? launch_step_mode<true, true, true>(e, nsteps, trace_dev, trace_chain)
+                 : launch_step_mode<true, false, true>(e, nsteps, trace_dev, trace_chain);
+  if (idx) return instr ? launch_step_mode<true, true, false>(e, nsteps, trace_dev, trace_chain)
+                        : launch_step_mode<true, false, false>(e, nsteps, trace_dev, trace_chain);
+  return instr ? launch_step_mode<false, true, false>(e, nsteps, trace_dev, trace_chain)
+               : launch_step_mode<false, false, false>(e, nsteps, trace_dev, trace_chain);
 }
 
 int fcm_chain_launch_apply(fcm_ensemble* e, u32 chain, int nedits, int mode) {

@@ -353,6 +353,7 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   if ((rc = copy_bounds(p, bounds_min, nmin, bounds_max, nmax))) return fail(rc);
   if ((rc = weighted_index_init(move_weights, p.cum, &p.scale))) return fail(rc);
   p.n = n; p.nchains = nchains;
+  e->deep_hint = len0 > 6;                           // flag_count0 reaches dimension 6: see fcm_chain_launch_step
   p.W = ((n + 63) / 64 + 1) & ~1u;
   if (p.W == 0) p.W = 2;
 

@@ -228,6 +228,7 @@ struct fcm_ensemble {
   int force_rows = 0;                     // 1: hot path gathers from the adjacency rows even when the clique index exists
   int have_index = 0;                     // the static clique index was built
   int cliques = 0;                        // clique moves enabled (bigger per-warp shared memory)
+  int deep_hint = 0;                      // the start graph has simplices beyond the hot loop's register levels (dimension > 5)
   int stats = 1;                          // 1: the kernels keep the neighbourhood-size statistic (sumK / nonempty)
   u64 index_bytes = 0;
   cudaAccessPolicyWindow l2_window = {};    // the clique index slab, given to every chain-kernel launch (num_bytes = 0: none)
