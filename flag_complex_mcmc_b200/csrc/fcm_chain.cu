@@ -33,6 +33,7 @@
 
 #include <algorithm>
 #include <cstdlib>
+#include <mutex>
 
 #ifndef FCM_CHAIN_MINBLOCKS
 #define FCM_CHAIN_MINBLOCKS 7              // 7 blocks x 4 warps = 28 chains per SM: 4096 chains fill 148 SMs in one wave (72 registers per thread)
@@ -2239,6 +2240,10 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
   }
   if (per_warp * wpb > e->ctx->smem_optin) { fcm_set_error("neighbourhood tile does not fit shared memory"); return FCM_ELIMIT; }
   const size_t smem = per_warp * wpb;
+  // a kernel's attributes are state of the function, not of the launch: two host threads stepping ensembles of different
+  // shapes (src/bin/all_cxs.rs runs a private State per OS thread) must not interleave "set the size" and "launch"
+  static std::mutex launch_mu;
+  std::lock_guard<std::mutex> launch_lock(launch_mu);
   FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR, DEEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
     // shared-memory carve-out: what the resident blocks need and no more - the rest of the 256 KB stays L1 (spilled
@@ -2283,6 +2288,8 @@ int fcm_chain_launch_step(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev,
 
 int fcm_chain_launch_apply(fcm_ensemble* e, u32 chain, int nedits, int mode) {
   size_t smem = e->smem_per_warp;
+  static std::mutex launch_mu;
+  std::lock_guard<std::mutex> launch_lock(launch_mu);
   FCM_CUDA(cudaFuncSetAttribute(chain_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   chain_apply_kernel<<<1, 32, smem, e->ctx->stream>>>(e->p, chain, e->edit_dev, nedits, mode, e->io_dev);
   e->ctx->launches++;

@@ -21,6 +21,7 @@
 
 #include <algorithm>
 #include <cstring>
+#include <mutex>
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -542,6 +543,8 @@ static int launch_local(fcm_graph* g, u32 part, u32 nparts, u32 kcap, const Emit
   constexpr int LOCAL_THREADS = LocalCfg<WK>::THREADS;
   size_t smem = (size_t)kcap * LS * 8 + (size_t)(kcap + (kcap & 1)) * 4 + (size_t)(LOCAL_THREADS / 32) * stack_cap(kcap) * 8;
   auto kern = count_local_kernel<WK, EMIT>;
+  static std::mutex launch_mu;                          // the attribute is state of the function: set-and-launch is one step (host threads)
+  std::lock_guard<std::mutex> launch_lock(launch_mu);
   FCM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
   FCM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, LOCAL_THREADS, smem));
