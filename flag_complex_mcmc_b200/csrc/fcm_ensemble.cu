@@ -4,6 +4,7 @@
 #include "fcm_internal.cuh"
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -148,10 +149,14 @@ struct CliqueEnum {
     }
   }
 };
-static std::vector<std::vector<u32>> maximal_cliques(u32 n, const std::vector<std::vector<u32>>& und, int nthreads) {
+static std::vector<u64> undirected_bit_rows(u32 n, const std::vector<std::vector<u32>>& und) {
   const u32 W = (n + 63) / 64;
   std::vector<u64> bits((size_t)n * W, 0);
   for (u32 v = 0; v < n; v++) for (u32 w : und[v]) bits[(size_t)v * W + (w >> 6)] |= 1ULL << (w & 63);
+  return bits;
+}
+static std::vector<std::vector<u32>> maximal_cliques(u32 n, const std::vector<std::vector<u32>>& und, const std::vector<u64>& bits, int nthreads) {
+  const u32 W = (n + 63) / 64;
   std::vector<std::vector<std::vector<u32>>> part(nthreads);
   std::vector<std::thread> th;
   for (int t = 0; t < nthreads; t++)
@@ -344,6 +349,14 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   REQUIRE(move_weights, "move_weights is null");
   const bool want_cliques = move_weights[2] != 0.0 || move_weights[3] != 0.0;
   FCM_CUDA(cudaSetDevice(ctx->device));
+  const bool timing = getenv("FCM_TIMING") != nullptr;   // FCM_TIMING=1: the phases of this call on stderr
+  auto t_last = std::chrono::steady_clock::now();
+  auto lap = [&](const char* what) {
+    if (!timing) return;
+    const auto now = std::chrono::steady_clock::now();
+    fprintf(stderr, "[fcm] ensemble_create: %-44s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+    t_last = now;
+  };
   fcm_ensemble* e = new fcm_ensemble();
   e->ctx = ctx;
   EnsParams& p = e->p;
@@ -411,8 +424,10 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   std::vector<u64> nb_off;                    // 64-bit while summing; uploaded as u32
   std::vector<u32> nb_list;
   u32 maxc = 0;
+  lap("pairs, containers, undirected lists (host)");
   if ((rc = edge_neighborhoods_device(ctx, n, pair_ab, nb_off, nb_list, &maxc))) return fail(rc);
   p.maxc = maxc;
+  lap("edge neighbourhoods (device)");
 
   // ---- static clique index (hot path of chain_step_kernel): for every pair the slots of the edges
   //      between its common neighbours and its endpoints (triangles) and of the edges among its
@@ -421,6 +436,7 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   std::vector<uint4> pinfo;
   std::vector<uint2> tri;
   std::vector<u32> k4;
+  std::vector<u64> und_bits;                  // n x ceil(n/64) undirected bit rows (host), built when the index or the cliques need them
   {
     const u64 nslots_ = 2 * p.npairs;
     u64 work = 0;
@@ -442,6 +458,8 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
         if (it == L.end() || *it != to) return FCM_NONE;
         return 2 * undpid[from][it - L.begin()] + (from > to ? 0u : 1u);
       };
+      und_bits = undirected_bit_rows(n, und);
+      const u32 Wb = (n + 63) / 64;
       tri.resize(nb_list.size());
       std::vector<u64> k4_off(p.npairs + 1, 0);
       std::vector<std::vector<u32>> k4_part(nthreads);
@@ -460,7 +478,9 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
           if (c <= 32)
             for (u32 i = 0; i < c; i++)
               for (u32 j = i + 1; j < c; j++) {
-                const u32 sl = slot_of(nb_list[o + i], nb_list[o + j]);
+                const u32 wi = nb_list[o + i], wj = nb_list[o + j];
+                if (!((und_bits[(size_t)wi * Wb + (wj >> 6)] >> (wj & 63)) & 1ULL)) continue;   // nine in ten are not adjacent: no search
+                const u32 sl = slot_of(wi, wj);
                 if (sl != FCM_NONE) { k4_part[t].push_back((sl << 10) | (j << 5) | i); m++; }
               }
           k4_cnt[t].push_back(m);
@@ -485,6 +505,7 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
       } else tri.clear();
     }
   }
+  lap("clique index (host threads)");
   u32 kneed = 2 * maxc + 4;                            // double-edge move: two pairs + four endpoints
   // ---- clique moves: maximal cliques by order, the order distribution, the sorted pair keys ----
   std::vector<u32> cq_verts;
@@ -500,7 +521,9 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     for (u32 v = 0; v < n; v++) pkey_begin[v + 1] += pkey_begin[v];
   }
   if (want_cliques) {
-    std::vector<std::vector<u32>> cl = maximal_cliques(n, und, nthreads);
+    if (und_bits.empty()) und_bits = undirected_bit_rows(n, und);
+    std::vector<std::vector<u32>> cl = maximal_cliques(n, und, und_bits, nthreads);
+    lap("maximal cliques (host threads)");
     size_t maxo = 0;
     for (auto& c : cl) maxo = std::max(maxo, c.size());
     if (maxo > FCM_MAXD) { fcm_set_error("a maximal clique of order %zu (> %d)", maxo, FCM_MAXD); return fail(FCM_EDIM); }
@@ -513,23 +536,36 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     }
     cq_verts.resize(std::max<u64>(base, 1));
     std::vector<u64> fill(maxo, 0);
-    u32 kunion = 0;
-    std::vector<u32> mark(n, 0);
-    u32 stamp = 0;
     for (auto& c : cl) {                               // lexicographic order is kept inside every order
       const size_t o = c.size() - 1;
       std::copy(c.begin(), c.end(), cq_verts.begin() + p.cq_base[o] + fill[o] * (o + 1));
       fill[o]++;
-      // |edgeset_neighborhood| of a permutation of this clique: its vertices + the common neighbours of its pairs
-      stamp++;
-      u32 usz = 0;
-      for (u32 v : c) if (mark[v] != stamp) { mark[v] = stamp; usz++; }
-      for (size_t i = 0; i < c.size(); i++)
-        for (size_t j = i + 1; j < c.size(); j++) {
-          const u32 q = e->pairmap[pkey(c[j], c[i])];
-          for (u64 t = nb_off[q]; t < nb_off[q + 1]; t++) if (mark[nb_list[t]] != stamp) { mark[nb_list[t]] = stamp; usz++; }
+    }
+    // |edgeset_neighborhood| of a permutation of a clique: its vertices + the common neighbours of its pairs; the largest
+    // one sizes the full path's local matrix (host threads, one mark array each)
+    u32 kunion = 0;
+    {
+      std::vector<u32> best(nthreads, 0);
+      std::vector<std::thread> th;
+      for (int t = 0; t < nthreads; t++) th.emplace_back([&, t]() {
+        std::vector<u32> mark(n, 0);
+        u32 stamp = 0, mx = 0;
+        for (size_t ci = t; ci < cl.size(); ci += nthreads) {
+          const std::vector<u32>& c = cl[ci];
+          stamp++;
+          u32 usz = 0;
+          for (u32 v : c) if (mark[v] != stamp) { mark[v] = stamp; usz++; }
+          for (size_t i = 0; i < c.size(); i++)
+            for (size_t j = i + 1; j < c.size(); j++) {
+              const u32 q = e->pairmap.find(pkey(c[j], c[i]))->second;
+              for (u64 x = nb_off[q]; x < nb_off[q + 1]; x++) if (mark[nb_list[x]] != stamp) { mark[nb_list[x]] = stamp; usz++; }
+            }
+          mx = std::max(mx, usz);
         }
-      kunion = std::max(kunion, usz);
+        best[t] = mx;
+      });
+      for (auto& t : th) t.join();
+      for (u32 b : best) kunion = std::max(kunion, b);
     }
     std::vector<double> w(maxo);
     for (size_t o = 0; o < maxo; o++) w[o] = std::pow((double)cnt[o], 0.2);   // src/bin/sample.rs:87
@@ -538,6 +574,7 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     e->cliques = 1;
     kneed = std::max<u32>(kneed, std::min<u32>(n, 2 * kunion));   // clique_swap: two cliques
   }
+  lap("pair keys + clique tables");
   p.Kcap = std::min<u32>(std::max<u32>(kneed, 8), 512);
   u32 kw = (p.Kcap + 63) / 64;
   p.KWcap = kw <= 1 ? 1 : kw <= 2 ? 2 : kw <= 4 ? 4 : 8;
@@ -634,6 +671,7 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   E_CUDA(cudaMemcpyAsync(p.st, st.data(), sizeof(ChainState) * nchains, cudaMemcpyHostToDevice, s));
   if ((rc = fcm_chain_launch_replicate(e))) return fail(rc);
   E_CUDA(cudaStreamSynchronize(s));
+  lap("device allocation, uploads, replication");
 #undef E_CUDA
   e->pair_ab_host = std::move(pair_ab);
   *out = e;
