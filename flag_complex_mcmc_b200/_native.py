@@ -26,7 +26,7 @@ SYMBOLS = [
     "fcm_ensemble_edgebits_info", "fcm_ensemble_edgebits_slots", "fcm_ensemble_edgebits",
     "fcm_ensemble_read_doubles", "fcm_ensemble_restore",
     "fcm_graph_status", "fcm_comm_create", "fcm_comm_connect", "fcm_comm_destroy",
-    "fcm_graph_count_allreduce_async", "fcm_graph_count_allreduce",
+    "fcm_graph_count_allreduce_async", "fcm_graph_count_allreduce", "fcm_graph_count_noalloc",
 ]
 
 
@@ -82,6 +82,7 @@ def lib():
     L.fcm_comm_destroy.argtypes = [vp]
     L.fcm_graph_count_allreduce_async.argtypes = [vp, vp, P(vp)]
     L.fcm_graph_count_allreduce.argtypes = [vp, vp, vp, P(i32)]
+    L.fcm_graph_count_noalloc.argtypes = [vp, u32, u32, vp, P(i32)]
     L.fcm_graph_set_kernel.argtypes = [vp, i32]
     L.fcm_graph_info.argtypes = [vp, P(u32), P(u64), P(u32), P(u32)]
     L.fcm_graph_cells.argtypes = [vp, i32, i32, vp, u64, P(u64)]

@@ -630,3 +630,81 @@ int fcm_cells_launch(fcm_graph* g, u32 dim_min, u32 dim_max, u32* cells_dev, u64
   if (kmax <= 512) return launch_local<8, true>(g, 0, 1, kcap, ea, none);
   return launch_local<16, true>(g, 0, 1, kcap, ea, none);
 }
+
+// ---------------------------------------------------------------------------------------------------
+// fcm_graph_count_noalloc: the dense-row count with its scratch in a file-scope device array.
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The entry point
+// calls no cudaMalloc / cudaFree / pool routine: count_dense_kernel's candidate-set stacks, its ticket, its error
+// flag and the count vector all live in g_noalloc_scratch below.  Every GPU that loads libfcm.so holds the array
+// (about 4.1 MB) until the process exits.
+//   limit   rows of at most FCM_NOALLOC_MAXW 64-bit words, i.e. n <= 64 * FCM_NOALLOC_MAXW = 4096 vertices (the row
+//           stride is ceil(n/64) + 1 rounded down to even); larger graphs are refused with FCM_ELIMIT.
+//   sharing every call on a device uses the same array and finds the previous call's contents in it: the words that
+//           must start at zero (counts, ticket, flags) are cleared by the call; the stacks are written before they are
+//           read.  Calls that overlap on the GPU would race - inside one process the call holds a mutex from its
+//           first enqueue to its synchronize, so they cannot.
+// In host code `g_noalloc_scratch` is a host-side stand-in for the symbol, not a device address: the address the
+// kernel gets comes from cudaGetSymbolAddress, asked once per device with that device current (noalloc_scratch()).
+// ---------------------------------------------------------------------------------------------------
+#define FCM_NOALLOC_MAXW_ 64                               // == FCM_NOALLOC_MAXW (include/fcm.h)
+#define NOALLOC_BLOCKS 64                                  // 64 blocks x DENSE_WARPS warps = 256 stacks
+#define NOALLOC_HDR_WORDS 64                               // [0, 33) counts, [40, 44) = u32 ctrl[CT_WORDS], rest unused
+#define NOALLOC_WORDS (NOALLOC_HDR_WORDS + (size_t)NOALLOC_BLOCKS * DENSE_WARPS * MAXL_DENSE * FCM_NOALLOC_MAXW_)
+static_assert(FCM_NOALLOC_MAXW_ == FCM_NOALLOC_MAXW, "fcm.h and fcm_count.cu disagree on the limit");
+static_assert(NOALLOC_WORDS * 8 <= (5u << 20), "the static scratch is meant to stay modest");
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[NOALLOC_WORDS];
+
+#define NOALLOC_MAXDEV 64
+static std::mutex g_noalloc_mu;
+static u64* g_noalloc_ptr[NOALLOC_MAXDEV];                 // device address of the array on each device (null: not asked yet)
+
+// device address of g_noalloc_scratch on `device` (which must be current); nullptr + error text on failure
+static u64* noalloc_scratch(int device) {
+  if (device < 0 || device >= NOALLOC_MAXDEV) { fcm_set_error("device ordinal %d beyond %d", device, NOALLOC_MAXDEV - 1); return nullptr; }
+  if (!g_noalloc_ptr[device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) { fcm_set_error("cudaGetSymbolAddress(g_noalloc_scratch) -> %s", cudaGetErrorString(e)); cudaGetLastError(); return nullptr; }
+    g_noalloc_ptr[device] = (u64*)p;
+  }
+  return g_noalloc_ptr[device];
+}
+
+extern "C" int fcm_graph_count_noalloc(fcm_graph* g, uint32_t part, uint32_t nparts, uint64_t* counts, int* len) {
+  if (!g || !counts || !len) { fcm_set_error("fcm_graph_count_noalloc: graph/counts/len is null"); return FCM_EINVAL; }
+  if (nparts < 1 || part >= nparts) { fcm_set_error("fcm_graph_count_noalloc: need part < nparts"); return FCM_EINVAL; }
+  if (g->W > FCM_NOALLOC_MAXW_) {
+    fcm_set_error("fcm_graph_count_noalloc: rows of %u words exceed the static scratch (FCM_NOALLOC_MAXW = %d words, n <= %d vertices); "
+                  "use fcm_graph_count", g->W, FCM_NOALLOC_MAXW_, 64 * FCM_NOALLOC_MAXW_);
+    return FCM_ELIMIT;
+  }
+  fcm_ctx* c = g->ctx;
+  FCM_CUDA(cudaSetDevice(c->device));
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);            // one user of the array at a time (see above)
+  u64* const base = noalloc_scratch(c->device);
+  if (!base) return FCM_ECUDA;
+  u64* const cnt = base;
+  u32* const ctrl = (u32*)(base + 40);
+  u64* const stacks = base + NOALLOC_HDR_WORDS;
+  cudaStream_t s = c->stream;
+  FCM_CUDA(cudaMemsetAsync(base, 0, NOALLOC_HDR_WORDS * 8, s));   // counts, ticket, flags start at zero; the stacks need not
+  if (g->n) {
+    CommArgs none;
+    memset(&none, 0, sizeof(none));
+    count_dense_kernel<<<NOALLOC_BLOCKS, DENSE_WARPS * 32, 0, s>>>(g->adj, g->order, g->n, nullptr, part, nparts, g->W,
+                                                                   &ctrl[CT_TICKET], ctrl, stacks, cnt, none);
+    c->launches++;
+    FCM_CUDA(cudaGetLastError());
+  }
+  u64* const pin = c->pin;                                 // pinned words of the context (allocated at fcm_ctx_create)
+  FCM_CUDA(cudaMemcpyAsync(pin, base, (FCM_MAXD + 1 + 7 + CT_WORDS / 2) * 8, cudaMemcpyDeviceToHost, s));
+  FCM_CUDA(cudaStreamSynchronize(s));
+  const u32* const hctrl = (const u32*)(pin + 40);
+  if (hctrl[CT_ERR]) { fcm_set_error("a simplex of dimension >= %d was met", FCM_MAXD); return FCM_EDIM; }
+  memcpy(counts, pin, FCM_MAXD * 8);
+  int l = FCM_MAXD;
+  while (l > 0 && counts[l - 1] == 0) l--;
+  *len = l;
+  return FCM_OK;
+}

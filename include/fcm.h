@@ -137,6 +137,17 @@ int fcm_graph_count_allreduce_async(fcm_graph* g, fcm_comm* c, uint64_t** counts
 /* Same, synchronous: counts[FCM_MAXD] zero padded, *len = top non-empty dimension + 1 of the WHOLE graph. */
 int fcm_graph_count_allreduce(fcm_graph* g, fcm_comm* c, uint64_t* counts, int* len);
 
+/* fcm_graph_count without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments and result as fcm_graph_count (the dense-row kernel counts); the kernel's scratch - its
+ * candidate-set stacks, ticket, error flag and count vector - lives in one file-scope device array of about 4.1 MB that
+ * every GPU loading libfcm.so holds until exit.  The call uses no cudaMalloc / cudaFree / memory-pool routine.
+ * Limit: adjacency rows of at most FCM_NOALLOC_MAXW 64-bit words (n <= 4096 vertices); beyond that FCM_ELIMIT.
+ * All calls on a device share the array: the call clears what must start at zero, and calls that overlap on the GPU
+ * would race (within one process the library serialises them).  Synchronous. */
+#define FCM_NOALLOC_MAXW 64
+int fcm_graph_count_noalloc(fcm_graph* g, uint32_t part, uint32_t nparts, uint64_t* counts, int* len);
+
 /* flag_complex::for_each_cell(&G, &mut F, min, max) (src/bin/all_cxs.rs:60-64,79-83) as a bulk call:
  * every cell of dimension dim_min..dim_max (dim_max <= 6) as one row of dim_max + 1 vertex ids
  * (v0..vd, padded with 0xffffffff), rows in the order the recursion meets them with candidates in
