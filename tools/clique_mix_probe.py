@@ -8,11 +8,13 @@ from tools import synth
 name = sys.argv[1] if len(sys.argv) > 1 else "c3_er_2000"
 nch = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
 P = int(sys.argv[3]) if len(sys.argv) > 3 else 200
+stats = len(sys.argv) > 4 and sys.argv[4] == "stats"      # default: statistic off, the kernel bench.py times
 ctx = fcm.Context(0)
 n, e = synth.config(name)
 t0 = time.time()
 s = fcm.initialize_new_sampler(ctx, n, e, list(range(nch)), target_relaxation=0.01, simple=False)
 print("create %.2f s" % (time.time() - t0), s.info())
+s.set_stats(stats)
 s.step(P); ctx.synchronize(); s.status()
 ctx.timer_begin()
 s.step(P)
