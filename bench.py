@@ -615,13 +615,18 @@ def main():
         rbytes = 8 * W4 * simplices                            # dense-row model, whole graph
         # e2e through the library's sharded call with HOST buffers: every rank uploads the edge list, builds its rows +
         # CSR, counts its shard, all-reduces inside the kernel and reads the vector back
-        barrier()
-        t0 = time.perf_counter()
-        g2 = fcm.DeviceGraph(ctx, n4, e4)
-        c2 = ds.trim(g2.count_allreduce(comm))
-        re2e = max_over_ranks(time.perf_counter() - t0)
-        g2.close()
-        assert c2 == counts, (c2, counts)
+        e2e_runs = []
+        for rep in range(4):                                   # one warm-up call (the memory pool grows once), then three timed
+            barrier()
+            t0 = time.perf_counter()
+            g2 = fcm.DeviceGraph(ctx, n4, e4)
+            c2 = ds.trim(g2.count_allreduce(comm))
+            dt = max_over_ranks(time.perf_counter() - t0)
+            g2.close()
+            assert c2 == counts, (c2, counts)
+            if rep:
+                e2e_runs.append(dt)
+        re2e = sorted(e2e_runs)[1]                             # median of three
         ccap = read_capture(COUNT_CAPTURE)
         rtraffic, issue, winst = None, None, None
         if ccap and ngpu == 1 and args.recount_graph == ccap.get("graph", "c4_geo_31346"):
@@ -638,8 +643,9 @@ def main():
             "gpu_launches": int(rl), "clocks": rclocks,
             "sharding": "source vertices, degree-descending round-robin over %d rank(s)" % ngpu,
             "e2e": {"value": simplices / re2e, "unit": "simplices/s", "h2d_bytes_per_step": int(e4.nbytes),
-                    "d2h_bytes_per_step": 8 * 33, "seconds": re2e,
-                    "what": "DeviceGraph(host edge list) + count_allreduce on every rank: upload, build bit rows + CSR, count the shard, all-reduce, download"},
+                    "d2h_bytes_per_step": 8 * 33, "seconds": re2e, "seconds_runs": e2e_runs,
+                    "what": "DeviceGraph(host edge list) + count_allreduce on every rank: upload, build bit rows + CSR, count the shard, all-reduce, download; "
+                            "median of three calls after one warm-up call"},
             "roofline": {"bound": "issue", "kernel": "count_local_kernel",
                          "dense_row_model": {"achieved": rbytes / (ms_fused * 1e-3) / 1e9 / ngpu, "peak": peak, "unit": "GB/s",
                                              "frac": rbytes / (ms_fused * 1e-3) / 1e9 / ngpu / peak,

@@ -26,7 +26,7 @@ SYMBOLS = [
     "fcm_ensemble_edgebits_info", "fcm_ensemble_edgebits_slots", "fcm_ensemble_edgebits",
     "fcm_ensemble_read_doubles", "fcm_ensemble_restore",
     "fcm_graph_status", "fcm_comm_create", "fcm_comm_connect", "fcm_comm_destroy",
-    "fcm_graph_count_allreduce_async", "fcm_graph_count_allreduce", "fcm_graph_count_noalloc",
+    "fcm_graph_count_allreduce_async", "fcm_graph_count_allreduce", "fcm_graph_count_noalloc", "fcm_ensemble_set_policy",
 ]
 
 
@@ -92,6 +92,7 @@ def lib():
     L.fcm_ensemble_set_bounds.argtypes = [vp, vp, i32, vp, i32]
     L.fcm_ensemble_set_kernel.argtypes = [vp, i32]
     L.fcm_ensemble_set_stats.argtypes = [vp, i32]
+    L.fcm_ensemble_set_policy.argtypes = [vp, i32]
     L.fcm_ensemble_index_info.argtypes = [vp, P(i32), P(u64)]
     L.fcm_ensemble_step.argtypes = [vp, u64]
     L.fcm_ensemble_step_trace.argtypes = [vp, u64, u32, vp]

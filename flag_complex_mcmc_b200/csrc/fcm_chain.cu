@@ -65,6 +65,13 @@ __device__ __forceinline__ u64 gen_range(Rng& g, u64 range) {
   }
 }
 
+// THE EDGE-SAMPLER POLICY SEAM ("isolated behind one small policy").  Graph::sample_edge / sample_double_edge of
+// the external flag-complex crate pick an element of the insertion-ordered container from one gen_range(0..len) draw r.
+// Policy 0 (the documented assumption, oracle/fcm_oracle.cpp Graph::sample_edge): element r.  Policy 1: element len-1-r -
+// not a guess about the crate, it exists so that tests can show GPU and oracle change together when the policy changes
+// (tests/test_gpu_chain.py::test_sampler_policy_seam); the crate's real rule, once known, goes here and in the oracle.
+__device__ __forceinline__ u32 sample_at(const EnsParams& p, u32 r, u32 len) { return p.sample_policy ? len - 1u - r : r; }
+
 struct Chain {                        // pointers of one chain + live scalars
   u64* adj;
   u32 *items, *pos, *dbl, *dblpos, *ori;
@@ -1515,11 +1522,11 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
       return 1;
     }
     if (kind == 0) {
-      if (E) { idx = (u32)gen_range(g, E); slot = ITEMS(idx); }
+      if (E) { idx = sample_at(p, (u32)gen_range(g, E), E); slot = ITEMS(idx); }
     } else if (ND) {
       if (2ULL * ND >= E) return FCM_EINVAL;              // reference spins forever (FIXME :307)
-      didx = (u32)gen_range(g, ND);
-      idx = (u32)gen_range(g, E);                         // the next draw does not depend on the loaded pair
+      didx = sample_at(p, (u32)gen_range(g, ND), ND);
+      idx = sample_at(p, (u32)gen_range(g, E), E);                         // the next draw does not depend on the loaded pair
       dpair = DBL(didx);
       slot = ITEMS(idx);
     }
@@ -1556,7 +1563,7 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
       abA = make_uint2(i0.x, i0.y); oA = i0.z; kA = i0.w; cA = (int)i1.x; mA = (int)i1.y;
       if (!((oriA >> ((slot ^ 1) & 31)) & 1u)) break;     // a single edge
       first_try = false;
-      idx = (u32)gen_range(g, E);
+      idx = sample_at(p, (u32)gen_range(g, E), E);
       slot = ITEMS(idx);
     }
     const bool first = g.next() < 0x8000000000000000ULL;  // gen_bool(0.5)
@@ -1594,8 +1601,8 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
       const int k2 = draw_kind(p, h);
       if (k2 == 0 ? E != 0 : (k2 == 1 && ND != 0 && 2ULL * ND < E)) {
         u32 d2 = 0;
-        if (k2 == 1) d2 = (u32)gen_range(h, ND);
-        const u32 i2 = (u32)gen_range(h, E);
+        if (k2 == 1) d2 = sample_at(p, (u32)gen_range(h, ND), ND);
+        const u32 i2 = sample_at(p, (u32)gen_range(h, E), E);
         if (lane == 0) {
           *(ulonglong2*)&srngla[0] = make_ulonglong2(h.s0, h.s1); *(ulonglong2*)&srngla[2] = make_ulonglong2(h.s2, h.s3);
           *(uint4*)&sla[LA_KIND] = make_uint4((u32)k2, i2, d2, 0u);
@@ -1884,7 +1891,7 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
       uint2 abA = make_uint2(0, 0), abD = make_uint2(0, 0);
       if (kind == 0) {
         if (E) {
-          idx = (u32)gen_range(g, E);
+          idx = sample_at(p, (u32)gen_range(g, E), E);
           slot = ITEMS(idx);
           last = ITEMS(E - 1);
           if constexpr (IDX) {
@@ -1903,8 +1910,8 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
         }
       } else if (ND) {
         if (2ULL * ND >= E) { err = FCM_EINVAL; break; }       // reference spins forever (FIXME :307)
-        didx = (u32)gen_range(g, ND);
-        idx = (u32)gen_range(g, E);                     // the next draw does not depend on the loaded pair
+        didx = sample_at(p, (u32)gen_range(g, ND), ND);
+        idx = sample_at(p, (u32)gen_range(g, E), E);                     // the next draw does not depend on the loaded pair
         dpair = DBL(didx);
         slot = ITEMS(idx);
         if constexpr (IDX) {
@@ -1931,7 +1938,7 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
             single = rev == FCM_NONE;
           }
           if (single) break;
-          idx = (u32)gen_range(g, E);
+          idx = sample_at(p, (u32)gen_range(g, E), E);
           slot = ITEMS(idx);
         }
         const bool first = g.next() < 0x8000000000000000ULL;   // gen_bool(0.5)

@@ -691,6 +691,13 @@ extern "C" int fcm_ensemble_set_kernel(fcm_ensemble* e, int kind) {
   return FCM_OK;
 }
 
+extern "C" int fcm_ensemble_set_policy(fcm_ensemble* e, int policy) {
+  REQUIRE(e, "ensemble is null");
+  REQUIRE(policy == 0 || policy == 1, "sampler policy must be 0 (element r) or 1 (element len-1-r)");
+  e->p.sample_policy = (u32)policy;
+  return FCM_OK;
+}
+
 extern "C" int fcm_ensemble_set_stats(fcm_ensemble* e, int on) {
   REQUIRE(e, "ensemble is null");
   e->stats = on != 0;

@@ -202,6 +202,7 @@ struct EnsParams {
   // settings
   u64 bmin[FCM_MAXB], bmax[FCM_MAXB];
   int nmin, nmax;
+  u32 sample_policy;                // edge-sampler policy (fcm_ensemble_set_policy): 0 = element r, 1 = element len-1-r
   double cum[3], scale;             // WeightedIndex<f64>
   // clique moves (src/lib.rs:214-290); cq_norders = 0 when the ensemble was created without them
   int cq_norders;                   // cliques_by_order.len()

@@ -483,6 +483,10 @@ class MCMCSampler:
         return {"n": n.value, "npairs": npairs.value, "nchains": nch.value, "max_common_nbhd": maxc.value,
                 "bytes_per_chain": bpc.value}
 
+    def set_policy(self, policy):
+        """edge-sampler policy seam (include/fcm.h): 0 = element r of the container (default), 1 = element len-1-r"""
+        check(lib().fcm_ensemble_set_policy(self.h, int(policy)))
+
     def set_stats(self, on):
         """Switch the neighbourhood-size statistic (sumK / nonempty of read_all) on (default) or off."""
         check(lib().fcm_ensemble_set_stats(self.h, 1 if on else 0))

@@ -208,6 +208,13 @@ int fcm_ensemble_set_bounds(fcm_ensemble* e, const uint64_t* bounds_min, int nmi
  * flag_count, accept/reject and the trace are identical. */
 int fcm_ensemble_set_kernel(fcm_ensemble* e, int kind);
 
+/* The edge-sampler policy, i.e. which element of the insertion-ordered edge container Graph::sample_edge /
+ * sample_double_edge (external flag-complex crate; src/lib.rs:293,306,309) return for a draw r = gen_range(0..len):
+ * 0 (default) = element r, the documented assumption of oracle/fcm_oracle.cpp; 1 = element len-1-r.  Policy 1 is not a
+ * claim about the crate: the crate's source is not available here (parity unpinned), and this switch is the single place
+ * where its real rule goes once known - the tests show the CUDA path and the oracle change together under it. */
+int fcm_ensemble_set_policy(fcm_ensemble* e, int policy);
+
 /* Instrumentation switch.  on (default): every non-empty proposal adds its neighbourhood size
  * |State::edgeset_neighborhood| (src/lib.rs:99-111) to the statistic fcm_ensemble_read_all returns
  * in stats[2].  off: the statistic stands still (a double-edge move then skips the size of the union

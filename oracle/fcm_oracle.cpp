@@ -170,6 +170,7 @@ struct WeightedIndexF64 {
 //   by the normalised pair [min,max]; sample_double_edge returns that [min,max].
 //   An empty set returns None WITHOUT consuming a draw.
 // ---------------------------------------------------------------------------------------------
+static int g_sample_policy = 0;          // see Graph::at (process-wide: tests set it, run, and set it back)
 static inline u64 ekey(Node a, Node b) { return ((u64)a << 32) | b; }
 
 struct EdgeSet {
@@ -209,14 +210,17 @@ struct Graph {
     dbl.swap_remove(std::min(f, t), std::max(f, t));
   }
   void set_edge(Node f, Node t, bool add) { if (add) add_edge(f, t); else remove_edge(f, t); }
+  // THE POLICY SEAM: which element a draw r = gen_range(0..len) names.  0 = element r (the documented assumption),
+  // 1 = element len-1-r (exists to show that the CUDA path follows the oracle when the policy changes; orc_set_policy)
+  static size_t at(size_t r, size_t len) { return g_sample_policy ? len - 1 - r : r; }
   bool sample_edge(Xoshiro256SS& rng, Edge& out) const {
     if (edges.items.empty()) return false;
-    out = edges.items[gen_range_u64(rng, edges.items.size())];
+    out = edges.items[at(gen_range_u64(rng, edges.items.size()), edges.items.size())];
     return true;
   }
   bool sample_double_edge(Xoshiro256SS& rng, Edge& out) const {
     if (dbl.items.empty()) return false;
-    out = dbl.items[gen_range_u64(rng, dbl.items.size())];
+    out = dbl.items[at(gen_range_u64(rng, dbl.items.size()), dbl.items.size())];
     return true;
   }
   // [a,b] with a > b, once per adjacent pair (asserted at src/lib.rs:344)
@@ -849,6 +853,7 @@ void* orc_sampler_new(u32 n, u64 ne, const u32* edges, u64 seed, double target_r
   return s;
 }
 void orc_sampler_free(void* h) { delete (Sampler*)h; }
+void orc_set_policy(int policy) { g_sample_policy = policy ? 1 : 0; }
 void orc_sampler_set_bounds(void* h, const u64* mn, int nmin, const u64* mx, int nmax) {
   Sampler* s = (Sampler*)h;
   s->bounds.flag_count_min.assign(mn, mn + nmin);

@@ -98,6 +98,7 @@ pub const FCM_NOALLOC_MAXW: u32 = 64;
 #[link(name = "fcm")]
 extern "C" {
     pub fn fcm_graph_status(g: *mut FcmGraph) -> c_int;
+    pub fn fcm_ensemble_set_policy(e: *mut FcmEnsemble, policy: c_int) -> c_int;
     pub fn fcm_comm_create(ctx: *mut FcmCtx, kind: c_int, rank: u32, nranks: u32, out: *mut *mut FcmComm,
                            handle_out: *mut u8) -> c_int;
     pub fn fcm_comm_connect(c: *mut FcmComm, handles: *const u8) -> c_int;

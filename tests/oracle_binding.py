@@ -55,6 +55,8 @@ def lib():
     L.orc_sampler_free.restype = None
     L.orc_sampler_set_bounds.argtypes = [vp, vp, i32, vp, i32]
     L.orc_sampler_set_bounds.restype = None
+    L.orc_set_policy.argtypes = [i32]
+    L.orc_set_policy.restype = None
     L.orc_sampler_steps.argtypes = [vp, u64, vp]
     L.orc_sampler_next.argtypes = [vp]
     L.orc_sampler_info.argtypes = [vp, P(u64), P(u64), P(u64), P(u64), P(u64), P(i32), P(i32), P(i32)]
@@ -188,6 +190,11 @@ class Rng:
     def weighted_index(self, weights):
         w = np.asarray(weights, dtype=np.float64)
         return int(lib().orc_weighted_index(_p(w), int(w.size), _p(self.s), None, None))
+
+
+def set_policy(policy):
+    """edge-sampler policy of the oracle (process-wide): 0 = element r, 1 = element len-1-r"""
+    lib().orc_set_policy(int(policy))
 
 
 class Sampler:

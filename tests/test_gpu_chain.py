@@ -467,3 +467,34 @@ def test_all_moves_fuzz_random_graphs(block, ctx):
         s.close()
     assert ran >= 5
     assert rejected > 0
+
+
+@pytest.mark.parametrize("kernel", [0, 1, 2])
+def test_sampler_policy_seam(kernel, ctx, graphs):
+    """the edge-sampler policy of the external crate (which element a draw names) is an ASSUMPTION isolated
+    behind one switch.  Under a second policy (element len-1-r) the CUDA path and the oracle must still agree proposal by
+    proposal, and both must differ from the default policy's trajectory: swapping in the crate's real rule is one place
+    on each side (sample_at in fcm_chain.cu, Graph::at in oracle/fcm_oracle.cpp)."""
+    n, e = graphs["c2_chunglu_279"]                       # has double edges: both containers are sampled
+    traces = {}
+    try:
+        for policy in (0, 1):
+            orc.set_policy(policy)
+            s = fcm.initialize_new_sampler(ctx, n, e, [7, 8], target_relaxation=0.01, simple=True)
+            s.set_kernel(kernel)
+            s.set_policy(policy)
+            o = orc.Sampler(n, e, 8, 0.01)
+            got, want = s.step_trace(3000, 1), o.steps(3000)
+            assert_trace_equal(got, want)
+            compare_chain(s, 1, o)
+            traces[policy] = got
+            s.close()
+    finally:
+        orc.set_policy(0)
+    assert not np.array_equal(traces[0]["a"], traces[1]["a"])          # the policy does decide the trajectory
+    with pytest.raises(fcm.FcmError):
+        s2 = fcm.initialize_new_sampler(ctx, n, e, [1], simple=True)
+        try:
+            s2.set_policy(2)
+        finally:
+            s2.close()
