@@ -293,6 +293,10 @@ enum { PK_KIND = 0, PK_SLOT, PK_DELME, PK_IDX, PK_DIDX, PK_DPAIR, PK_LAST, PK_QP
 #define CQ_SCRATCH 160                  // u32 words behind the header: clique_swap's rank / row tables (128) + perm_a while it is drawn (32)
 #define CQ_BYTES (3 * FCM_MAXCQ * 4 + 64 + CQ_SCRATCH * 4)
 // staging block of the index hot path (idx_proposal), laid over the full path's arrays behind SM_TILE
+#ifndef FCM_CQ_PREFETCH
+#define FCM_CQ_PREFETCH 0              // clique moves: L2 prefetch of the next edit's orientation words - measured SLOWER (53.5 vs 56.8 M
+                                       // proposals/s, default mix on C3): the path is bound by instruction fetch / issue, not by the round trips
+#endif
 #ifndef FCM_LA
 #define FCM_LA 0                       // look-ahead: measured no gain on B200 (profiles/README.md r02_h), off; -DFCM_LA=1 builds it
 #endif
@@ -700,6 +704,7 @@ __device__ __forceinline__ bool hot_tag(const G32& g, int c, bool flip, const u3
     TZ |= ((1u << nZ) - 1) << (c + nY + nY2);
     __syncwarp();
     if (lane >= c && lane < c + ne) a = A32[src[lane - c]];
+#pragma unroll 1                                         // (unrolled it is 350 instructions at every inlined copy: the loops that call this live in the instruction cache)
     for (int k = 0; k < ne; k++) a |= ((a >> src[k]) & 1u) << (c + k);
   }
   const u32 allow = (X & bit) ? (X | TY | TY2 | TZ) : (TY & bit) ? (TY | TZ) : (TY2 & bit) ? (TY2 | TZ) : (TZ & bit) ? TZ : 0u;
@@ -940,6 +945,21 @@ __device__ u32 find_pair(const EnsParams& p, u32 a, u32 b) {
   return FCM_NONE;
 }
 
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// The edits of a clique move are counted one after the other, and each one waits a DRAM round trip for the orientation
+// words its pair's triangles / 4-cliques name.  While edit t's words are in flight, the words edit t+1 will ask for are
+// pulled into L2 (the static entries that name them are L2 hits): edit t+1 then finds them there - with edit t's own
+// change already in them, since that is written through L2 too.  Nothing is held in registers or shared memory.
+__device__ __forceinline__ void clique_prefetch_edit(const EnsParams& p, const u32* cb, const u32* ori, u32 slot, u32 W32, int lane) {
+  const uint4 i0 = __ldg(&p.pinfo[2 * (slot >> 1)]), i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]);
+  const int c = (int)i1.x, m = (int)i1.y;
+  if (c > NARROW_C) return;
+  if (lane < c) { const uint2 t = __ldg(&p.tri[i0.z + lane]); prefetch_l2(&ori[t.x >> 5]); prefetch_l2(&ori[t.y >> 5]); }
+  if (lane < m) prefetch_l2(&ori[__ldg(&p.k4[i0.w + lane]) >> 15]);
+  if (lane + 32 < m) prefetch_l2(&ori[__ldg(&p.k4[i0.w + 32 + lane]) >> 15]);
+  if (lane == 0) prefetch_l2(&ori[slot >> 5]);             // the word the edit rewrites
+}
+
 // kind 2 = clique_permute, 3 = clique_swap.  The chain's RNG state (after the move-kind draw) and all
 // other state are in HBM (the hot stretch has been closed).  Returns 0 or an FCM_E* code.
 __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned char* wb, int lane, int kind,
@@ -1165,6 +1185,7 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
         u32* const sA32 = (u32*)(wb + SM_A);
         OriReq r;
         idx_issue(p, ori, i0.z, cc, i0.w, (int)i1.y, !(slot & 1), lane, r);
+        if (FCM_CQ_PREFETCH && t + 1 < nedit) clique_prefetch_edit(p, cb, ori, s.edits[2 * (t + 1)], W32, lane);
         const G32 g = idx_finish(p, ori, i0.w, (int)i1.y, r, sA32, lane);
         // first the flip path's tagged single-mask graph (<= 32 tagged copies, <= DELTA_SD + 1 vertices);
         // when it does not fit, the general tagged count on the same gathered rows
