@@ -89,7 +89,8 @@ extern "C" int fcm_ctx_destroy(fcm_ctx* c) {
   cudaEventDestroy(c->ev1);
   cudaStreamDestroy(c->own);
   if (c->pin) cudaFreeHost(c->pin);
-  for (int i = 0; i < 2; i++) { if (c->stage_host[i]) cudaFreeHost(c->stage_host[i]); if (c->stage_ev[i]) cudaEventDestroy(c->stage_ev[i]); }
+  for (int i = 0; i < 2; i++) if (c->stage_host[i]) cudaFreeHost(c->stage_host[i]);
+  for (int i = 0; i < 16; i++) if (c->stage_evs[i]) cudaEventDestroy(c->stage_evs[i]);
   delete c;
   return FCM_OK;
 }
@@ -121,39 +122,44 @@ extern "C" int fcm_ctx_timer_end(fcm_ctx* c, float* ms) {
 extern "C" uint64_t fcm_ctx_launches(const fcm_ctx* c) { return c ? c->launches : 0; }
 
 // Big uploads from pageable host memory (an edge list is 8 bytes per edge: 66 MB at C4).  The driver's own pageable path
-// copies through one thread; here the list goes through two pinned 8 MB buffers, filled by several host threads while
-// the previous chunk is on the wire.  Small lists take the plain call.
+// copies through one thread.  Here FCM_STAGE_THREADS host threads (spawned once per call) each take one stripe of the list
+// and push it through their own two slices of the context's pinned staging buffers: fill a slice with memcpy, enqueue
+// its cudaMemcpyAsync on the context stream, fill the other slice while that one is on the wire.  The copies of all
+// threads land on the same stream (they write disjoint ranges, their order does not matter).  Small lists take the plain call.
+#define FCM_STAGE_THREADS 8
 int fcm_upload_edges(fcm_ctx* c, void* dst_dev, const void* src_host, size_t bytes) {
   cudaStream_t s = c->stream;
   if (bytes < (4u << 20)) { FCM_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, s)); return FCM_OK; }
   for (int i = 0; i < 2; i++)
-    if (!c->stage_host[i]) {
-      FCM_CUDA(cudaHostAlloc((void**)&c->stage_host[i], FCM_STAGE_BYTES, cudaHostAllocDefault));
-      FCM_CUDA(cudaEventCreateWithFlags(&c->stage_ev[i], cudaEventDisableTiming));
+    if (!c->stage_host[i]) FCM_CUDA(cudaHostAlloc((void**)&c->stage_host[i], FCM_STAGE_BYTES, cudaHostAllocDefault));
+  for (int i = 0; i < 2 * FCM_STAGE_THREADS; i++)
+    if (!c->stage_evs[i]) FCM_CUDA(cudaEventCreateWithFlags(&c->stage_evs[i], cudaEventDisableTiming));
+  const int nth = (int)std::max(1u, std::min(std::thread::hardware_concurrency(), (unsigned)FCM_STAGE_THREADS));
+  const size_t slice = (FCM_STAGE_BYTES / FCM_STAGE_THREADS) & ~(size_t)4095;      // per thread and buffer: 1 MB
+  const size_t stripe = ((bytes + nth - 1) / nth + 4095) & ~(size_t)4095;
+  const int device = c->device;
+  std::vector<cudaError_t> err(nth, cudaSuccess);
+  std::vector<std::thread> th;
+  for (int t = 0; t < nth; t++) th.emplace_back([&, t]() {
+    cudaError_t e = cudaSetDevice(device);
+    const size_t lo = std::min(bytes, stripe * t), hi = std::min(bytes, stripe * (t + 1));
+    int buf = 0;
+    for (size_t done = lo; done < hi && e == cudaSuccess; buf ^= 1) {
+      const size_t now = std::min(slice, hi - done);
+      unsigned char* const d = c->stage_host[buf] + slice * t;
+      cudaEvent_t ev = c->stage_evs[2 * t + buf];
+      e = cudaEventSynchronize(ev);                          // the copy that last used this slice has left it
+      if (e != cudaSuccess) break;
+      memcpy(d, (const unsigned char*)src_host + done, now);
+      e = cudaMemcpyAsync((unsigned char*)dst_dev + done, d, now, cudaMemcpyHostToDevice, s);
+      if (e == cudaSuccess) e = cudaEventRecord(ev, s);
+      done += now;
     }
-  const int nth = (int)std::max(1u, std::min(std::thread::hardware_concurrency(), 4u));
-  size_t done = 0;
-  int buf = 0;
-  while (done < bytes) {
-    const size_t now = std::min<size_t>(FCM_STAGE_BYTES, bytes - done);
-    FCM_CUDA(cudaEventSynchronize(c->stage_ev[buf]));      // the copy that last used this buffer has left it
-    unsigned char* const d = c->stage_host[buf];
-    const unsigned char* const sp = (const unsigned char*)src_host + done;
-    if (nth == 1 || now < (1u << 20)) memcpy(d, sp, now);
-    else {
-      std::vector<std::thread> th;
-      const size_t per = (now / nth + 4095) & ~(size_t)4095;
-      for (int t = 0; t < nth; t++) {
-        const size_t a = std::min(now, per * t), b = std::min(now, per * (t + 1));
-        if (b > a) th.emplace_back([=]() { memcpy(d + a, sp + a, b - a); });
-      }
-      for (auto& t : th) t.join();
-    }
-    FCM_CUDA(cudaMemcpyAsync((unsigned char*)dst_dev + done, d, now, cudaMemcpyHostToDevice, s));
-    FCM_CUDA(cudaEventRecord(c->stage_ev[buf], s));
-    done += now;
-    buf ^= 1;
-  }
+    err[t] = e;
+  });
+  for (auto& t : th) t.join();
+  for (int t = 0; t < nth; t++)
+    if (err[t] != cudaSuccess) { fcm_set_error("edge-list upload: %s", cudaGetErrorString(err[t])); return FCM_ECUDA; }
   return FCM_OK;
 }
 

@@ -32,7 +32,7 @@ struct fcm_ctx {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   u64 launches = 0;
   unsigned char* stage_host[2] = {nullptr, nullptr};   // pinned staging of big host -> device uploads (edge lists), FCM_STAGE_BYTES each
-  cudaEvent_t stage_ev[2] = {nullptr, nullptr};
+  cudaEvent_t stage_evs[16] = {};                      // per staging thread and slice: the copy out of it has completed
   u64* pin = nullptr;               // FCM_PIN_WORDS of pinned host memory: small read-backs that must not take the
                                     // driver's pageable-copy path (it blocks the other host threads' launches)
 };
