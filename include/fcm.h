@@ -13,6 +13,11 @@
  *     (src/lib.rs:65,86,104,309); a Rust shim turns non-zero into panic!().
  *   - no CPU fallback: every compute entry point fails with FCM_ENODEVICE when no CUDA device
  *     is usable.
+ *   - process-global side effects, all on the device of the context: fcm_ctx_create raises the release threshold of the
+ *     device's default memory pool (memory of destroyed graphs is kept for the next one: flagser_count is called over and
+ *     over by the research binaries); fcm_ensemble_create raises cudaLimitPersistingL2CacheSize to cover the clique index
+ *     (the window itself is a per-launch attribute, no stream is modified; fcm_ensemble_destroy resets the persisting
+ *     lines); loading the library reserves ~4.1 MB per GPU for fcm_graph_count_noalloc's static scratch.
  *   - a handle (ctx / graph / ensemble) is owned by one host thread at a time (the reference's
  *     `&mut self`, src/lib.rs:61,81,181); different handles may be used from different threads.
  */
