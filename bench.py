@@ -516,15 +516,16 @@ def main():
         z = np.load(os.path.join(ROOT, "tests", "golden", "fixtures.npz"))
         cfgs = {}
         cases = [("c1", 200, z["counterexample_seo_greedy_5_start"].reshape(-1, 2).astype(np.uint32), 1,
-                  "flag_file_examples/counterexample_seo_greedy_5_start.flag, `sample -s 0` (1 chain, step = sample_distance proposals)"),
+                  "flag_file_examples/counterexample_seo_greedy_5_start.flag, `sample -s 0` (1 chain, step = min(sample_distance, 20000 / 4000) proposals)"),
                  ("c2", 279, z["c2_chunglu_279"].reshape(-1, 2).astype(np.uint32), 1, "C. elegans-shaped Chung-Lu graph (279 nodes, 2200 edges), 1 chain"),
                  ("c3_1024", n, e, 1024, "ER n=2000 p=0.05 (C3), 1024 batched chains, step = %d proposals per chain" % P)]
         for name, cn, ce, nch, what in cases:
             entry = {"workload": what, "chains": nch}
             for mixname, simple in (("simple", True), ("default_mix", False)):
                 sc_ = fcm.initialize_new_sampler(ctx, cn, ce, list(range(nch)), target_relaxation=0.01, simple=simple)
-                Pc = sc_.sample_distance if nch == 1 else (P if simple else max(P // 10, 1))
-                Pc = min(Pc, 100000)
+                # a step of a one-chain config = sample_distance proposals (src/bin/sample.rs:102), capped so that the whole
+                # default bench stays within minutes: these legs report rates
+                Pc = min(sc_.sample_distance, 20000 if simple else 4000) if nch == 1 else (P if simple else max(P // 10, 1))
                 sc_.set_stats(False)
                 sc_.step(Pc)
                 ctx.synchronize()
