@@ -1829,8 +1829,10 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
 // IDX = true: the hot path reads the static clique index + the chain's orientation bits;
 // IDX = false: it gathers from the chain's adjacency rows (graphs too large for the index).
 // INSTR = true: per-proposal trace and the neighbourhood-size statistic (sumK / nonempty) are produced.
-template <bool IDX, bool INSTR, bool DEEP>
-__global__ void __launch_bounds__(128, FCM_CHAIN_MINBLOCKS)
+// MINB = resident blocks per SM the kernel is compiled for: 7 (28 chains per SM, 72 registers per thread: 4096 chains in one
+// wave) or 4 (16 chains per SM, 128 registers, no spills) for ensembles that four blocks per SM already hold in one wave.
+template <bool IDX, bool INSTR, bool DEEP, int MINB>
+__global__ void __launch_bounds__(128, MINB)
 chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec* __restrict__ trace, u32 trace_chain,
                   u32 smem_per_warp, int force_full) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -2243,7 +2245,7 @@ int fcm_chain_launch_replicate(fcm_ensemble* e) {
   return FCM_OK;
 }
 
-template <bool IDX, bool INSTR, bool DEEP>
+template <bool IDX, bool INSTR, bool DEEP, int MINB>
 static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
   EnsParams p = e->p;
   // ensembles with clique moves size the local matrix M for the union neighbourhood of two cliques; when
@@ -2262,7 +2264,7 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
     for (int w = 4; w >= 1; w >>= 1) {
       if (per_warp * w > e->ctx->smem_optin) continue;
       // blocks per SM: registers (72 per thread, 64 K per SM => 28 warps) and shared memory
-      const size_t resident = std::min<size_t>(28 / w, (size_t)(227 * 1024) / (per_warp * w + 1024)) * w;
+      const size_t resident = std::min<size_t>((MINB * 4) / w, (size_t)(227 * 1024) / (per_warp * w + 1024)) * w;
       if (resident > best) { best = resident; wpb = w; }
     }
   }
@@ -2272,15 +2274,15 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
   // shapes (src/bin/all_cxs.rs runs a private State per OS thread) must not interleave "set the size" and "launch"
   static std::mutex launch_mu;
   std::lock_guard<std::mutex> launch_lock(launch_mu);
-  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR, DEEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR, DEEP, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
     // shared-memory carve-out: what the resident blocks need and no more - the rest of the 256 KB stays L1 (spilled
     // registers, the static index entries a proposal re-reads).  FCM_CARVEOUT=<percent> overrides (measurements).
-    const size_t per_sm = std::min<size_t>(28 / wpb, (size_t)(227 * 1024) / (smem + 1024));
+    const size_t per_sm = std::min<size_t>((MINB * 4) / wpb, (size_t)(227 * 1024) / (smem + 1024));
     int pct = (int)((per_sm * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
     if (const char* cv = getenv("FCM_CARVEOUT")) pct = atoi(cv);
     pct = std::max(0, std::min(100, pct));
-    FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR, DEEP>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+    FCM_CUDA(cudaFuncSetAttribute(chain_step_kernel<IDX, INSTR, DEEP, MINB>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
   }
   const u32 blocks = (p.nchains + wpb - 1) / wpb;
   const u64 chunk = 1ULL << 24;                         // the kernel's per-launch counters are 32-bit
@@ -2293,7 +2295,7 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
     attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
     attr[0].val.accessPolicyWindow = e->l2_window;
     cfg.attrs = attr; cfg.numAttrs = e->l2_window.num_bytes ? 1 : 0;
-    FCM_CUDA(cudaLaunchKernelEx(&cfg, chain_step_kernel<IDX, INSTR, DEEP>, p, now, trace_dev ? trace_dev + done : (fcm_trace_rec*)nullptr,
+    FCM_CUDA(cudaLaunchKernelEx(&cfg, chain_step_kernel<IDX, INSTR, DEEP, MINB>, p, now, trace_dev ? trace_dev + done : (fcm_trace_rec*)nullptr,
                                 trace_chain, (u32)per_warp, (int)e->force_full));
     e->ctx->launches++;
   }
@@ -2301,17 +2303,25 @@ static int launch_step_mode(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_de
   return FCM_OK;
 }
 
-int fcm_chain_launch_step(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
+template <int MINB>
+static int launch_step_pick(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
   const bool idx = e->have_index && !e->force_rows, instr = trace_dev != nullptr || e->stats;
   // graphs that start with simplices beyond dimension DELTA_SD + 2 run the index kernel that counts deep cliques in
   // place; the others keep the leaner loop (a deep clique met later sends that proposal through cold_step: same result)
   if (idx && e->deep_hint)
-    return instr ? launch_step_mode<true, true, true>(e, nsteps, trace_dev, trace_chain)
-                 : launch_step_mode<true, false, true>(e, nsteps, trace_dev, trace_chain);
-  if (idx) return instr ? launch_step_mode<true, true, false>(e, nsteps, trace_dev, trace_chain)
-                        : launch_step_mode<true, false, false>(e, nsteps, trace_dev, trace_chain);
-  return instr ? launch_step_mode<false, true, false>(e, nsteps, trace_dev, trace_chain)
-               : launch_step_mode<false, false, false>(e, nsteps, trace_dev, trace_chain);
+    return instr ? launch_step_mode<true, true, true, MINB>(e, nsteps, trace_dev, trace_chain)
+                 : launch_step_mode<true, false, true, MINB>(e, nsteps, trace_dev, trace_chain);
+  if (idx) return instr ? launch_step_mode<true, true, false, MINB>(e, nsteps, trace_dev, trace_chain)
+                        : launch_step_mode<true, false, false, MINB>(e, nsteps, trace_dev, trace_chain);
+  return instr ? launch_step_mode<false, true, false, MINB>(e, nsteps, trace_dev, trace_chain)
+               : launch_step_mode<false, false, false, MINB>(e, nsteps, trace_dev, trace_chain);
+}
+int fcm_chain_launch_step(fcm_ensemble* e, u64 nsteps, fcm_trace_rec* trace_dev, u32 trace_chain) {
+  // ensembles that 4 blocks x 4 warps per SM hold in one wave get the 128-register instance (no spills: +5 % at
+  // 1024 / 2048 chains on C3, profiles/README.md); larger ones need 7 blocks per SM to stay in one wave
+  const bool small = (u64)e->p.nchains <= (u64)e->ctx->sm_count * 16;
+  return small ? launch_step_pick<4>(e, nsteps, trace_dev, trace_chain)
+               : launch_step_pick<FCM_CHAIN_MINBLOCKS>(e, nsteps, trace_dev, trace_chain);
 }
 
 int fcm_chain_launch_apply(fcm_ensemble* e, u32 chain, int nedits, int mode) {

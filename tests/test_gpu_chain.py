@@ -498,3 +498,26 @@ def test_sampler_policy_seam(kernel, ctx, graphs):
             s2.set_policy(2)
         finally:
             s2.close()
+
+
+@pytest.mark.parametrize("simple", [True, False])
+def test_large_ensemble_runs_the_seven_blocks_per_sm_instance(simple, ctx, graphs):
+    """Ensembles of more than 16 chains per SM run the kernel instance compiled for 7 blocks per SM (72 registers), smaller
+    ones the 128-register instance (fcm_chain_launch_step): 2500 chains here, three of them against the oracle, and the same
+    seeds in a small ensemble must give the same chains."""
+    n, e = graphs["c2_chunglu_279"]
+    mw = ds.MOVE_DISTRIBUTION_SIMPLE if simple else ds.MOVE_DISTRIBUTION
+    seeds = list(range(100, 2600))
+    s = fcm.initialize_new_sampler(ctx, n, e, seeds, target_relaxation=0.01, simple=simple)
+    steps = 600 if simple else 150
+    s.step(steps)
+    s.status()
+    small = fcm.initialize_new_sampler(ctx, n, e, [seeds[0], seeds[1234], seeds[2499]], target_relaxation=0.01, simple=simple)
+    small.step(steps)
+    for k, j in ((0, 0), (1234, 1), (2499, 2)):
+        o = orc.Sampler(n, e, seeds[k], 0.01, move_weights=mw)
+        o.steps(steps, trace=False)
+        compare_chain(s, k, o)
+        compare_chain(small, j, o)
+    s.close()
+    small.close()
