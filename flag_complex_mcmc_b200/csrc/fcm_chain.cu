@@ -298,7 +298,8 @@ enum { PK_KIND = 0, PK_SLOT, PK_DELME, PK_IDX, PK_DIDX, PK_DPAIR, PK_LAST, PK_QP
                                        // proposals/s, default mix on C3): the path is bound by instruction fetch / issue, not by the round trips
 #endif
 #ifndef FCM_LA
-#define FCM_LA 0                       // look-ahead: measured no gain on B200 (profiles/README.md r02_h), off; -DFCM_LA=1 builds it
+#define FCM_LA 0                       // look-ahead in the 7-blocks-per-SM instance: measured a loss there (28 warps per SM hide the latency
+                                       // themselves: 502.6 vs 511 M), off; the 4-blocks-per-SM instance of small ensembles has it on (LA below)
 #endif
 #ifndef FCM_LA2
 #define FCM_LA2 1
@@ -1495,7 +1496,8 @@ __device__ __forceinline__ G32 stage_finish(const EnsParams& p, const u32* ori, 
   return g;
 }
 
-template <bool INSTR, bool DEEP>
+// LA: the look-ahead is compiled in (ensembles of at most 16 chains per SM: +6 % at 1024 chains, +4 % at 64)
+template <bool INSTR, bool DEEP, bool LA>
 __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, unsigned char* const wb, const int lane,
                                             const u32 step, const u32 nsteps, fcm_trace_rec* trace, int force_full,
                                             u32& sumK, u32& nonempty) {
@@ -1617,7 +1619,7 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
   // ---- look-ahead, level 1: the next proposal's kind and container indices; its entries start travelling ----
   {
     bool nla = false;
-    if (FCM_LA && step + 1 < nsteps) {
+    if (LA && step + 1 < nsteps) {
       Rng h = g;
       const int k2 = draw_kind(p, h);
       if (k2 == 0 ? E != 0 : (k2 == 1 && ND != 0 && 2ULL * ND < E)) {
@@ -1737,7 +1739,7 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
   // ---- look-ahead, level 2: the entries have landed - the next proposal's pair records and orientation words ----
   cp_async_wait<0>();
   __syncwarp();
-  if (FCM_LA2 && sla[LA_VALID]) {
+  if (LA && FCM_LA2 && sla[LA_VALID]) {
     if (lane < 2) {
       const u32 s2 = sla[LA_SLOT];
       cp_async16((u32)__cvta_generic_to_shared(&spinfo[lane]), &p.pinfo[2 * (s2 >> 1) + lane]);
@@ -1805,12 +1807,12 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
         const bool changed = nslot != sla[LA_SLOT] || ndp != sla[LA_DPAIR];
         const bool oriclash = (nslot >> 5) == wa || (nslot >> 5) == wd || (nmove && ((ndp >> 4) == wa || (ndp >> 4) == wd));
         sla[LA_SLOT] = nslot; sla[LA_DPAIR] = ndp;
-        sla[LA_L2] = (!FCM_LA2 || changed || oriclash) ? 0u : 1u;
+        sla[LA_L2] = (!LA || !FCM_LA2 || changed || oriclash) ? 0u : 1u;
       }
     }
     if (ok) sfc[lane] = fnew;
     __syncwarp();
-  } else if (FCM_LA2 && lane == 0 && sla[LA_VALID]) sla[LA_L2] = 1u;
+  } else if (LA && FCM_LA2 && lane == 0 && sla[LA_VALID]) sla[LA_L2] = 1u;
   if constexpr (INSTR) {
     if (trace != nullptr && lane == 0) {
       fcm_trace_rec tr;
@@ -1880,7 +1882,7 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
     if constexpr (IDX) { if (lane == 0) ((u32*)(wb + SM_TILE + ST_LA))[LA_VALID] = 0; __syncwarp(); }
     for (; step < nsteps; step++) {
       if constexpr (IDX) {
-        const int rc = idx_proposal<INSTR, DEEP>(p, cb, wb, lane, step, nsteps, trace, force_full, sumK, nonempty);
+        const int rc = idx_proposal<INSTR, DEEP, (MINB < FCM_CHAIN_MINBLOCKS) || FCM_LA>(p, cb, wb, lane, step, nsteps, trace, force_full, sumK, nonempty);
         if (rc == 1) { cold = true; break; }
         if (rc) { err = rc; break; }
         continue;
