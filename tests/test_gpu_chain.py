@@ -521,3 +521,19 @@ def test_large_ensemble_runs_the_seven_blocks_per_sm_instance(simple, ctx, graph
         compare_chain(small, j, o)
     s.close()
     small.close()
+
+
+def test_pair_numbering_is_internal(ctx, graphs, monkeypatch):
+    """Pair ids are an internal numbering ((big, small) order by default, first appearance with FCM_PAIR_ORDER=0, the
+    round-1 layout kept for A/B measurements): trajectories, containers and samples do not depend on it."""
+    n, e = graphs["c2_chunglu_279"]
+    out = {}
+    for order in ("1", "0"):
+        monkeypatch.setenv("FCM_PAIR_ORDER", order)
+        s = fcm.initialize_new_sampler(ctx, n, e, [5, 6], target_relaxation=0.01, simple=False)
+        o = orc.Sampler(n, e, 6, 0.01, move_weights=ds.MOVE_DISTRIBUTION)
+        assert_trace_equal(s.step_trace(400, 1), o.steps(400))
+        compare_chain(s, 1, o)
+        out[order] = (s.edgebits(1, 1)[0].tobytes(), s.read(1)["flag_count"])
+        s.close()
+    assert out["0"] == out["1"]
