@@ -552,8 +552,46 @@ __device__ __forceinline__ void red_adj_bit(const EnsParams& p, u32* a32, u32 fr
   if (add) atomicOr(w, m); else atomicAnd(w, ~m);
 }
 
+
+// L2 eviction priorities (build switches, measurements in profiles/README.md): FCM_IDX_KEEP = the static clique index
+// (pinfo / tri / k4, shared by every chain) is loaded with an evict_last policy; FCM_STATE_STREAM = the per-chain
+// orientation words are fetched with evict_first (a chain's words are not touched again before 4095 other chains'
+// traffic has passed through L2).
+#ifndef FCM_IDX_KEEP
+#define FCM_IDX_KEEP 0
+#endif
+#ifndef FCM_STATE_STREAM
+#define FCM_STATE_STREAM 0
+#endif
+__device__ __forceinline__ u64 l2_policy_keep() { u64 pol; asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol)); return pol; }
+__device__ __forceinline__ u64 l2_policy_stream() { u64 pol; asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol)); return pol; }
+__device__ __forceinline__ u32 ldg_idx(const u32* g) {
+#if FCM_IDX_KEEP
+  u32 v; asm("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(g), "l"(l2_policy_keep())); return v;
+#else
+  return __ldg(g);
+#endif
+}
+__device__ __forceinline__ uint2 ldg_idx(const uint2* g) {
+#if FCM_IDX_KEEP
+  uint2 v; asm("ld.global.nc.L2::cache_hint.v2.u32 {%0, %1}, [%2], %3;" : "=r"(v.x), "=r"(v.y) : "l"(g), "l"(l2_policy_keep())); return v;
+#else
+  return __ldg(g);
+#endif
+}
+__device__ __forceinline__ uint4 ldg_idx(const uint4* g) {
+#if FCM_IDX_KEEP
+  uint4 v; asm("ld.global.nc.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(g), "l"(l2_policy_keep())); return v;
+#else
+  return __ldg(g);
+#endif
+}
 __device__ __forceinline__ void cp_async4(u32 saddr, const void* g) {
+#if FCM_STATE_STREAM
+  asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 4, %2;" ::"r"(saddr), "l"(g), "l"(l2_policy_stream()) : "memory");
+#else
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(saddr), "l"(g) : "memory");
+#endif
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -644,9 +682,9 @@ struct OriReq { u32 sU, sV, wu, wv, e0, w0, e1, w1; };
 __device__ __forceinline__ void idx_issue(const EnsParams& p, const u32* ori, u32 o, int c, u32 k4o, int m, bool uBig,
                                           int lane, OriReq& r) {
   r.sU = r.sV = r.wu = r.wv = r.e0 = r.w0 = r.e1 = r.w1 = 0;
-  if (lane < c) { const uint2 t = __ldg(&p.tri[o + lane]); r.sU = uBig ? t.x : t.y; r.sV = uBig ? t.y : t.x; }
-  if (lane < m) r.e0 = __ldg(&p.k4[k4o + lane]);
-  if (lane + 32 < m) r.e1 = __ldg(&p.k4[k4o + 32 + lane]);
+  if (lane < c) { const uint2 t = ldg_idx(&p.tri[o + lane]); r.sU = uBig ? t.x : t.y; r.sV = uBig ? t.y : t.x; }
+  if (lane < m) r.e0 = ldg_idx(&p.k4[k4o + lane]);
+  if (lane + 32 < m) r.e1 = ldg_idx(&p.k4[k4o + 32 + lane]);
   if (lane < c) { r.wu = __ldcg(&ori[r.sU >> 5]); r.wv = __ldcg(&ori[r.sV >> 5]); }
   if (lane < m) r.w0 = __ldcg(&ori[r.e0 >> 15]);
   if (lane + 32 < m) r.w1 = __ldcg(&ori[r.e1 >> 15]);
@@ -665,7 +703,7 @@ __device__ __forceinline__ G32 idx_finish(const EnsParams& p, const u32* ori, u3
   if (lane < m) k4_scatter(r.e0, r.w0, A32);
   if (lane + 32 < m) k4_scatter(r.e1, r.w1, A32);
   for (int t = 64 + lane; t < m; t += 32) {
-    const u32 e = __ldg(&p.k4[k4o + t]);
+    const u32 e = ldg_idx(&p.k4[k4o + t]);
     k4_scatter(e, __ldcg(&ori[e >> 15]), A32);
   }
   const u32 tu = r.wu >> (r.sU & 30), tv = r.wv >> (r.sV & 30);   // lanes past c hold 0: never vote
@@ -952,12 +990,12 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 // pulled into L2 (the static entries that name them are L2 hits): edit t+1 then finds them there - with edit t's own
 // change already in them, since that is written through L2 too.  Nothing is held in registers or shared memory.
 __device__ __forceinline__ void clique_prefetch_edit(const EnsParams& p, const u32* cb, const u32* ori, u32 slot, u32 W32, int lane) {
-  const uint4 i0 = __ldg(&p.pinfo[2 * (slot >> 1)]), i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]);
+  const uint4 i0 = ldg_idx(&p.pinfo[2 * (slot >> 1)]), i1 = ldg_idx(&p.pinfo[2 * (slot >> 1) + 1]);
   const int c = (int)i1.x, m = (int)i1.y;
   if (c > NARROW_C) return;
-  if (lane < c) { const uint2 t = __ldg(&p.tri[i0.z + lane]); prefetch_l2(&ori[t.x >> 5]); prefetch_l2(&ori[t.y >> 5]); }
-  if (lane < m) prefetch_l2(&ori[__ldg(&p.k4[i0.w + lane]) >> 15]);
-  if (lane + 32 < m) prefetch_l2(&ori[__ldg(&p.k4[i0.w + 32 + lane]) >> 15]);
+  if (lane < c) { const uint2 t = ldg_idx(&p.tri[i0.z + lane]); prefetch_l2(&ori[t.x >> 5]); prefetch_l2(&ori[t.y >> 5]); }
+  if (lane < m) prefetch_l2(&ori[ldg_idx(&p.k4[i0.w + lane]) >> 15]);
+  if (lane + 32 < m) prefetch_l2(&ori[ldg_idx(&p.k4[i0.w + 32 + lane]) >> 15]);
   if (lane == 0) prefetch_l2(&ori[slot >> 5]);             // the word the edit rewrites
 }
 
@@ -1174,7 +1212,7 @@ __device__ __noinline__ int clique_step(const EnsParams& p, u32 chain, unsigned 
       const int sign = add ? 1 : -1;
       // index path: the pair's static entry holds its endpoints, list offset and length (one load, not three)
       uint4 i0 = make_uint4(0, 0, 0, 0), i1 = i0;
-      if (red) { i0 = __ldg(&p.pinfo[2 * (slot >> 1)]); i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]); }
+      if (red) { i0 = ldg_idx(&p.pinfo[2 * (slot >> 1)]); i1 = ldg_idx(&p.pinfo[2 * (slot >> 1) + 1]); }
       // the edge u -> v; dir 0 of a slot = big -> small
       const uint2 ft = red ? ((slot & 1) ? make_uint2(i0.y, i0.x) : make_uint2(i0.x, i0.y)) : slot_edge(p, slot);
       const u32 o = red ? i0.z : __ldg(&p.nb_off[slot >> 1]);
@@ -1428,19 +1466,19 @@ __device__ __forceinline__ void stage_issue(const EnsParams& p, const u32* ori, 
   u32 pk0 = 0, pk1 = 0;
   const u32 sbase = (u32)__cvta_generic_to_shared(stage + lane);
   if (lane < c) {
-    const uint2 t = __ldg(&p.tri[o + lane]);
+    const uint2 t = ldg_idx(&p.tri[o + lane]);
     const u32 sU = uBig ? t.x : t.y, sV = uBig ? t.y : t.x;
     cp_async4(sbase, &ori[sU >> 5]);
     cp_async4(sbase + 128, &ori[sV >> 5]);
     pk0 = (sU & 31u) | ((sV & 31u) << 5);
   }
   if (lane < m) {
-    const u32 e0 = __ldg(&p.k4[k4o + lane]);
+    const u32 e0 = ldg_idx(&p.k4[k4o + lane]);
     cp_async4(sbase + 256, &ori[e0 >> 15]);
     pk1 = e0 & 0x7fffu;
   }
   if (lane + 32 < m) {
-    const u32 e1 = __ldg(&p.k4[k4o + 32 + lane]);
+    const u32 e1 = ldg_idx(&p.k4[k4o + 32 + lane]);
     cp_async4(sbase + 384, &ori[e1 >> 15]);
     pk1 |= (e1 & 0x7fffu) << 15;
   }
@@ -1468,18 +1506,18 @@ __device__ __forceinline__ G32 stage_finish(const EnsParams& p, const u32* ori, 
   if (dropslot != FCM_NONE) {
     const u32 dw = dropslot >> 5, dm = ~(1u << (dropslot & 31));
     if (lane < c) {
-      const uint2 t = __ldg(&p.tri[o + lane]);
+      const uint2 t = ldg_idx(&p.tri[o + lane]);
       const u32 sU = uBig ? t.x : t.y, sV = uBig ? t.y : t.x;
       if ((sU >> 5) == dw) wu &= dm;
       if ((sV >> 5) == dw) wv &= dm;
     }
-    if (lane < m && (__ldg(&p.k4[k4o + lane]) >> 15) == dw) w0 &= dm;
-    if (lane + 32 < m && (__ldg(&p.k4[k4o + 32 + lane]) >> 15) == dw) w1 &= dm;
+    if (lane < m && (ldg_idx(&p.k4[k4o + lane]) >> 15) == dw) w0 &= dm;
+    if (lane + 32 < m && (ldg_idx(&p.k4[k4o + 32 + lane]) >> 15) == dw) w1 &= dm;
   }
   if (lane < m) k4_scatter_packed(pk1 & 0x7fffu, w0, A32);
   if (lane + 32 < m) k4_scatter_packed(pk1 >> 15, w1, A32);
   for (int t = 64 + lane; t < m; t += 32) {
-    const u32 e = __ldg(&p.k4[k4o + t]);
+    const u32 e = ldg_idx(&p.k4[k4o + t]);
     u32 w = __ldcg(&ori[e >> 15]);
     if (dropslot != FCM_NONE && (e >> 15) == (dropslot >> 5)) w &= ~(1u << (dropslot & 31));
     k4_scatter(e, w, A32);
@@ -1565,7 +1603,7 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
       last = ITEMS(E - 1);
       uint4 i0, i1;
       if (la2) { i0 = spinfo[0]; i1 = spinfo[1]; oriA = sla[LA_ORIA]; }
-      else { oriA = __ldcg(&ori[slot >> 5]); i0 = __ldg(&p.pinfo[2 * (slot >> 1)]); i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]); }
+      else { oriA = __ldcg(&ori[slot >> 5]); i0 = ldg_idx(&p.pinfo[2 * (slot >> 1)]); i1 = ldg_idx(&p.pinfo[2 * (slot >> 1) + 1]); }
       abA = make_uint2(i0.x, i0.y); oA = i0.z; kA = i0.w; cA = (int)i1.x; mA = (int)i1.y;
       live = !((oriA >> ((slot ^ 1) & 31)) & 1u);         // the reverse edge exists: empty transition
       sampled_edge = true;
@@ -1575,14 +1613,14 @@ __device__ __forceinline__ int idx_proposal(const EnsParams& p, u32* const cb, u
     {
       uint4 i0, i1;
       if (la2) { i0 = spinfo[2]; i1 = spinfo[3]; oriD = sla[LA_ORID]; }
-      else { oriD = __ldcg(&ori[dpair >> 4]); i0 = __ldg(&p.pinfo[2 * dpair]); i1 = __ldg(&p.pinfo[2 * dpair + 1]); }
+      else { oriD = __ldcg(&ori[dpair >> 4]); i0 = ldg_idx(&p.pinfo[2 * dpair]); i1 = ldg_idx(&p.pinfo[2 * dpair + 1]); }
       abD = make_uint2(i0.x, i0.y); oD = i0.z; kD = i0.w; cD = (int)i1.x; mD = (int)i1.y;
     }
     bool first_try = true;
     for (;;) {
       uint4 i0, i1;
       if (la2 && first_try) { i0 = spinfo[0]; i1 = spinfo[1]; oriA = sla[LA_ORIA]; }
-      else { oriA = __ldcg(&ori[slot >> 5]); i0 = __ldg(&p.pinfo[2 * (slot >> 1)]); i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]); }
+      else { oriA = __ldcg(&ori[slot >> 5]); i0 = ldg_idx(&p.pinfo[2 * (slot >> 1)]); i1 = ldg_idx(&p.pinfo[2 * (slot >> 1) + 1]); }
       abA = make_uint2(i0.x, i0.y); oA = i0.z; kA = i0.w; cA = (int)i1.x; mA = (int)i1.y;
       if (!((oriA >> ((slot ^ 1) & 31)) & 1u)) break;     // a single edge
       first_try = false;
@@ -1921,7 +1959,7 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
           last = ITEMS(E - 1);
           if constexpr (IDX) {
             oriA = __ldcg(&ORI(slot >> 5));
-            const uint4 i0 = __ldg(&p.pinfo[2 * (slot >> 1)]), i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]);
+            const uint4 i0 = ldg_idx(&p.pinfo[2 * (slot >> 1)]), i1 = ldg_idx(&p.pinfo[2 * (slot >> 1) + 1]);
             abA = make_uint2(i0.x, i0.y); oA = i0.z; kA = i0.w; cA = (int)i1.x; mA = (int)i1.y;
             live = !((oriA >> ((slot ^ 1) & 31)) & 1u);     // the reverse edge exists: empty transition
           } else {
@@ -1941,7 +1979,7 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
         slot = ITEMS(idx);
         if constexpr (IDX) {
           oriD = __ldcg(&ORI(dpair >> 4));
-          const uint4 i0 = __ldg(&p.pinfo[2 * dpair]), i1 = __ldg(&p.pinfo[2 * dpair + 1]);
+          const uint4 i0 = ldg_idx(&p.pinfo[2 * dpair]), i1 = ldg_idx(&p.pinfo[2 * dpair + 1]);
           abD = make_uint2(i0.x, i0.y); oD = i0.z; kD = i0.w; cD = (int)i1.x; mD = (int)i1.y;
         } else {
           abD = __ldg(&p.pair_ab[dpair]);
@@ -1952,7 +1990,7 @@ chain_step_kernel(const __grid_constant__ EnsParams p, u32 nsteps, fcm_trace_rec
           bool single;
           if constexpr (IDX) {
             oriA = __ldcg(&ORI(slot >> 5));
-            const uint4 i0 = __ldg(&p.pinfo[2 * (slot >> 1)]), i1 = __ldg(&p.pinfo[2 * (slot >> 1) + 1]);
+            const uint4 i0 = ldg_idx(&p.pinfo[2 * (slot >> 1)]), i1 = ldg_idx(&p.pinfo[2 * (slot >> 1) + 1]);
             abA = make_uint2(i0.x, i0.y); oA = i0.z; kA = i0.w; cA = (int)i1.x; mA = (int)i1.y;
             single = !((oriA >> ((slot ^ 1) & 31)) & 1u);
           } else {
