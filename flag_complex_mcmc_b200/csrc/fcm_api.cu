@@ -215,7 +215,7 @@ extern "C" int fcm_graph_destroy(fcm_graph* g) {
   if (!g) return FCM_OK;
   if (g->ctx) cudaSetDevice(g->ctx->device);
   cudaStream_t s = g->ctx ? g->ctx->stream : nullptr;
-  fcm_pool_free(g->adj, s); fcm_pool_free(g->csr_off, s); fcm_pool_free(g->csr, s); fcm_pool_free(g->order, s);
+  fcm_pool_free(g->adj, s); fcm_pool_free(g->csr_off, s); fcm_pool_free(g->csr, s); fcm_pool_free(g->order, s); fcm_pool_free(g->oldid, s);
   fcm_pool_free(g->overflow, s); fcm_pool_free(g->counts, s); fcm_pool_free(g->ctrl, s); fcm_pool_free(g->scratch, s);
   delete g;
   return FCM_OK;

@@ -23,8 +23,11 @@
 #include <cstring>
 #include <mutex>
 
+#include <cooperative_groups.h>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+
+namespace cg = cooperative_groups;
 
 #define DENSE_WARPS 4
 #define MAXL_DENSE (FCM_MAXD - 1)   // level l holds candidates for vertex index l+1
@@ -33,16 +36,161 @@
 // graph construction
 // ---------------------------------------------------------------------------------------------------
 __global__ void set_bits_kernel(const uint2* __restrict__ edges, u64 ne, u32 n, u32 W, int normalise,
-                                u64* __restrict__ adj, u32* __restrict__ ctrl) {
+                                const u32* __restrict__ newid, u64* __restrict__ adj, u32* __restrict__ ctrl) {
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   u64 stride = (u64)gridDim.x * blockDim.x;
   for (; i < ne; i += stride) {
     uint2 e = edges[i];
     u32 a = e.x, b = e.y;
     if (a >= n || b >= n || a == b) { atomicExch(&ctrl[CT_ERR], 1u); continue; }
-    if (normalise && a < b) { u32 t = a; a = b; b = t; }   // src/lib.rs:126-129: edge big -> small
+    if (normalise && a < b) { u32 t = a; a = b; b = t; }   // src/lib.rs:126-129: edge big -> small (the caller's ids decide)
+    if (newid) { a = newid[a]; b = newid[b]; }             // the graph's internal numbering (locality order below)
     atomicOr((unsigned long long*)&adj[(u64)a * W + (b >> 6)], 1ULL << (b & 63));
   }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// locality order of the vertices (large graphs)
+// ---------------------------------------------------------------------------------------------------
+// The count is invariant under renumbering the vertices, its speed is not: count_local_kernel gathers the k x k tile
+// of a source by bit probes into the rows of its out-neighbours, and with ids scattered over the graph (BASELINE
+// config 4: ids are hashes of the position) every probe is its own sector.  Graphs beyond LOC_MIN_N vertices are
+// therefore built under an internal numbering in which neighbours get nearby ids; fcm_graph_cells maps ids back
+// (EmitArgs::oldid), nothing else of the API sees vertex ids.  The order, all on the device in ONE cooperative launch
+// over the uploaded edge list (no CSR exists yet):
+//   1. breadth-first levels of the undirected graph from vertex 0, level-synchronous sweeps over the edge list;
+//   2. the same from the farthest vertex found (largest level, smallest id): levels along the graph's long axis;
+//   3. two Jacobi sweeps x[a] <- (x[a] + sum of x[b] over the edges a -> b) / (outdeg(a) + 1) on the level as a fixed-
+//      point number, which turns the handful of levels into a smooth coordinate (C4: 6 levels -> median |i - j| over
+//      the edges 3 829 -> 1 234 of 31 346; the positions' own long axis gives 1 228; tools/relabel_probe.py);
+//   4. stable radix sort of the vertices by x.
+// Integer arithmetic throughout: every rank of a sharded count builds the same numbering (the shards are dealt from
+// the degree order of the renumbered graph).  FCM_RELABEL=0 switches it off, =1 forces it for every graph (tests).
+#define LOC_MIN_N 4096u
+#define LOC_INF 0xffffffffu
+#define LOC_FRAC 20
+#define LOC_MAXLEV 63u
+__global__ void __launch_bounds__(256)
+locality_kernel(const uint2* __restrict__ edges, u64 ne, u32 n, u32* lev, u32* x, unsigned long long* acc, u32* deg,
+                u32* ctl, unsigned long long* far, u32* iota) {
+  cg::grid_group grid = cg::this_grid();
+  const u64 tid = (u64)blockIdx.x * blockDim.x + threadIdx.x, nt = (u64)gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31;
+  u32 stamp = 0, root = 0;
+  for (int pass = 0; pass < 2; pass++) {
+    for (u64 i = tid; i < n; i += nt) __stcg(&lev[i], i == root ? 0u : LOC_INF);
+    grid.sync();
+    for (u32 L = 0;; L++) {
+      stamp++;
+      bool any = false;
+      for (u64 i = tid; i < ne; i += nt) {
+        const uint2 e = __ldg(&edges[i]);
+        if (e.x >= n || e.y >= n) continue;              // reported by set_bits_kernel
+        const u32 la = __ldcg(&lev[e.x]), lb = __ldcg(&lev[e.y]);
+        if (la == L && lb == LOC_INF) { __stcg(&lev[e.y], L + 1); any = true; }
+        else if (lb == L && la == LOC_INF) { __stcg(&lev[e.x], L + 1); any = true; }
+      }
+      if (any) __stcg(&ctl[0], stamp);                   // this sweep reached a new vertex
+      grid.sync();
+      if (__ldcg(&ctl[0]) < stamp) break;                // (a thread already in the next sweep may have written stamp + 1)
+    }
+    for (u64 i = tid; i < n; i += nt) {
+      const u32 l = __ldcg(&lev[i]);
+      if (l != LOC_INF) atomicMax(&far[pass], ((unsigned long long)l << 32) | (LOC_INF - (u32)i));
+    }
+    grid.sync();
+    root = LOC_INF - (u32)__ldcg(&far[pass]);
+  }
+  const u32 maxlev = (u32)(__ldcg(&far[1]) >> 32);
+  for (u64 i = tid; i < n; i += nt) {
+    u32 l = __ldcg(&lev[i]);
+    if (l == LOC_INF) l = maxlev + 1;                    // other components: behind the reached ones
+    x[i] = min(l, LOC_MAXLEV) << LOC_FRAC;
+    deg[i] = 0; acc[i] = 0; iota[i] = (u32)i;
+  }
+  grid.sync();
+  for (int sweep = 0; sweep < 2; sweep++) {
+    for (u64 i0 = tid - lane; i0 < ne; i0 += nt) {       // warp-uniform trip count
+      const u64 i = i0 + lane;
+      uint2 e = make_uint2(LOC_INF, LOC_INF);
+      if (i < ne) e = __ldg(&edges[i]);
+      const bool ok = e.x < n && e.y < n;
+      const u32 a = ok ? e.x : LOC_INF;
+      const u32 v = ok ? __ldcg(&x[e.y]) : 0u;
+      // edge lists come sorted by source (src/io.rs reads them in file order): one atomic per run of equal sources
+      const u32 m = __match_any_sync(0xffffffffu, a);
+      const u32 sum = __reduce_add_sync(m, v);           // <= 32 * 63 * 2^20 < 2^32
+      if (ok && lane == __ffs((int)m) - 1) {
+        atomicAdd(&acc[a], (unsigned long long)sum);
+        if (sweep == 0) atomicAdd(&deg[a], (u32)__popc(m));
+      }
+    }
+    grid.sync();
+    for (u64 i = tid; i < n; i += nt) {
+      const unsigned long long t = __ldcg(&acc[i]) + x[i];
+      x[i] = (u32)(t / (__ldcg(&deg[i]) + 1u));
+      acc[i] = 0;
+    }
+    grid.sync();
+  }
+}
+__global__ void invert_order_kernel(const u32* __restrict__ oldid, u32 n, u32* __restrict__ newid) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) newid[oldid[i]] = i;
+}
+
+static bool want_locality_order(u32 n, u64 ne) {
+  const char* env = getenv("FCM_RELABEL");
+  if (env && env[0] == '0') return false;
+  if (env && env[0] == '1') return n >= 2 && ne > 0;
+  return n > LOC_MIN_N && ne > 0;
+}
+
+// g->oldid (kept with the graph: internal id -> caller's id) and *newid_out (caller's id -> internal id, for the build only)
+static int locality_order(fcm_graph* g, const uint2* edges_dev, u64 ne, u32** newid_out) {
+  fcm_ctx* c = g->ctx;
+  cudaStream_t s = c->stream;
+  const u32 n = g->n;
+  int coop = 0;
+  FCM_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device));
+  if (!coop) return FCM_OK;                               // the build then keeps the caller's ids
+  u32 *lev = nullptr, *x = nullptr, *deg = nullptr, *ctl = nullptr, *iota = nullptr, *xs = nullptr, *newid = nullptr;
+  unsigned long long *acc = nullptr, *far = nullptr;
+  void* tmp = nullptr;
+  auto release = [&]() { fcm_pool_free(lev, s); fcm_pool_free(x, s); fcm_pool_free(deg, s); fcm_pool_free(ctl, s); fcm_pool_free(iota, s);
+                         fcm_pool_free(xs, s); fcm_pool_free(acc, s); fcm_pool_free(far, s); fcm_pool_free(tmp, s); };
+#define L_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { fcm_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); release(); fcm_pool_free(newid, s); return FCM_ECUDA; } } while (0)
+  L_CUDA(fcm_pool_alloc(&lev, (size_t)n * 4, s));
+  L_CUDA(fcm_pool_alloc(&x, (size_t)n * 4, s));
+  L_CUDA(fcm_pool_alloc(&deg, (size_t)n * 4, s));
+  L_CUDA(fcm_pool_alloc(&iota, (size_t)n * 4, s));
+  L_CUDA(fcm_pool_alloc(&xs, (size_t)n * 4, s));
+  L_CUDA(fcm_pool_alloc(&newid, (size_t)n * 4, s));
+  L_CUDA(fcm_pool_alloc(&acc, (size_t)n * 8, s));
+  L_CUDA(fcm_pool_alloc(&ctl, 16, s));
+  L_CUDA(fcm_pool_alloc(&far, 16, s));
+  L_CUDA(fcm_pool_alloc(&g->oldid, (size_t)n * 4, s));
+  L_CUDA(cudaMemsetAsync(ctl, 0, 16, s));
+  L_CUDA(cudaMemsetAsync(far, 0, 16, s));
+  int per_sm = 0;
+  L_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, locality_kernel, 256, 0));
+  const u32 blocks = (u32)std::max<u64>(1, std::min<u64>((u64)c->sm_count * std::max(per_sm, 1), (ne + 255) / 256));
+  u64 ne_arg = ne;
+  u32 n_arg = n;
+  void* args[] = {(void*)&edges_dev, (void*)&ne_arg, (void*)&n_arg, (void*)&lev, (void*)&x, (void*)&acc, (void*)&deg, (void*)&ctl, (void*)&far, (void*)&iota};
+  L_CUDA(cudaLaunchCooperativeKernel((const void*)locality_kernel, dim3(blocks), dim3(256), args, 0, s));
+  c->launches++;
+  size_t tbytes = 0;
+  L_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tbytes, x, xs, iota, g->oldid, (int)n, 0, 32, s));
+  L_CUDA(fcm_pool_alloc((unsigned char**)&tmp, std::max<size_t>(tbytes, 16), s));
+  L_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tbytes, x, xs, iota, g->oldid, (int)n, 0, 32, s));
+  invert_order_kernel<<<(n + 255) / 256, 256, 0, s>>>(g->oldid, n, newid);
+  c->launches += 2;
+  L_CUDA(cudaGetLastError());
+#undef L_CUDA
+  release();
+  *newid_out = newid;
+  return FCM_OK;
 }
 
 // one warp per row: out-degree -> off[v + 1] (scanned in place afterwards) and the sort key of the source order
@@ -91,11 +239,14 @@ int fcm_graph_build_device(fcm_graph* g, const uint2* edges_dev, u64 ne_in, int 
   size_t words = (size_t)n * g->W;
   FCM_CUDA(cudaMemsetAsync(g->adj, 0, words * 8, s));
   FCM_CUDA(cudaMemsetAsync(g->ctrl, 0, CT_WORDS * 4, s));
+  u32* newid = nullptr;
+  if (want_locality_order(n, ne_in)) { const int rc = locality_order(g, edges_dev, ne_in, &newid); if (rc) return rc; }
   if (ne_in) {
     int blocks = (int)std::min<u64>((ne_in + 255) / 256, 148 * 16);
-    set_bits_kernel<<<blocks, 256, 0, s>>>(edges_dev, ne_in, n, g->W, normalise, g->adj, g->ctrl);
+    set_bits_kernel<<<blocks, 256, 0, s>>>(edges_dev, ne_in, n, g->W, normalise, newid, g->adj, g->ctrl);
     c->launches++;
   }
+  fcm_pool_free(newid, s);                               // stream-ordered: behind set_bits_kernel
   FCM_CUDA(cudaMemsetAsync(g->csr_off, 0, 8, s));
   u32 *key = nullptr, *val = nullptr, *key2 = nullptr;
   void* tmp = nullptr;
@@ -171,15 +322,19 @@ __host__ __device__ constexpr u32 stack_cap(u32 kcap) { return kcap + 128; }   /
 
 // for_each_cell (flag_complex::for_each_cell, src/bin/all_cxs.rs:60-64): where the cells of dimension
 // emit_min..emit_max go.  Row r of `cells` = the vertices (v0..vd) of one cell, padded with FCM_NONE.
-struct EmitArgs { u32 emit_min, emit_max, stride; u32* cells; u64 cap; unsigned long long* ncells; };
+struct EmitArgs { u32 emit_min, emit_max, stride; u32* cells; u64 cap; unsigned long long* ncells; const u32* oldid; };   // oldid: internal -> caller's ids (null = same)
 
 __device__ __forceinline__ void emit_cell(const EmitArgs& ea, u32 v0, const u32* verts, u64 e, u32 d) {
   if (d < ea.emit_min || d > ea.emit_max) return;
   const u64 row = atomicAdd(ea.ncells, 1ULL);
   if (row >= ea.cap) return;
   u32* out = ea.cells + row * ea.stride;
-  out[0] = v0;
-  for (u32 t = 0; t < ea.stride - 1; t++) out[1 + t] = t < d ? verts[(e >> (10 * t)) & 1023u] : FCM_NONE;
+  out[0] = ea.oldid ? ea.oldid[v0] : v0;
+  for (u32 t = 0; t < ea.stride - 1; t++) {
+    u32 v = FCM_NONE;
+    if (t < d) { v = verts[(e >> (10 * t)) & 1023u]; if (ea.oldid) v = ea.oldid[v]; }
+    out[1 + t] = v;
+  }
 }
 
 // P = candidates for the vertex of index `lvl` (non-empty, already counted).  Generic levels: explicit
@@ -594,7 +749,7 @@ int fcm_count_launch(fcm_graph* g, u32 part, u32 nparts, const CommArgs* comm) {
   u32 kcap;
   // (rows: the actual largest out-degree rounded up to 32, so that more CTAs fit one SM)
   kcap = std::min<u32>(1024u, std::max<u32>(32u, (kmax + 31u) & ~31u));
-  const EmitArgs noemit = {0, 0, 0, nullptr, 0, nullptr};
+  const EmitArgs noemit = {0, 0, 0, nullptr, 0, nullptr, nullptr};
   // sources that do not fit the tile are appended to g->overflow and counted by the dense-row kernel behind
   // this one (their number stays on the device: ctrl[CT_NOVER]); the all-reduce then rides on that kernel
   const bool spill = kmax > kcap;
@@ -621,7 +776,7 @@ int fcm_cells_launch(fcm_graph* g, u32 dim_min, u32 dim_max, u32* cells_dev, u64
   if (kmax > 1024) { fcm_set_error("for_each_cell: out-degree %u exceeds the 1024-column tile", kmax); return FCM_ELIMIT; }
   if (dim_max > (u32)LocalCfg<1>::MAXIDS) { fcm_set_error("for_each_cell: dim_max > %d", LocalCfg<1>::MAXIDS); return FCM_ELIMIT; }
   const u32 kcap = std::min<u32>(1024u, std::max<u32>(32u, (kmax + 31u) & ~31u));
-  const EmitArgs ea = {dim_min, dim_max, dim_max + 1, cells_dev, cap, ncells_dev};
+  const EmitArgs ea = {dim_min, dim_max, dim_max + 1, cells_dev, cap, ncells_dev, g->oldid};
   CommArgs none;
   memset(&none, 0, sizeof(none));
   if (kmax <= 64) return launch_local<1, true>(g, 0, 1, kcap, ea, none);

@@ -48,6 +48,7 @@ struct fcm_graph {
   u64* csr_off = nullptr;           // n + 1
   u32* csr = nullptr;               // ne, each out-list ascending
   u32* order = nullptr;             // vertices by descending out-degree
+  u32* oldid = nullptr;             // n, or null: internal vertex id -> caller's id when the graph was built under the locality order (fcm_count.cu)
   u64* counts = nullptr;            // FCM_MAXD + 1 ([FCM_MAXD]: ranks in error, all-reduce paths only)
   u32* ctrl = nullptr;              // [0] ticket, [1] overflow count, [2] error flag, [3] ticket2
   u32* overflow = nullptr;          // n

@@ -118,6 +118,28 @@ def test_peer_allreduce_device_result_equals_sum(graphs):
     close_all(gs, comms, ctxs)
 
 
+def test_allreduce_over_graphs_built_under_the_locality_order(expected, graphs, monkeypatch):
+    """every rank renumbers the vertices on its own (graphs beyond 4096 vertices; forced here): the numbering is integer
+    arithmetic on the edge list, so the ranks' shards still partition the sources and the sum is the plain count"""
+    monkeypatch.setenv("FCM_RELABEL", "1")
+    ctxs, comms = make_ranks([0, 0, 0], fcm.COMM_PEER)
+    n, e = graphs["c3_er_2000"]
+    gs = [fcm.DeviceGraph(c, n, e) for c in ctxs]
+    got = [None] * 3
+
+    def run(r):
+        got[r] = gs[r].count_allreduce(comms[r])
+    for it in range(2):
+        th = [threading.Thread(target=run, args=(r,)) for r in range(3)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        for r in range(3):
+            assert fcm.directed_scm.trim(got[r]) == expected["c3_er_2000"]["flag_count"], (it, r)
+    close_all(gs, comms, ctxs)
+
+
 def test_missing_rank_times_out_instead_of_hanging(graphs, monkeypatch):
     monkeypatch.setenv("FCM_COMM_TIMEOUT_MS", "150")
     ctxs, comms = make_ranks([0, 0], fcm.COMM_PEER)

@@ -142,6 +142,54 @@ def test_c4_full_size_known_answer(ctx, expected):
     g.close()
 
 
+def test_c4_known_answer_under_the_callers_numbering(ctx, expected, monkeypatch):
+    # the same count with the library's locality order of the vertices switched off
+    monkeypatch.setenv("FCM_RELABEL", "0")
+    n, e = synth.config("c4_geo_31346")
+    g = fcm.DeviceGraph(ctx, n, e)
+    assert g.flagser_count() == expected["c4_geo_31346"]["flag_count"]
+    g.close()
+
+
+def test_locality_order_is_invisible(ctx, graphs, expected, monkeypatch):
+    """Graphs beyond 4096 vertices are built under an internal numbering of the vertices (breadth-first levels from a far
+    vertex, smoothed, sorted: fcm_count.cu); FCM_RELABEL=1 forces it for every graph.  Counts, shard sums, the normalised
+    graph's counts and both kernels are unchanged, and for_each_cell still speaks the caller's ids in the recursion's order."""
+    monkeypatch.setenv("FCM_RELABEL", "1")
+    for name in ("counterexample_any_order", "c2_chunglu_279", "c3_er_2000"):
+        n, e = graphs[name]
+        g = fcm.DeviceGraph(ctx, n, e)
+        assert g.flagser_count() == expected[name]["flag_count"], name
+        whole = g.count_shard(0, 1)
+        tot = np.zeros(N.FCM_MAXD, dtype=np.uint64)
+        for part in range(3):
+            tot += g.count_shard(part, 3)
+        assert np.array_equal(tot, whole), name
+        g.set_kernel(1)
+        assert g.flagser_count() == expected[name]["flag_count"], name
+        g.close()
+        gn = fcm.DeviceGraph(ctx, n, e, normalised=True)
+        assert gn.flagser_count() == expected[name]["ncliques"], name
+        gn.close()
+    for name, dmin, dmax in (("counterexample_any_order", 0, 3), ("c2_chunglu_279", 2, 2)):
+        n, e = graphs[name]
+        g = ds.DeviceGraph(ctx, n, e)
+        assert np.array_equal(g.cells(dmin, dmax), orc.cells(n, e, dmin, dmax)), name
+        g.close()
+    # several components, vertex 0 and others isolated, a two-vertex graph, an edge list in shuffled order
+    e = np.concatenate([rand_graph(40, 0.3, 5, pdouble=0.3) + 1, rand_graph(30, 0.4, 6) + 50]).astype(np.uint32)
+    for n, ee in ((85, e), (2, np.array([[1, 0]], dtype=np.uint32)), (64, rand_graph(64, 0.5, 3, pdouble=0.5))):
+        g = ds.DeviceGraph(ctx, n, ee)
+        assert g.flagser_count() == orc.count(n, ee), n
+        assert np.array_equal(g.cells(0, 2), orc.cells(n, ee, 0, 2)), n
+        g.close()
+    monkeypatch.setenv("FCM_RELABEL", "0")
+    n, e = graphs["c2_chunglu_279"]
+    g = fcm.DeviceGraph(ctx, n, e)
+    assert g.flagser_count() == expected["c2_chunglu_279"]["flag_count"]
+    g.close()
+
+
 @pytest.mark.parametrize("name,dmin,dmax", [("counterexample_any_order", 0, 3), ("c2_chunglu_279", 2, 2),
                                             ("c2_chunglu_279", 0, 6), ("counterexample_seo_greedy_5_start", 1, 4)])
 def test_for_each_cell_matches_oracle_rows(name, dmin, dmax, ctx, graphs):
