@@ -87,6 +87,11 @@ uint64_t fcm_ctx_launches(const fcm_ctx* ctx);
  * 3. Device-resident graph for (sharded) full recounts: State::new's `graph.flagser_count()`
  *    (src/lib.rs:51) and Bounds::calculate's count of the normalised graph (src/lib.rs:125-130).
  *    Adjacency is kept in HBM as packed 64-bit out-neighbour rows (row stride padded to 16 B).
+ *    Graphs of more than 4096 vertices are stored under an internal numbering of the vertices (a locality
+ *    order computed on the device at create: neighbours get nearby ids, which is what the count's gather
+ *    wants).  Counts do not depend on it, fcm_graph_cells reports the caller's ids; which source vertices a
+ *    shard (part, nparts) holds is the library's choice - only the sum over the parts is defined.
+ *    Environment: FCM_RELABEL=0 keeps the caller's ids, FCM_RELABEL=1 renumbers every graph (tests).
  * ---------------------------------------------------------------------------------------------- */
 int fcm_graph_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, const uint32_t (*edges)[2],
                      fcm_graph** out);
