@@ -58,7 +58,8 @@ __global__ void set_bits_kernel(const uint2* __restrict__ edges, u64 ne, u32 n, 
 // therefore built under an internal numbering in which neighbours get nearby ids; fcm_graph_cells maps ids back
 // (EmitArgs::oldid), nothing else of the API sees vertex ids.  The order, all on the device in ONE cooperative launch
 // over the uploaded edge list (no CSR exists yet):
-//   1. breadth-first levels of the undirected graph from vertex 0, level-synchronous sweeps over the edge list;
+//   1. breadth-first levels of the undirected graph from vertex 0, level-synchronous sweeps over the edge list (at most
+//      LOC_MAXLEV of them: what lies deeper is treated as one last level);
 //   2. the same from the farthest vertex found (largest level, smallest id): levels along the graph's long axis;
 //   3. two Jacobi sweeps x[a] <- (x[a] + sum of x[b] over the edges a -> b) / (outdeg(a) + 1) on the level as a fixed-
 //      point number, which turns the handful of levels into a smooth coordinate (C4: 6 levels -> median |i - j| over
@@ -80,7 +81,7 @@ locality_kernel(const uint2* __restrict__ edges, u64 ne, u32 n, u32* lev, u32* x
   for (int pass = 0; pass < 2; pass++) {
     for (u64 i = tid; i < n; i += nt) __stcg(&lev[i], i == root ? 0u : LOC_INF);
     grid.sync();
-    for (u32 L = 0;; L++) {
+    for (u32 L = 0; L < LOC_MAXLEV; L++) {               // deeper levels would be clamped below anyway: a graph of large diameter costs 63 sweeps, not its diameter
       stamp++;
       bool any = false;
       for (u64 i = tid; i < ne; i += nt) {
@@ -174,7 +175,10 @@ static int locality_order(fcm_graph* g, const uint2* edges_dev, u64 ne, u32** ne
   L_CUDA(cudaMemsetAsync(far, 0, 16, s));
   int per_sm = 0;
   L_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, locality_kernel, 256, 0));
-  const u32 blocks = (u32)std::max<u64>(1, std::min<u64>((u64)c->sm_count * std::max(per_sm, 1), (ne + 255) / 256));
+  // all blocks of a cooperative launch must be resident together: at most half of an SM's thread slots, so that the launch
+  // also fits beside a kernel that does not drain (another rank's count waiting in its all-reduce on the same device)
+  per_sm = std::max(1, std::min(per_sm, 4));
+  const u32 blocks = (u32)std::max<u64>(1, std::min<u64>((u64)c->sm_count * per_sm, (ne + 255) / 256));
   u64 ne_arg = ne;
   u32 n_arg = n;
   void* args[] = {(void*)&edges_dev, (void*)&ne_arg, (void*)&n_arg, (void*)&lev, (void*)&x, (void*)&acc, (void*)&deg, (void*)&ctl, (void*)&far, (void*)&iota};

@@ -188,6 +188,18 @@ def test_locality_order_is_invisible(ctx, graphs, expected, monkeypatch):
     g = fcm.DeviceGraph(ctx, n, e)
     assert g.flagser_count() == expected["c2_chunglu_279"]["flag_count"]
     g.close()
+    # beyond 4096 vertices the order is on by default; a graph whose diameter (5999) is far beyond the 63 levels the
+    # sweeps go: a directed path with a transitive triangle at its far end
+    monkeypatch.delenv("FCM_RELABEL")
+    n = 6000
+    path = np.stack([np.arange(n - 1), np.arange(1, n)], 1).astype(np.uint32)
+    ee = np.concatenate([path, np.array([[n - 3, n - 1]], dtype=np.uint32)])
+    g = ds.DeviceGraph(ctx, n, ee)
+    assert g.flagser_count() == [n, n, 1]
+    tri = g.cells(2, 2)
+    assert tri.tolist() == [[n - 3, n - 2, n - 1]]
+    assert np.array_equal(g.cells(1, 1), ee[np.lexsort((ee[:, 1], ee[:, 0]))])
+    g.close()
 
 
 @pytest.mark.parametrize("name,dmin,dmax", [("counterexample_any_order", 0, 3), ("c2_chunglu_279", 2, 2),
