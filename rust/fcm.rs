@@ -108,3 +108,24 @@ extern "C" {
     // no counterpart in the reference (no cudaMalloc inside the call)
     pub fn fcm_graph_count_noalloc(g: *mut FcmGraph, part: u32, nparts: u32, counts: *mut u64, len: *mut c_int) -> c_int;
 }
+
+// ---- the remaining entry points of include/fcm.h: stream / timer / launch counter of a context, asynchronous count,
+//      kernel choice and size queries.  The reference has no counterpart (they are what bench.py and the tests use to
+//      measure and to compare kernels); declared so that this file mirrors the header completely
+//      (tests/test_abi.py::test_rust_shim_declares_every_entry_point). ----
+#[link(name = "fcm")]
+extern "C" {
+    pub fn fcm_ctx_set_stream(ctx: *mut FcmCtx, cuda_stream: *mut c_void) -> c_int;
+    pub fn fcm_ctx_timer_begin(ctx: *mut FcmCtx) -> c_int;
+    pub fn fcm_ctx_timer_end(ctx: *mut FcmCtx, ms_out: *mut f32) -> c_int;
+    pub fn fcm_ctx_launches(ctx: *const FcmCtx) -> u64;
+    pub fn fcm_graph_count_async(g: *mut FcmGraph, part: u32, nparts: u32, counts_dev: *mut *mut u64) -> c_int;
+    pub fn fcm_graph_set_kernel(g: *mut FcmGraph, kind: c_int) -> c_int;
+    pub fn fcm_graph_info(g: *const FcmGraph, n: *mut u32, nedges: *mut u64, words_per_row: *mut u32,
+                          max_out_degree: *mut u32) -> c_int;
+    pub fn fcm_ensemble_set_kernel(e: *mut FcmEnsemble, kind: c_int) -> c_int;
+    pub fn fcm_ensemble_set_stats(e: *mut FcmEnsemble, on: c_int) -> c_int;
+    pub fn fcm_ensemble_index_info(e: *const FcmEnsemble, have_index: *mut c_int, index_bytes: *mut u64) -> c_int;
+    pub fn fcm_ensemble_info(e: *const FcmEnsemble, n: *mut u32, npairs: *mut u64, nchains: *mut u32,
+                             max_common_nbhd: *mut u32, bytes_per_chain: *mut u64) -> c_int;
+}

@@ -28,6 +28,22 @@ def test_library_exports_every_declared_symbol():
     assert L.fcm_abi_version() == 2
 
 
+def test_rust_shim_declares_every_entry_point():
+    """rust/fcm.rs (the binding a maintainer of the reference drops into src/) cannot be compiled here (no rustc): at least
+    keep it in step with the header - every function of include/fcm.h is declared exactly once, and nothing else is."""
+    rs = open(os.path.join(ROOT, "rust", "fcm.rs")).read()
+    declared = re.findall(r"pub fn (fcm_[a-z_0-9]+)\s*\(", rs)
+    assert sorted(declared) == header_symbols()
+    # argument counts agree with the C declarations
+    hdr = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "fcm.h")).read(), flags=re.S)
+    for name in header_symbols():
+        c_args = re.search(r"\b%s\s*\(([^;]*?)\)\s*;" % name, hdr, flags=re.S).group(1)
+        r_args = re.search(r"pub fn %s\s*\((.*?)\)\s*(->|;)" % name, rs, flags=re.S).group(1)
+        nc = 0 if c_args.strip() in ("", "void") else len([a for a in re.sub(r"\([^()]*\)", "", c_args).split(",")])
+        nr = 0 if not r_args.strip() else len([a for a in r_args.split(",") if ":" in a])
+        assert nc == nr, (name, c_args, r_args)
+
+
 def test_no_cpu_fallback_without_device():
     L = N.lib()
     if L.fcm_device_count() > 0:
