@@ -44,6 +44,22 @@ def test_rust_shim_declares_every_entry_point():
         assert nc == nr, (name, c_args, r_args)
 
 
+def test_ctypes_signatures_have_the_headers_argument_counts():
+    """the Python host side binds through ctypes: a drifted argtypes list would corrupt a call silently"""
+    L = N.lib()
+    hdr = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "fcm.h")).read(), flags=re.S)
+    checked = 0
+    for name in header_symbols():
+        f = getattr(L, name)
+        if f.argtypes is None:
+            continue
+        c_args = re.search(r"\b%s\s*\(([^;]*?)\)\s*;" % name, hdr, flags=re.S).group(1)
+        nc = 0 if c_args.strip() in ("", "void") else len(re.sub(r"\([^()]*\)", "", c_args).split(","))
+        assert len(f.argtypes) == nc, (name, c_args, f.argtypes)
+        checked += 1
+    assert checked >= 40
+
+
 def test_no_cpu_fallback_without_device():
     L = N.lib()
     if L.fcm_device_count() > 0:
