@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <thread>
 
 #define REQUIRE(cond, msg)                                 \
@@ -120,14 +121,67 @@ static int weighted_index_init_n(const std::vector<double>& w, double* cum, doub
 // v, by pivoted expansion over sorted candidate lists with bit-row adjacency tests (one host thread
 // per stripe of v).  Order handed to the chains: each clique ascending, cliques lexicographic - the
 // documented assumption of oracle/fcm_oracle.cpp (the crate is not on disk: parity unpinned).
+// Maximal cliques as one flat list: clique c = verts[off[c] .. off[c + 1]), ascending; cliques in lexicographic order.
+struct CliqueList {
+  std::vector<u32> verts;
+  std::vector<u64> off{0};
+  size_t size() const { return off.size() - 1; }
+  const u32* begin(size_t c) const { return verts.data() + off[c]; }
+  u32 order(size_t c) const { return (u32)(off[c + 1] - off[c]); }
+};
+// Bron-Kerbosch with pivoting inside the neighbourhood of one vertex v, everything as bit sets over the local ids
+// 0..d-1 of und[v] (LW 64-bit words): P / X / the local adjacency rows never leave the stack frame.
+template <int LW>
+struct LocalBK {
+  u64 row[LW * 64][LW];
+  u32 R[FCM_MAXD + 2];
+  std::vector<u32>* out;                                // flat: order, then the local ids of the clique (without v)
+  bool too_deep = false;
+  static int popc(const u64* a, const u64* b) { int c = 0; for (int w = 0; w < LW; w++) c += __builtin_popcountll(a[w] & b[w]); return c; }
+  void expand(int depth, u64* P, u64* X) {
+    bool pe = true, xe = true;
+    for (int w = 0; w < LW; w++) { pe &= P[w] == 0; xe &= X[w] == 0; }
+    if (pe) {
+      if (xe) { out->push_back((u32)depth); for (int t = 0; t < depth; t++) out->push_back(R[t]); }
+      return;
+    }
+    if (depth > FCM_MAXD) { too_deep = true; return; }   // a clique beyond FCM_MAXD + 1 vertices: reported by the caller
+    int pivot = -1, best = -1;
+    for (int w = 0; w < LW; w++) {
+      u64 m = P[w] | X[w];
+      while (m) {
+        const int u = w * 64 + __builtin_ctzll(m);
+        m &= m - 1;
+        const int c = popc(P, row[u]);
+        if (c > best) { best = c; pivot = u; }
+      }
+    }
+    u64 cand[LW];
+    for (int w = 0; w < LW; w++) cand[w] = P[w] & ~row[pivot][w];
+    for (int w = 0; w < LW; w++) {
+      u64 m = cand[w];
+      while (m) {
+        const int u = w * 64 + __builtin_ctzll(m);
+        m &= m - 1;
+        u64 P2[LW], X2[LW];
+        for (int y = 0; y < LW; y++) { P2[y] = P[y] & row[u][y]; X2[y] = X[y] & row[u][y]; }
+        R[depth] = (u32)u;
+        expand(depth + 1, P2, X2);
+        P[u >> 6] &= ~(1ULL << (u & 63));
+        X[u >> 6] |= 1ULL << (u & 63);
+      }
+    }
+  }
+};
+// the general form (neighbourhoods beyond 256 vertices): sorted candidate lists, bit-row adjacency tests
 struct CliqueEnum {
   const std::vector<std::vector<u32>>& und;
   const std::vector<u64>& bits;          // n x W undirected bit rows
   u32 W;
-  std::vector<std::vector<u32>> out;
+  std::vector<u32>* out;                 // flat: order, then the clique's vertices (global ids, v included, unsorted)
   bool adj(u32 a, u32 b) const { return (bits[(size_t)a * W + (b >> 6)] >> (b & 63)) & 1ULL; }
   void expand(std::vector<u32>& R, std::vector<u32>& P, std::vector<u32>& X) {
-    if (P.empty()) { if (X.empty()) { out.push_back(R); std::sort(out.back().begin(), out.back().end()); } return; }
+    if (P.empty()) { if (X.empty()) { out->push_back((u32)R.size()); out->insert(out->end(), R.begin(), R.end()); } return; }
     u32 pivot = P[0]; size_t best = 0; bool first = true;
     for (int which = 0; which < 2; which++)
       for (u32 u : (which ? X : P)) {
@@ -155,25 +209,154 @@ static std::vector<u64> undirected_bit_rows(u32 n, const std::vector<std::vector
   for (u32 v = 0; v < n; v++) for (u32 w : und[v]) bits[(size_t)v * W + (w >> 6)] |= 1ULL << (w & 63);
   return bits;
 }
-static std::vector<std::vector<u32>> maximal_cliques(u32 n, const std::vector<std::vector<u32>>& und, const std::vector<u64>& bits, int nthreads) {
+// The cliques whose smallest vertex is v, appended to `raw` as (order, vertices ascending)* in lexicographic order.
+// `local_of` (n entries, thread-private) holds the local id of every neighbour of v while the call runs; `scratch` and
+// `keys` are reused between calls.
+template <int LW>
+static bool cliques_of_vertex_bits(u32 v, const std::vector<u32>& nb, const std::vector<u64>& bits, u32 W, LocalBK<LW>& bk,
+                                   std::vector<u32>& local_of, std::vector<u32>& scratch, std::vector<u64>& keys, std::vector<u32>& raw) {
+  const int d = (int)nb.size();
+  for (int i = 0; i < d; i++) local_of[nb[i]] = (u32)i;
+  // local adjacency rows: row(nb[i]) & row(v), word by word, the surviving bits renamed through local_of
+  const u64* gv = &bits[(size_t)v * W];
+  for (int i = 0; i < d; i++) {
+    for (int w = 0; w < LW; w++) bk.row[i][w] = 0;
+    const u64* gi = &bits[(size_t)nb[i] * W];
+    for (u32 w = 0; w < W; w++) {
+      u64 m = gi[w] & gv[w];
+      while (m) {
+        const u32 l = local_of[w * 64 + (u32)__builtin_ctzll(m)];
+        m &= m - 1;
+        bk.row[i][l >> 6] |= 1ULL << (l & 63);
+      }
+    }
+  }
+  u64 P[LW], X[LW];
+  for (int w = 0; w < LW; w++) P[w] = X[w] = 0;
+  for (int i = 0; i < d; i++) (nb[i] > v ? P : X)[i >> 6] |= 1ULL << (i & 63);
+  scratch.clear();
+  bk.out = &scratch;
+  bk.too_deep = false;
+  bk.expand(0, P, X);
+  if (bk.too_deep) return false;
+  // Lexicographic order of the group.  und[v] is ascending, so local ids order like vertices: a clique of at most 7
+  // members besides v packs into one u64 (9 bits per member, local id + 1, first member in the top bits, 0 = "no more":
+  // a prefix sorts before its extensions), and the group is a sort of integers.  Larger cliques: compare the lists.
+  bool packable = true;
+  for (size_t x = 0; x < scratch.size(); x += scratch[x] + 1) {
+    const u32 o = scratch[x];
+    if (o > 7) packable = false;
+    std::sort(scratch.begin() + x + 1, scratch.begin() + x + 1 + o);
+  }
+  if (packable) {
+    keys.clear();
+    for (size_t x = 0; x < scratch.size(); x += scratch[x] + 1) {
+      u64 k = 0;
+      for (u32 t = 0; t < 7; t++) k = (k << 9) | (t < scratch[x] ? (u64)(scratch[x + 1 + t] + 1) : 0ULL);
+      keys.push_back(k);
+    }
+    std::sort(keys.begin(), keys.end());
+    for (u64 k : keys) {
+      const size_t at = raw.size();
+      raw.push_back(0);
+      raw.push_back(v);
+      for (int t = 6; t >= 0; t--) { const u32 l = (u32)((k >> (9 * t)) & 511u); if (l) raw.push_back(nb[l - 1]); }
+      raw[at] = (u32)(raw.size() - at - 1);
+    }
+  } else {
+    std::vector<u32> idx;
+    for (size_t x = 0; x < scratch.size(); x += scratch[x] + 1) idx.push_back((u32)x);
+    std::sort(idx.begin(), idx.end(), [&](u32 a, u32 b) {
+      return std::lexicographical_compare(scratch.begin() + a + 1, scratch.begin() + a + 1 + scratch[a],
+                                          scratch.begin() + b + 1, scratch.begin() + b + 1 + scratch[b]);
+    });
+    for (u32 a : idx) {
+      raw.push_back(scratch[a] + 1);
+      raw.push_back(v);
+      for (u32 t = 0; t < scratch[a]; t++) raw.push_back(nb[scratch[a + 1 + t]]);
+    }
+  }
+  return true;
+}
+// *too_big: a clique of more than FCM_MAXD + 1 vertices was met (the list is then incomplete)
+static CliqueList maximal_cliques(u32 n, const std::vector<std::vector<u32>>& und, const std::vector<u64>& bits, int nthreads, bool* too_big) {
   const u32 W = (n + 63) / 64;
-  std::vector<std::vector<std::vector<u32>>> part(nthreads);
+  // per vertex: where its group sits in its thread's raw buffer, how many cliques / vertices it holds
+  struct Group { u64 at = 0, ncl = 0, nv = 0; };
+  std::vector<Group> grp(n);
+  std::vector<std::vector<u32>> raws(nthreads);
+  std::vector<int> deep(nthreads, 0);
   std::vector<std::thread> th;
   for (int t = 0; t < nthreads; t++)
     th.emplace_back([&, t]() {
-      CliqueEnum ce{und, bits, W, {}};
+      std::vector<u32>& raw = raws[t];
+      std::vector<u32> scratch, grp_raw, idx, local_of(n, 0);
+      std::vector<u64> keys;
+      auto bk1 = std::make_unique<LocalBK<1>>();
+      auto bk2 = std::make_unique<LocalBK<2>>();
+      auto bk4 = std::make_unique<LocalBK<4>>();
       for (u32 v = t; v < n; v += nthreads) {
-        std::vector<u32> R{v}, P, X;
-        for (u32 w : und[v]) (w > v ? P : X).push_back(w);
-        ce.expand(R, P, X);
+        const std::vector<u32>& nb = und[v];
+        Group& g = grp[v];
+        g.at = raw.size();
+        bool ok = true;
+        if (nb.size() <= 64) ok = cliques_of_vertex_bits<1>(v, nb, bits, W, *bk1, local_of, scratch, keys, raw);
+        else if (nb.size() <= 128) ok = cliques_of_vertex_bits<2>(v, nb, bits, W, *bk2, local_of, scratch, keys, raw);
+        else if (nb.size() <= 256) ok = cliques_of_vertex_bits<4>(v, nb, bits, W, *bk4, local_of, scratch, keys, raw);
+        else {
+          CliqueEnum ce{und, bits, W, &scratch};
+          scratch.clear();
+          std::vector<u32> R{v}, P, X;
+          for (u32 w : nb) (w > v ? P : X).push_back(w);
+          ce.expand(R, P, X);
+          grp_raw.clear();
+          for (size_t x = 0; x < scratch.size();) {
+            const u32 o = scratch[x++];
+            grp_raw.push_back(o);
+            const size_t at = grp_raw.size();
+            for (u32 k = 0; k < o; k++) grp_raw.push_back(scratch[x++]);
+            std::sort(grp_raw.begin() + at, grp_raw.end());
+          }
+          idx.clear();
+          for (size_t x = 0; x < grp_raw.size(); x += grp_raw[x] + 1) idx.push_back((u32)x);
+          std::sort(idx.begin(), idx.end(), [&](u32 a, u32 b) {
+            return std::lexicographical_compare(grp_raw.begin() + a + 1, grp_raw.begin() + a + 1 + grp_raw[a],
+                                                grp_raw.begin() + b + 1, grp_raw.begin() + b + 1 + grp_raw[b]);
+          });
+          for (u32 a : idx) raw.insert(raw.end(), grp_raw.begin() + a, grp_raw.begin() + a + 1 + grp_raw[a]);
+        }
+        if (!ok) { deep[t] = 1; continue; }
+        // what the group holds: walk it once
+        g.ncl = 0; g.nv = 0;
+        for (size_t x = g.at; x < raw.size(); x += raw[x] + 1) { g.ncl++; g.nv += raw[x]; }
       }
-      part[t] = std::move(ce.out);
     });
   for (auto& t : th) t.join();
-  std::vector<std::vector<u32>> all;
-  for (auto& pt : part) for (auto& c : pt) all.push_back(std::move(c));
-  std::sort(all.begin(), all.end());
-  return all;
+  CliqueList cl;
+  *too_big = false;
+  for (int d : deep) if (d) *too_big = true;
+  if (*too_big) return cl;
+  // groups in ascending v = all cliques in lexicographic order; every thread copies its own groups into place
+  std::vector<u64> cbase(n + 1, 0), vbase(n + 1, 0);
+  for (u32 v = 0; v < n; v++) { cbase[v + 1] = cbase[v] + grp[v].ncl; vbase[v + 1] = vbase[v] + grp[v].nv; }
+  cl.off.assign(cbase[n] + 1, 0);
+  cl.verts.resize(vbase[n]);
+  th.clear();
+  for (int t = 0; t < nthreads; t++)
+    th.emplace_back([&, t]() {
+      const std::vector<u32>& raw = raws[t];
+      for (u32 v = t; v < n; v += nthreads) {
+        u64 x = grp[v].at, c = cbase[v], o = vbase[v];
+        for (u64 k = 0; k < grp[v].ncl; k++) {
+          const u32 ord = raw[x++];
+          cl.off[c++] = o;
+          for (u32 y = 0; y < ord; y++) cl.verts[o++] = raw[x++];
+        }
+      }
+    });
+  for (auto& t : th) t.join();
+  cl.off[cbase[n]] = vbase[n];
+  return cl;
 }
 
 // ---- compute_edge_neighborhoods (src/lib.rs:331-356) on the device: for every adjacent pair (big, small)
@@ -515,20 +698,22 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
   {
     std::vector<u32> rk(p.npairs);
     for (u64 q = 0; q < p.npairs; q++) rk[q] = (u32)q;
-    std::sort(rk.begin(), rk.end(), [&](u32 x, u32 y) { return pkey(pair_ab[x].x, pair_ab[x].y) < pkey(pair_ab[y].x, pair_ab[y].y); });
+    auto key_less = [&](u32 x, u32 y) { return pkey(pair_ab[x].x, pair_ab[x].y) < pkey(pair_ab[y].x, pair_ab[y].y); };
+    if (!std::is_sorted(rk.begin(), rk.end(), key_less)) std::sort(rk.begin(), rk.end(), key_less);   // (pair ids are dealt in key order by default)
     for (u64 r = 0; r < p.npairs; r++) { pkeys[r] = pkey(pair_ab[rk[r]].x, pair_ab[rk[r]].y); pkey_pair[r] = rk[r]; }
     for (u64 r = 0; r < p.npairs; r++) pkey_begin[(size_t)(pkeys[r] >> 32) + 1]++;
     for (u32 v = 0; v < n; v++) pkey_begin[v + 1] += pkey_begin[v];
   }
   if (want_cliques) {
     if (und_bits.empty()) und_bits = undirected_bit_rows(n, und);
-    std::vector<std::vector<u32>> cl = maximal_cliques(n, und, und_bits, nthreads);
+    bool too_big = false;
+    const CliqueList cl = maximal_cliques(n, und, und_bits, nthreads, &too_big);
     lap("maximal cliques (host threads)");
     size_t maxo = 0;
-    for (auto& c : cl) maxo = std::max(maxo, c.size());
-    if (maxo > FCM_MAXD) { fcm_set_error("a maximal clique of order %zu (> %d)", maxo, FCM_MAXD); return fail(FCM_EDIM); }
+    for (size_t ci = 0; ci < cl.size(); ci++) maxo = std::max<size_t>(maxo, cl.order(ci));
+    if (too_big || maxo > FCM_MAXD) { fcm_set_error("a maximal clique of order %s%d", too_big ? "> " : "", too_big ? FCM_MAXD : (int)maxo); return fail(FCM_EDIM); }
     std::vector<u64> cnt(maxo, 0);
-    for (auto& c : cl) cnt[c.size() - 1]++;
+    for (size_t ci = 0; ci < cl.size(); ci++) cnt[cl.order(ci) - 1]++;
     u64 base = 0;
     for (size_t o = 0; o < maxo; o++) {
       if (cnt[o] > 0xffffffffULL || base > 0xffffffffULL) { fcm_set_error("too many maximal cliques"); return fail(FCM_ELIMIT); }
@@ -536,13 +721,14 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
     }
     cq_verts.resize(std::max<u64>(base, 1));
     std::vector<u64> fill(maxo, 0);
-    for (auto& c : cl) {                               // lexicographic order is kept inside every order
-      const size_t o = c.size() - 1;
-      std::copy(c.begin(), c.end(), cq_verts.begin() + p.cq_base[o] + fill[o] * (o + 1));
+    for (size_t ci = 0; ci < cl.size(); ci++) {        // lexicographic order is kept inside every order
+      const size_t o = cl.order(ci) - 1;
+      std::copy(cl.begin(ci), cl.begin(ci) + o + 1, cq_verts.begin() + p.cq_base[o] + fill[o] * (o + 1));
       fill[o]++;
     }
     // |edgeset_neighborhood| of a permutation of a clique: its vertices + the common neighbours of its pairs; the largest
-    // one sizes the full path's local matrix (host threads, one mark array each)
+    // one sizes the full path's local matrix (host threads, one mark array each; the pair of two vertices by binary
+    // search in the key run of the bigger one)
     u32 kunion = 0;
     {
       std::vector<u32> best(nthreads, 0);
@@ -550,14 +736,18 @@ extern "C" int fcm_ensemble_create(fcm_ctx* ctx, uint32_t n, uint64_t nedges, co
       for (int t = 0; t < nthreads; t++) th.emplace_back([&, t]() {
         std::vector<u32> mark(n, 0);
         u32 stamp = 0, mx = 0;
-        for (size_t ci = t; ci < cl.size(); ci += nthreads) {
-          const std::vector<u32>& c = cl[ci];
+        const size_t c0 = cl.size() * t / nthreads, c1 = cl.size() * (t + 1) / nthreads;
+        for (size_t ci = c0; ci < c1; ci++) {
+          const u32* c = cl.begin(ci);
+          const u32 ord = cl.order(ci);
           stamp++;
           u32 usz = 0;
-          for (u32 v : c) if (mark[v] != stamp) { mark[v] = stamp; usz++; }
-          for (size_t i = 0; i < c.size(); i++)
-            for (size_t j = i + 1; j < c.size(); j++) {
-              const u32 q = e->pairmap.find(pkey(c[j], c[i]))->second;
+          for (u32 i = 0; i < ord; i++) if (mark[c[i]] != stamp) { mark[c[i]] = stamp; usz++; }
+          for (u32 i = 0; i < ord; i++)
+            for (u32 j = i + 1; j < ord; j++) {
+              const u64 key = pkey(c[j], c[i]);          // ascending clique: c[j] is the bigger vertex
+              const u64* lo = std::lower_bound(pkeys.data() + pkey_begin[c[j]], pkeys.data() + pkey_begin[c[j] + 1], key);
+              const u32 q = pkey_pair[lo - pkeys.data()];
               for (u64 x = nb_off[q]; x < nb_off[q + 1]; x++) if (mark[nb_list[x]] != stamp) { mark[nb_list[x]] = stamp; usz++; }
             }
           mx = std::max(mx, usz);
