@@ -26,7 +26,7 @@ SYMBOLS = [
     "fcm_ensemble_edgebits_info", "fcm_ensemble_edgebits_slots", "fcm_ensemble_edgebits",
     "fcm_ensemble_read_doubles", "fcm_ensemble_restore",
     "fcm_graph_status", "fcm_comm_create", "fcm_comm_connect", "fcm_comm_destroy",
-    "fcm_graph_count_allreduce_async", "fcm_graph_count_allreduce", "fcm_graph_count_noalloc", "fcm_ensemble_set_policy",
+    "fcm_graph_count_allreduce_async", "fcm_graph_count_allreduce", "fcm_graph_count_noalloc", "fcm_ensemble_set_policy", "fcm_maximal_cliques",
 ]
 
 
@@ -87,6 +87,7 @@ def lib():
     L.fcm_graph_info.argtypes = [vp, P(u32), P(u64), P(u32), P(u32)]
     L.fcm_graph_cells.argtypes = [vp, i32, i32, vp, u64, P(u64)]
     L.fcm_edge_neighborhoods.argtypes = [vp, u32, u64, vp, P(u64), P(u64), vp, vp, vp]
+    L.fcm_maximal_cliques.argtypes = [u32, u64, vp, P(u64), P(u64), vp, vp]
     L.fcm_ensemble_create.argtypes = [vp, u32, u64, vp, u32, vp, vp, i32, vp, i32, vp, i32, vp, P(vp)]
     L.fcm_ensemble_destroy.argtypes = [vp]
     L.fcm_ensemble_set_bounds.argtypes = [vp, vp, i32, vp, i32]

@@ -508,6 +508,35 @@ extern "C" int fcm_edge_neighborhoods(fcm_ctx* ctx, uint32_t n, uint64_t nedges,
   return FCM_OK;
 }
 
+// Graph::compute_maximal_cliques (src/lib.rs:41) as a call of its own: host threads, no device (include/fcm.h)
+extern "C" int fcm_maximal_cliques(uint32_t n, uint64_t nedges, const uint32_t (*edges)[2], uint64_t* ncliques_out,
+                                   uint64_t* nverts_out, uint32_t* sizes_out, uint32_t* verts_out) {
+  REQUIRE(ncliques_out && nverts_out, "ncliques/nverts is null");
+  REQUIRE(nedges == 0 || edges, "edges is null");
+  REQUIRE((sizes_out == nullptr) == (verts_out == nullptr), "sizes_out and verts_out go together");
+  std::vector<std::vector<u32>> und(n);
+  for (u64 i = 0; i < nedges; i++) {
+    const u32 a = edges[i][0], b = edges[i][1];
+    if (a >= n || b >= n || a == b) { fcm_set_error("edge %llu = (%u,%u): vertex id >= n or self loop", (unsigned long long)i, a, b); return FCM_EINVAL; }
+    und[a].push_back(b); und[b].push_back(a);
+  }
+  for (auto& l : und) { std::sort(l.begin(), l.end()); l.erase(std::unique(l.begin(), l.end()), l.end()); }
+  const int nthreads = (int)std::max(1u, std::min(std::thread::hardware_concurrency(), 32u));
+  bool too_big = false;
+  const CliqueList cl = maximal_cliques(n, und, undirected_bit_rows(n, und), nthreads, &too_big);
+  if (too_big) { fcm_set_error("a maximal clique of order > %d", FCM_MAXD); return FCM_EDIM; }
+  for (size_t c = 0; c < cl.size(); c++)
+    if (cl.order(c) > (u32)FCM_MAXD) { fcm_set_error("a maximal clique of order %u (> %d)", cl.order(c), FCM_MAXD); return FCM_EDIM; }
+  if (sizes_out) {
+    REQUIRE(*ncliques_out >= cl.size() && *nverts_out >= cl.verts.size(), "buffers are smaller than the first call reported");
+    for (size_t c = 0; c < cl.size(); c++) sizes_out[c] = cl.order(c);
+    if (!cl.verts.empty()) memcpy(verts_out, cl.verts.data(), cl.verts.size() * 4);
+  }
+  *ncliques_out = cl.size();
+  *nverts_out = cl.verts.size();
+  return FCM_OK;
+}
+
 extern "C" int fcm_ensemble_destroy(fcm_ensemble* e) {
   if (!e) return FCM_OK;
   if (e->ctx) { cudaSetDevice(e->ctx->device); cudaStreamSynchronize(e->ctx->stream); }

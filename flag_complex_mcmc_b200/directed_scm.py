@@ -346,6 +346,29 @@ def compute_edge_neighborhoods(ctx, n, edges):
     return {(int(a), int(b)): [int(x) for x in lst[int(off[q]):int(off[q + 1])]] for q, (a, b) in enumerate(pairs)}
 
 
+def compute_maximal_cliques(n, edges):
+    """Graph::compute_maximal_cliques (external crate, called by State::new, src/lib.rs:41): the maximal cliques of the
+    underlying undirected graph, vertices ascending, cliques in lexicographic order.  Host code in the reference and here
+    (libfcm.so runs the same enumeration inside fcm_ensemble_create); needs no device."""
+    e = edges_array(edges)
+    nc, nv = C.c_uint64(), C.c_uint64()
+    check(lib().fcm_maximal_cliques(int(n), int(e.shape[0]), ptr(e), C.byref(nc), C.byref(nv), None, None))
+    sizes = np.zeros(max(nc.value, 1), dtype=np.uint32)
+    verts = np.zeros(max(nv.value, 1), dtype=np.uint32)
+    check(lib().fcm_maximal_cliques(int(n), int(e.shape[0]), ptr(e), C.byref(nc), C.byref(nv), ptr(sizes), ptr(verts)))
+    ends = np.cumsum(sizes[:nc.value], dtype=np.int64)
+    return [verts[int(b) - int(k):int(b)].tolist() for k, b in zip(sizes[:nc.value], ends)]
+
+
+def cliques_by_order(n, edges):
+    """State::cliques_by_order (src/lib.rs:41-49): cliques_by_order[k] = the maximal cliques of k + 1 vertices"""
+    cl = compute_maximal_cliques(n, edges)
+    out = [[] for _ in range(max((len(c) for c in cl), default=0))]
+    for c in cl:
+        out[len(c) - 1].append(c)
+    return out
+
+
 def undirected_edges(edges):
     """[a,b] with a > b once per adjacent pair (src/lib.rs:344 asserts a > b)."""
     e = edges_array(edges)

@@ -184,6 +184,17 @@ int fcm_edge_neighborhoods(fcm_ctx* ctx, uint32_t n, uint64_t nedges, const uint
                            uint64_t* npairs, uint64_t* list_len, uint32_t* pairs_out,
                            uint64_t* off_out, uint32_t* list_out);
 
+/* Graph::compute_maximal_cliques of the external flag-complex crate (called by State::new, src/lib.rs:41-49, which
+ * files the cliques by order into State::cliques_by_order): the maximal cliques of the underlying undirected graph,
+ * each with its vertices ascending, the cliques in lexicographic order (the order the oracle assumes; parity
+ * unpinned).  HOST code - it is host code in the reference too, fcm_ensemble_create runs the same
+ * enumeration on host threads and needs no device for it; this entry point exposes that step so that a port of
+ * State::new can fill cliques_by_order, and so that it is tested without a GPU.  Call with sizes_out = verts_out = NULL
+ * to get *ncliques and *nverts (= sum of the orders), then with sizes_out[ncliques], verts_out[nverts].
+ * FCM_EDIM for a clique of more than FCM_MAXD vertices (the chain kernels' limit). */
+int fcm_maximal_cliques(uint32_t n, uint64_t nedges, const uint32_t (*edges)[2], uint64_t* ncliques, uint64_t* nverts,
+                        uint32_t* sizes_out, uint32_t* verts_out);
+
 /* ------------------------------------------------------------------------------------------------
  * 4. Ensemble of independent chains on one device: MCMCSampler (src/lib.rs:164-198), one warp per
  *    chain.  All chains start from the same graph (edge order = insertion order of the edge list,

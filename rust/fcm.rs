@@ -128,4 +128,7 @@ extern "C" {
     pub fn fcm_ensemble_index_info(e: *const FcmEnsemble, have_index: *mut c_int, index_bytes: *mut u64) -> c_int;
     pub fn fcm_ensemble_info(e: *const FcmEnsemble, n: *mut u32, npairs: *mut u64, nchains: *mut u32,
                              max_common_nbhd: *mut u32, bytes_per_chain: *mut u64) -> c_int;
+    // Graph::compute_maximal_cliques (src/lib.rs:41): host code, no device; two-call sizing like fcm_edge_neighborhoods
+    pub fn fcm_maximal_cliques(n: u32, nedges: u64, edges: *const [Node; 2], ncliques: *mut u64, nverts: *mut u64,
+                               sizes_out: *mut u32, verts_out: *mut u32) -> c_int;
 }

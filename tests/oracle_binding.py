@@ -34,6 +34,8 @@ def lib():
     L.orc_count_sources.argtypes = [u32, u64, vp, vp, u32, vp]
     L.orc_count_sources_mt.argtypes = [u32, u64, vp, vp, u32, i32, vp]
     L.orc_ncliques.argtypes = [u32, u64, vp, i32, vp, P(i32)]
+    L.orc_maximal_cliques.argtypes = [u32, u64, vp, vp, vp, P(u64)]
+    L.orc_maximal_cliques.restype = u64
     L.orc_rng_seed.argtypes = [u64, vp]
     L.orc_rng_seed.restype = None
     L.orc_rng_next.argtypes = [vp]
@@ -112,6 +114,21 @@ def count_sources_mt(n, edges, sources, nthreads):
     out = np.zeros(ORC_MAXD, dtype=np.uint64)
     rc = lib().orc_count_sources_mt(int(n), e.shape[0], _p(e), _p(s), int(s.size), int(nthreads), _p(out))
     assert rc == 0
+    return out
+
+
+def maximal_cliques(n, edges):
+    """compute_maximal_cliques of the restatement: list of ascending vertex lists, lexicographic"""
+    e = _e(edges)
+    tot = C.c_uint64()
+    nc = lib().orc_maximal_cliques(int(n), e.shape[0], _p(e), None, None, C.byref(tot))
+    sizes = np.zeros(max(nc, 1), dtype=np.uint32)
+    verts = np.zeros(max(tot.value, 1), dtype=np.uint32)
+    lib().orc_maximal_cliques(int(n), e.shape[0], _p(e), _p(sizes), _p(verts), C.byref(tot))
+    out, at = [], 0
+    for k in sizes[:nc]:
+        out.append([int(v) for v in verts[at:at + int(k)]])
+        at += int(k)
     return out
 
 
