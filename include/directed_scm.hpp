@@ -206,6 +206,29 @@ inline Counts flagser_count(Context& ctx, uint32_t n, const std::vector<Edge>& e
   return trim(counts, len);
 }
 
+// graph.compute_maximal_cliques() (external crate, src/lib.rs:41): vertices ascending, cliques lexicographic.  Host code.
+inline std::vector<std::vector<Node>> compute_maximal_cliques(uint32_t n, const std::vector<Edge>& edges) {
+  const auto* e = reinterpret_cast<const uint32_t(*)[2]>(edges.data());
+  uint64_t nc = 0, nv = 0;
+  check(fcm_maximal_cliques(n, edges.size(), e, &nc, &nv, nullptr, nullptr));
+  std::vector<uint32_t> sizes(nc ? nc : 1), verts(nv ? nv : 1);
+  check(fcm_maximal_cliques(n, edges.size(), e, &nc, &nv, sizes.data(), verts.data()));
+  std::vector<std::vector<Node>> out;
+  out.reserve(nc);
+  size_t at = 0;
+  for (uint64_t c = 0; c < nc; c++) { out.emplace_back(verts.begin() + at, verts.begin() + at + sizes[c]); at += sizes[c]; }
+  return out;
+}
+// State::new's filing by order (src/lib.rs:42-49): cliques_by_order[k - 1] = the maximal cliques of k vertices
+inline std::vector<std::vector<std::vector<Node>>> cliques_by_order(uint32_t n, const std::vector<Edge>& edges) {
+  std::vector<std::vector<std::vector<Node>>> by;
+  for (auto& c : compute_maximal_cliques(n, edges)) {
+    if (c.size() > by.size()) by.resize(c.size());
+    by[c.size() - 1].push_back(std::move(c));
+  }
+  return by;
+}
+
 const double MOVE_DISTRIBUTION_SIMPLE[4] = {0.5, 0.5, 0.0, 0.0};   // src/bin/sample.rs:16
 const double MOVE_DISTRIBUTION[4] = {0.1, 0.1, 0.6, 0.2};          // src/bin/sample.rs:17
 

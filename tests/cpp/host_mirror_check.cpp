@@ -34,6 +34,16 @@ int main(int argc, char** argv) {
       printf("{\"n\": %u, \"nedges\": %zu, \"edges_fnv\": %llu}\n", ge.first, ge.second.size(), (unsigned long long)h);
       return 0;
     }
+    if (argc >= 3 && !strcmp(argv[1], "cliques")) {          // sizes of cliques_by_order + an FNV hash of the clique list
+      auto ge = read_flag_file(argv[2]);
+      const auto by = cliques_by_order(ge.first, ge.second);
+      uint64_t h = 1469598103934665603ULL;
+      for (const auto& c : compute_maximal_cliques(ge.first, ge.second)) { for (Node x : c) { h ^= x; h *= 1099511628211ULL; } h ^= 0xffu; h *= 1099511628211ULL; }
+      printf("{\"by_order\": [");
+      for (size_t k = 0; k < by.size(); k++) printf("%s%zu", k ? ", " : "", by[k].size());
+      printf("], \"fnv\": %llu}\n", (unsigned long long)h);
+      return 0;
+    }
     if (argc < 6 || strcmp(argv[1], "run")) { fprintf(stderr, "usage: %s selfcheck | run file.flag seed nsteps simple\n", argv[0]); return 2; }
     auto ge = read_flag_file(argv[2]);
     const uint64_t seed = strtoull(argv[3], 0, 10), nsteps = strtoull(argv[4], 0, 10);

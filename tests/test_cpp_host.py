@@ -34,6 +34,25 @@ def test_cpp_host_maths_match_python_mirror_and_oracle(driver):
     assert r["relax_de"] == ds.calc_relax_de(sc)
 
 
+def test_cpp_cliques_by_order_matches_oracle(driver, tmp_path, graphs):
+    """compute_maximal_cliques + State::new's filing by order (src/lib.rs:41-49) through the C++ mirror: host code, no device"""
+    for name in ("counterexample_any_order", "c2_chunglu_279"):
+        n, e = graphs[name]
+        f = str(tmp_path / (name + ".flag"))
+        ds.save_flag_file(f, n, e)
+        r = json.loads(subprocess.check_output([driver, "cliques", f]))
+        want = orc.maximal_cliques(n, e)
+        by = [0] * max(len(c) for c in want)
+        h = 1469598103934665603
+        for c in want:
+            by[len(c) - 1] += 1
+            for x in c:
+                h = ((h ^ int(x)) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+            h = ((h ^ 0xFF) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+        assert r["by_order"] == by, name
+        assert r["fnv"] == h, name
+
+
 def fnv(edges):
     h = 1469598103934665603
     for x in np.asarray(edges, dtype=np.uint64).reshape(-1):
