@@ -36,6 +36,31 @@ def test_random_graphs_match_the_oracle(n, p, seed):
     assert got == sorted(got) and all(c == sorted(c) for c in got)
 
 
+def brute_force_maximal_cliques(n, e):
+    """every vertex subset that is a clique and has no common neighbour outside it (n <= 12)"""
+    adj = [[False] * n for _ in range(n)]
+    for a, b in e:
+        adj[a][b] = adj[b][a] = True
+    out = []
+    for mask in range(1, 1 << n):
+        vs = [v for v in range(n) if (mask >> v) & 1]
+        if all(adj[a][b] for a, b in itertools.combinations(vs, 2)) and \
+                not any(all(adj[w][v] for v in vs) for w in range(n) if not (mask >> w) & 1):
+            out.append(vs)
+    return sorted(out)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_small_graphs_against_brute_force(seed):
+    """pins the oracle's enumeration (and the library's) to the definition itself"""
+    r = np.random.default_rng(100 + seed)
+    n = int(r.integers(1, 12))
+    e = rand_graph(n, float(r.uniform(0.1, 0.8)), seed)
+    want = brute_force_maximal_cliques(n, e.tolist())
+    assert orc.maximal_cliques(n, e) == want
+    assert fcm.compute_maximal_cliques(n, e) == want
+
+
 def test_word_widths_and_the_general_form():
     """neighbourhoods of <= 64 / 128 / 256 vertices use 1 / 2 / 4-word sets, larger ones the list form: a hub joined to
     everything on top of a sparse graph walks through all of them"""
